@@ -1,0 +1,142 @@
+"""Source generation and compilation drivers (host side, run once per model).
+
+Plays the role of ``pybamm.codegen.compilation.aot_compile`` in the reference
+(packages/pybamm/src/pybamm/codegen/compilation.py:61-196: CasADi CodeGenerator -> C ->
+gcc -> shared object, cached on disk), but the product target is an sm_100a kernel image:
+
+  bundle (.npz) --codegen--> <name>_cuda.h --nvcc--> pybamm_b200/_build/pbgpu_model_<name>.so
+                \\-codegen--> <name>_c.h    --gcc---> oracle/_build/oracle_<name>.so   (tests / CPU baseline only)
+"""
+from __future__ import annotations
+
+import hashlib
+import json
+import os
+import subprocess
+
+from .bundle import ModelBundle
+from . import codegen
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(PKG)
+BUILD = os.path.join(PKG, "_build")
+CSRC = os.path.join(PKG, "csrc")
+MODELS = os.path.join(PKG, "models")
+ORACLE = os.path.join(ROOT, "oracle")
+
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-Xcompiler", "-fPIC", "--shared", "-Xptxas", "-v"]
+
+
+def load_bundle(name_or_path) -> ModelBundle:
+    path = name_or_path
+    if not os.path.exists(path):
+        path = os.path.join(MODELS, f"{name_or_path}.npz")
+    return ModelBundle.load(path)
+
+
+def _write_if_changed(path, text):
+    if os.path.exists(path):
+        with open(path) as f:
+            if f.read() == text:
+                return False
+    os.makedirs(os.path.dirname(path), exist_ok=True)
+    with open(path, "w") as f:
+        f.write(text)
+    return True
+
+
+def _src_digest(paths):
+    h = hashlib.sha256()
+    for p in paths:
+        with open(p, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+def generate(bundle: ModelBundle, dialect: str, outdir=BUILD):
+    text, info = codegen.generate(bundle, dialect)
+    path = os.path.join(outdir, f"{bundle.name}_{dialect}.h")
+    _write_if_changed(path, text)
+    with open(os.path.join(outdir, f"{bundle.name}_{dialect}.json"), "w") as f:
+        json.dump(info, f, indent=1)
+    return path, info
+
+
+def build_oracle(bundle: ModelBundle, force=False):
+    """Compile the CPU oracle for a bundle (tests / bench cpu_baseline only)."""
+    outdir = os.path.join(ORACLE, "_build")
+    os.makedirs(outdir, exist_ok=True)
+    header, _ = generate(bundle, "c", outdir)
+    out = os.path.join(outdir, f"oracle_{bundle.name}.so")
+    srcs = [os.path.join(ORACLE, f) for f in ("ida_oracle.c", "model_shim.c", "pbo_model.h")] + [header]
+    stamp = out + ".stamp"
+    dig = _src_digest(srcs)
+    if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:
+        return out
+    cmd = ["make", "-s", "-C", ORACLE, "-B", f"MODEL={bundle.name}", f"HEADER={header}", f"OUT={out}"]
+    subprocess.run(cmd, check=True)
+    with open(stamp, "w") as f:
+        f.write(dig)
+    return out
+
+
+def build_model(bundle: ModelBundle, force=False, team=None, verbose=False):
+    """Generate + nvcc-compile the sm_100a solver image of a bundle. Returns the .so path."""
+    os.makedirs(BUILD, exist_ok=True)
+    header, info = generate(bundle, "cuda", BUILD)
+    out = os.path.join(BUILD, f"pbgpu_model_{bundle.name}.so")
+    kernel_srcs = [os.path.join(CSRC, f) for f in ("pbgpu_model.cu", "pbgpu_ida.cuh", "pbgpu_team.cuh")]
+    inc = os.path.join(ROOT, "include")
+    srcs = kernel_srcs + [header, os.path.join(inc, "pbgpu.h")]
+    if team is None:
+        team = default_team(bundle)
+    dig = _src_digest(srcs) + f"-t{team}"
+    stamp = out + ".stamp"
+    if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:
+        return out
+    cmd = [NVCC] + NVCC_FLAGS + [f"-DPBM_HEADER=\"{header}\"", f"-DPB_TEAM_SIZE={team}", f"-I{inc}", f"-I{CSRC}",
+                                 kernel_srcs[0], "-o", out]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    log = r.stdout + r.stderr
+    with open(os.path.join(BUILD, f"pbgpu_model_{bundle.name}.ptxas.log"), "w") as f:
+        f.write(" ".join(cmd) + "\n" + log)
+    if verbose or r.returncode != 0:
+        print(log)
+    if r.returncode != 0:
+        raise RuntimeError(f"nvcc failed for model {bundle.name}")
+    with open(stamp, "w") as f:
+        f.write(dig)
+    return out
+
+
+def default_team(bundle: ModelBundle) -> int:
+    """Threads per system: one warp for small models, a CTA of several warps for large ones."""
+    n = bundle.n_states
+    if n <= 128:
+        return 32
+    if n <= 512:
+        return 64
+    if n <= 2048:
+        return 128
+    return 256
+
+
+def build_api(force=False):
+    """Compile the generic C-ABI host library libpbgpu.so (include/pbgpu.h)."""
+    os.makedirs(BUILD, exist_ok=True)
+    out = os.path.join(BUILD, "libpbgpu.so")
+    src = os.path.join(CSRC, "pbgpu_api.cpp")
+    inc = os.path.join(ROOT, "include")
+    dig = _src_digest([src, os.path.join(inc, "pbgpu.h")])
+    stamp = out + ".stamp"
+    if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:
+        return out
+    cuda_home = os.path.dirname(os.path.dirname(NVCC))
+    cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-pthread", f"-I{inc}", f"-I{cuda_home}/include", src, "-o", out,
+           f"-L{cuda_home}/lib64", "-lcudart", "-ldl", f"-Wl,-rpath,{cuda_home}/lib64"]
+    subprocess.run(cmd, check=True)
+    with open(stamp, "w") as f:
+        f.write(dig)
+    return out

@@ -1,0 +1,322 @@
+"""Emit model functions (residual, J - cj*M, events, initial conditions, output
+variables) and the static sparse-LU tables as C / CUDA source.
+
+Replaces the CasADi functions that ``IDAKLUSolver.set_up`` serialises for the native
+solver (packages/pybamm/src/pybamm/solvers/idaklu_solver.py:402-628) and the optional
+gcc AOT path (packages/pybamm/src/pybamm/codegen/compilation.py:61-196).
+
+One generator, two dialects selected by preprocessor macros of the including file:
+
+* ``cuda``: team-parallel device functions for sm_100a.  A *team* (one warp or one
+  CTA) evaluates one system; every stage walks (template, 32-instance tile) pairs
+  warp by warp; per-instance tables are slot-major so that lanes read consecutive
+  entries; stages are separated by ``PB_SYNC()``.
+* ``c``: the same programs as plain scalar C loops for the CPU oracle / CPU baseline
+  (``oracle/``).  The Jacobian is written in the bundle's CSC entry order there, and
+  into the LU slots of ``symbolic_lu`` in the CUDA dialect.
+"""
+from __future__ import annotations
+
+import hashlib
+
+import numpy as np
+
+from . import ir
+from .program import Program, build_program
+from . import symbolic_lu as slu
+
+_FMT = "%.17g"
+
+
+def _dlit(v):
+    v = float(v)
+    if np.isnan(v):
+        return "PB_NAN"
+    if np.isinf(v):
+        return "PB_INF" if v > 0 else "(-PB_INF)"
+    s = _FMT % v
+    if "." not in s and "e" not in s and "n" not in s:
+        s += ".0"
+    return s
+
+
+_UN = {
+    ir.NEG: "(-{a})", ir.ABS: "fabs({a})", ir.EXP: "exp({a})", ir.LOG: "log({a})", ir.SQRT: "sqrt({a})",
+    ir.TANH: "tanh({a})", ir.SINH: "sinh({a})", ir.COSH: "cosh({a})", ir.SIN: "sin({a})", ir.COS: "cos({a})",
+    ir.ASINH: "asinh({a})", ir.ATAN: "atan({a})", ir.ERF: "erf({a})", ir.ERFC: "erfc({a})",
+    ir.FLOOR: "floor({a})", ir.CEIL: "ceil({a})", ir.RECIP: "(1.0 / {a})", ir.SQR: "({a} * {a})",
+    ir.LOG10: "log10({a})", ir.SIGN: "(({a} > 0.0) - ({a} < 0.0))",
+}
+_BIN = {
+    ir.ADD: "({a} + {b})", ir.SUB: "({a} - {b})", ir.MUL: "({a} * {b})", ir.DIV: "({a} / {b})",
+    ir.POW: "pow({a}, {b})", ir.MIN: "fmin({a}, {b})", ir.MAX: "fmax({a}, {b})",
+    ir.LT: "(({a} < {b}) ? 1.0 : 0.0)", ir.LE: "(({a} <= {b}) ? 1.0 : 0.0)",
+    ir.MOD: "({a} - floor({a} / {b}) * {b})", ir.HYPOT: "hypot({a}, {b})",
+}
+
+
+class _Emitter:
+    def __init__(self, prefix):
+        self.prefix = prefix
+        self.tables = []     # lines
+        self.code = []
+        self.table_bytes = 0
+        self._ntab = 0
+
+    def table(self, ctype, values, hint="t"):
+        name = f"{self.prefix}_{hint}{self._ntab}"
+        self._ntab += 1
+        vals = list(values)
+        if ctype == "double":
+            body = ", ".join(_dlit(v) for v in vals)
+            self.table_bytes += 8 * len(vals)
+        else:
+            body = ", ".join(str(int(v)) for v in vals)
+            self.table_bytes += (2 if "short" in ctype else 4) * len(vals)
+        self.tables.append(f"static PB_TABLE const {ctype} {name}[{max(len(vals), 1)}] = {{{body if vals else '0'}}};")
+        return name
+
+
+def _itype(maxval):
+    return "unsigned short" if maxval < 65536 else "int"
+
+
+def _slot_expr(em, values, q, hint):
+    """Expression for per-instance integer ``values`` indexed by instance ``q``."""
+    vals = np.asarray(values, dtype=np.int64)
+    if len(vals) == 0:
+        return "0"
+    if np.all(vals == vals[0]):
+        return str(int(vals[0]))
+    d = vals[1] - vals[0]
+    if len(vals) > 2 and np.all(np.diff(vals) == d):
+        return f"({int(vals[0])} + {int(d)} * {q})"
+    if len(vals) == 2:
+        return f"({int(vals[0])} + {int(d)} * {q})"
+    name = em.table(_itype(int(vals.max())), vals, hint)
+    return f"(int)PB_LD({name}[{q}])"
+
+
+def _emit_template(em: _Emitter, tp, dest, lines, ind):
+    """Body of one template for instance index ``q`` (already in scope)."""
+    n = tp.n_inst
+    s_idx = np.asarray(tp.s_idx, dtype=np.int64).reshape(n, tp.n_s)
+    c_val = np.asarray(tp.c_val, dtype=np.float64).reshape(n, tp.n_c)
+    m_idx = np.asarray(tp.m_idx, dtype=np.int64).reshape(n, tp.n_m)
+    refs = {}
+    for k in range(tp.n_s):
+        e = _slot_expr(em, s_idx[:, k], "q", "s")
+        lines.append(f"{ind}const double s{k} = y[{e}];")
+        refs[("s", k)] = f"s{k}"
+    for k in range(tp.n_c):
+        col = c_val[:, k]
+        if np.all(col == col[0]) or (np.all(np.isnan(col))):
+            refs[("c", k)] = _dlit(col[0])
+        else:
+            name = em.table("double", col, "c")
+            lines.append(f"{ind}const double c{k} = PB_LD({name}[q]);")
+            refs[("c", k)] = f"c{k}"
+    for k in range(tp.n_m):
+        e = _slot_expr(em, m_idx[:, k], "q", "m")
+        lines.append(f"{ind}const double m{k} = tmp[{e}];")
+        refs[("m", k)] = f"m{k}"
+
+    def ref(r):
+        kind = r[0]
+        if kind == "v":
+            return f"v{r[1]}"
+        if kind == "i":
+            return f"p[{r[1]}]"
+        if kind == "t":
+            return "t"
+        if kind == "j":
+            return "cj"
+        return refs[r]
+
+    for k, (o, args) in enumerate(tp.body):
+        a = [ref(r) for r in args]
+        if o == ir.SELECT:
+            e = f"(({a[0]} != 0.0) ? {a[1]} : {a[2]})"
+        elif o in _UN:
+            e = _UN[o].format(a=a[0])
+        else:
+            e = _BIN[o].format(a=a[0], b=a[1])
+        lines.append(f"{ind}const double v{k} = {e};")
+    oe = _slot_expr(em, tp.out, "q", "o")
+    lines.append(f"{ind}{dest}[{oe}] = {ref(tp.result)};")
+
+
+def emit_program(prog: Program, fname: str, prefix: str):
+    """Return (tables_text, function_text)."""
+    em = _Emitter(prefix)
+    L = []
+    L.append(f"PB_FN void {fname}(const double* PB_RESTRICT y, const double* PB_RESTRICT p, const double t, const double cj, "
+             f"double* PB_RESTRICT out, double* PB_RESTRICT tmp) {{")
+    L.append("  (void)y; (void)p; (void)t; (void)cj; (void)out; (void)tmp;")
+    for si, st in enumerate(prog.stages):
+        tiles_tp, tiles_base = [], []
+        tpls = [(t, "tmp") for t in st.to_tmp] + [(t, "out") for t in st.to_out]
+        # tiles sorted by descending cost so that round-robin over warps balances
+        order = sorted(range(len(tpls)), key=lambda k: -tpls[k][0].cost)
+        for k in order:
+            t = tpls[k][0]
+            for base in range(0, t.n_inst, 32):
+                tiles_tp.append(k)
+                tiles_base.append(base)
+        nt = len(tiles_tp)
+        if si > 0:
+            L.append("  PB_SYNC();")
+        if nt == 0:
+            continue
+        if len(tpls) == 1:
+            t, dest = tpls[0]
+            L.append(f"  for (int q = PB_TID; q < {t.n_inst}; q += PB_TEAM) {{")
+            _emit_template(em, t, dest, L, "    ")
+            L.append("  }")
+            continue
+        ttp = em.table("unsigned char" if len(tpls) < 256 else "unsigned short", tiles_tp, "tt")
+        tbs = em.table(_itype(max(tiles_base) if tiles_base else 0), tiles_base, "tb")
+        L.append(f"  for (int tile = PB_WARP; tile < {nt}; tile += PB_NWARPS) {{")
+        L.append(f"    const int tb = (int)PB_LDU({tbs}[tile]);")
+        L.append(f"    switch ((int)PB_LDU({ttp}[tile])) {{")
+        for k, (t, dest) in enumerate(tpls):
+            L.append(f"    case {k}: {{")
+            L.append(f"      const int qe = (tb + 32 < {t.n_inst}) ? tb + 32 : {t.n_inst};")
+            L.append("      for (int q = tb + PB_LANE; q < qe; q += PB_LANES) {")
+            _emit_template(em, t, dest, L, "        ")
+            L.append("      }")
+            L.append("    } break;")
+        L.append("    }")
+        L.append("  }")
+    L.append("}")
+    return "\n".join(em.tables), "\n".join(L), em.table_bytes
+
+
+def _emit_jds(em_lines, name, j: slu.JDS, slot_max):
+    it = _itype(slot_max)
+
+    def arr(ctype, suffix, vals):
+        vals = list(np.asarray(vals).reshape(-1))
+        body = ", ".join(str(int(v)) for v in vals) if vals else "0"
+        em_lines.append(f"static PB_TABLE const {ctype} {name}_{suffix}[{max(len(vals), 1)}] = {{{body}}};")
+
+    em_lines.append(f"#define {name.upper()}_NLEV {j.n_levels}")
+    arr("int", "lev_task", j.lev_task)
+    arr("int", "lev_row", j.lev_row)
+    arr("int", "row_start", j.row_start)
+    arr(it, "row_cnt", j.row_cnt)
+    arr(it, "op_a", j.op_a)
+    arr(it, "op_b", j.op_b)
+    arr(it, "task_out", j.task_out)
+    arr(it, "task_aux", j.task_aux)
+    arr("unsigned char", "sync", j.sync)
+
+
+def model_functions(bundle, sym: slu.SymbolicLU | None, dialect: str):
+    """Build the Programs of a bundle. dialect 'c' -> Jacobian in CSC order; 'cuda' -> LU slots."""
+    g = bundle.graph
+    cjn = g.cj()
+    jroots = [g.sub(int(n), cjn) if (r == c and r < bundle.n_diff) else int(n)
+              for n, r, c in zip(bundle.jac_nodes, bundle.jac_rows, bundle.jac_cols)]
+    progs = {}
+    progs["res"] = build_program(g, bundle.rhs_alg, "res")
+    if dialect == "cuda":
+        progs["jac"] = build_program(g, jroots, "jac", out_index=sym.a_slot, n_out=sym.nnz_lu)
+    else:
+        progs["jac"] = build_program(g, jroots, "jac")
+    progs["events"] = build_program(g, bundle.events, "events")
+    progs["ic"] = build_program(g, bundle.ic, "ic")
+    vroots = [int(n) for name in bundle.variables for n in bundle.variables[name]]
+    progs["vars"] = build_program(g, vroots, "vars")
+    return progs
+
+
+def sample_matrices(bundle, p_nominal=None, n_samples=2, seed=0):
+    """Values of J - cj*M (bundle CSC order) at a few states / cj for pivot-order selection."""
+    g = bundle.graph
+    rng = np.random.default_rng(seed)
+    if p_nominal is None:
+        p_nominal = bundle.meta.get("nominal_inputs")
+    if p_nominal is None:
+        raise ValueError("nominal inputs are needed to sample the Jacobian")
+    p = np.asarray(p_nominal, dtype=np.float64)
+    y0 = g.evaluate(bundle.ic, 0.0, None, p)
+    diag = (bundle.jac_rows == bundle.jac_cols) & (bundle.jac_rows < bundle.n_diff)
+    out = []
+    for cj in (1.0, 1e-3, 1e3, 0.03, 30.0):
+        for k in range(n_samples):
+            y = y0 * (1.0 + (0.02 * rng.standard_normal(len(y0)) if k else 0.0))
+            pk = p * (1.0 + (0.05 * rng.standard_normal(len(p)) if k else 0.0))
+            v = g.evaluate(bundle.jac_nodes, 0.0, y, pk)
+            if not np.all(np.isfinite(v)):
+                continue
+            out.append(v - cj * diag)
+    # the consistent-initialisation matrix: identity on differential rows, J on algebraic rows
+    if bundle.n_alg:
+        v = g.evaluate(bundle.jac_nodes, 0.0, y0, p)
+        drow = bundle.jac_rows < bundle.n_diff
+        out.append(np.where(drow, diag.astype(float), v))
+    return out
+
+
+def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
+    """Return (source_text, info dict). The text is a header included by the integrator
+    translation unit (CUDA) or the oracle model shim (C)."""
+    if dialect == "cuda" and sym is None:
+        sym = slu.analyse(bundle.n_states, bundle.jac_rows, bundle.jac_cols, sample_matrices(bundle))
+    progs = model_functions(bundle, sym, dialect)
+    n_tmp = max(p.n_tmp for p in progs.values())
+    n_var = progs["vars"].n_out
+    out = []
+    out.append(f"/* generated by pybamm_b200.codegen ({dialect}) -- do not edit */")
+    out.append(f'#define PBM_NAME "{bundle.name}"')
+    out.append(f"#define PBM_N {bundle.n_states}")
+    out.append(f"#define PBM_NDIFF {bundle.n_diff}")
+    out.append(f"#define PBM_NP {max(bundle.n_inputs, 1)}")
+    out.append(f"#define PBM_NP_REAL {bundle.n_inputs}")
+    out.append(f"#define PBM_NEV {bundle.n_events}")
+    out.append(f"#define PBM_NNZ {len(bundle.jac_nodes)}")
+    out.append(f"#define PBM_NTMP {max(n_tmp, 1)}")
+    out.append(f"#define PBM_NVAR {n_var}")
+    info = dict(n_tmp=n_tmp, n_var=n_var, table_bytes=0, programs={})
+    for key in ("res", "jac", "events", "ic", "vars"):
+        tabs, fn, tb = emit_program(progs[key], f"pbm_{key}", f"pbm_{key}")
+        out.append(tabs)
+        out.append(fn)
+        info["table_bytes"] += tb
+        pr = progs[key]
+        info["programs"][key] = dict(stages=len(pr.stages), flops=pr.flops, transcendental=pr.n_transcendental,
+                                     n_tmp=pr.n_tmp,
+                                     templates=sum(len(s.to_tmp) + len(s.to_out) for s in pr.stages))
+        out.append(f"#define PBM_FLOPS_{key.upper()} {pr.flops}")
+    if dialect == "cuda":
+        out.append(f"#define PBM_NNZ_LU {sym.nnz_lu}")
+        lines = []
+        fill = sorted(set(range(sym.nnz_lu)) - set(int(s) for s in sym.a_slot))
+        it = _itype(sym.nnz_lu)
+        lines.append(f"#define PBM_NFILL {len(fill)}")
+        lines.append(f"static PB_TABLE const {it} pbm_fill[{max(len(fill), 1)}] = {{{', '.join(map(str, fill)) if fill else '0'}}};")
+        # per structural entry: 0 algebraic row, 1 differential row off-diagonal, 2 differential diagonal
+        kind = np.where(bundle.jac_rows < bundle.n_diff, np.where(bundle.jac_rows == bundle.jac_cols, 2, 1), 0)
+        lines.append(f"static PB_TABLE const unsigned char pbm_ent_kind[{len(kind)}] = {{{', '.join(map(str, kind.tolist()))}}};")
+        lines.append(f"static PB_TABLE const {it} pbm_ent_slot[{len(kind)}] = {{{', '.join(str(int(s)) for s in sym.a_slot)}}};")
+        lines.append(f"static PB_TABLE const {it} pbm_diag_slot[{sym.n}] = {{{', '.join(str(int(s)) for s in sym.diag_slot)}}};")
+        _emit_jds(lines, "pbm_fac", sym.factor, max(sym.nnz_lu, sym.n, 0xFFFF))
+        _emit_jds(lines, "pbm_fwd", sym.fwd, max(sym.nnz_lu, sym.n))
+        _emit_jds(lines, "pbm_bwd", sym.bwd, max(sym.nnz_lu, sym.n))
+        out.append("\n".join(lines))
+        out.append(f"#define PBM_FLOPS_FACTOR {sym.flops_factor}")
+        out.append(f"#define PBM_FLOPS_SOLVE {sym.flops_solve}")
+        info["lu"] = dict(nnz_lu=sym.nnz_lu, ordering=sym.ordering, factor_levels=sym.factor.n_levels,
+                          fwd_levels=sym.fwd.n_levels, bwd_levels=sym.bwd.n_levels,
+                          factor_team_syncs=int(sym.factor.sync.sum()),
+                          solve_team_syncs=int(sym.fwd.sync.sum() + sym.bwd.sync.sum()),
+                          flops_factor=sym.flops_factor, flops_solve=sym.flops_solve)
+    else:
+        rows = ", ".join(str(int(r)) for r in bundle.jac_rows)
+        cols = ", ".join(str(int(c)) for c in bundle.jac_cols)
+        out.append(f"static const int pbm_jac_rows[{len(bundle.jac_rows)}] = {{{rows}}};")
+        out.append(f"static const int pbm_jac_cols[{len(bundle.jac_cols)}] = {{{cols}}};")
+    text = "\n".join(out) + "\n"
+    info["sha"] = hashlib.sha256(text.encode()).hexdigest()[:16]
+    return text, info

@@ -22,7 +22,7 @@ import numpy as np
 # ---------------------------------------------------------------------------
 # op codes
 # ---------------------------------------------------------------------------
-CONST, STATE, INPUT, TIME = 0, 1, 2, 3
+CONST, STATE, INPUT, TIME, CJ = 0, 1, 2, 3, 4   # CJ: the BDF leading coefficient cj (Jacobian of F wrt y' scale)
 ADD, SUB, MUL, DIV, POW, MIN, MAX = 10, 11, 12, 13, 14, 15, 16
 LT, LE, MOD, HYPOT = 17, 18, 19, 20
 NEG, ABS, SIGN, EXP, LOG, SQRT, TANH, SINH, COSH = 30, 31, 32, 33, 34, 35, 36, 37, 38
@@ -30,14 +30,14 @@ SIN, COS, ASINH, ATAN, ERF, FLOOR, CEIL, RECIP, SQR = 39, 40, 41, 42, 43, 44, 45
 LOG10, ERFC = 48, 49
 SELECT = 60  # SELECT(c, a, b) = c != 0 ? a : b
 
-LEAF_OPS = (CONST, STATE, INPUT, TIME)
+LEAF_OPS = (CONST, STATE, INPUT, TIME, CJ)
 BINARY_OPS = (ADD, SUB, MUL, DIV, POW, MIN, MAX, LT, LE, MOD, HYPOT)
 UNARY_OPS = (NEG, ABS, SIGN, EXP, LOG, SQRT, TANH, SINH, COSH, SIN, COS, ASINH,
              ATAN, ERF, FLOOR, CEIL, RECIP, SQR, LOG10, ERFC)
 COMMUTATIVE = (ADD, MUL, MIN, MAX, HYPOT)
 
 OP_NAMES = {
-    CONST: "const", STATE: "state", INPUT: "input", TIME: "time",
+    CONST: "const", STATE: "state", INPUT: "input", TIME: "time", CJ: "cj",
     ADD: "add", SUB: "sub", MUL: "mul", DIV: "div", POW: "pow", MIN: "min", MAX: "max",
     LT: "lt", LE: "le", MOD: "mod", HYPOT: "hypot",
     NEG: "neg", ABS: "abs", SIGN: "sign", EXP: "exp", LOG: "log", SQRT: "sqrt",
@@ -50,7 +50,7 @@ OP_NAMES = {
 # materialisation decision in program.py and for the work model of DESIGN.md;
 # transcendental lengths were read off cuobjdump -sass of libdevice calls).
 OP_COST = {
-    CONST: 0, STATE: 0, INPUT: 0, TIME: 0,
+    CONST: 0, STATE: 0, INPUT: 0, TIME: 0, CJ: 0,
     ADD: 1, SUB: 1, MUL: 1, DIV: 10, POW: 60, MIN: 1, MAX: 1, LT: 1, LE: 1, MOD: 20,
     HYPOT: 12, NEG: 0, ABS: 0, SIGN: 2, EXP: 20, LOG: 25, SQRT: 8, TANH: 30, SINH: 35,
     COSH: 30, SIN: 30, COS: 30, ASINH: 45, ATAN: 35, ERF: 35, FLOOR: 1, CEIL: 1,
@@ -148,6 +148,9 @@ class Graph:
 
     def time(self) -> int:
         return self._new(TIME)
+
+    def cj(self) -> int:
+        return self._new(CJ)
 
     def is_const(self, n) -> bool:
         return self.op[n] == CONST
@@ -342,7 +345,7 @@ class Graph:
         return st, inp, tm
 
     # -- numpy evaluation (test/oracle helper; vectorised over a batch) ----
-    def evaluate(self, roots, t=0.0, y=None, p=None):
+    def evaluate(self, roots, t=0.0, y=None, p=None, cj=0.0):
         """Evaluate roots. y: (N,) or (B,N); p: (P,) or (B,P). Returns (len(roots),) or (B,len(roots))."""
         roots = np.asarray(roots, dtype=np.int64).reshape(-1)
         y = None if y is None else np.asarray(y, dtype=np.float64)
@@ -361,6 +364,8 @@ class Graph:
                     v = p[..., int(self.val[n])]
                 elif o == TIME:
                     v = np.asarray(t, dtype=np.float64)
+                elif o == CJ:
+                    v = np.float64(cj)
                 elif o == SELECT:
                     v = np.where(vals[self.a0[n]] != 0.0, vals[self.a1[n]], vals[self.a2[n]])
                 elif o in _UNARY_NUMPY:
@@ -567,6 +572,8 @@ class Graph:
                 m = g.input(self.val[n])
             elif o == TIME:
                 m = g.time()
+            elif o == CJ:
+                m = g.cj()
             elif o == SELECT:
                 m = g._new(o, remap[self.a0[n]], remap[self.a1[n]], remap[self.a2[n]])
             elif o in UNARY_OPS:

@@ -1,0 +1,433 @@
+"""Static-pattern sparse LU: ordering, symbolic factorisation and level schedules.
+
+Role in the reference: SuiteSparse KLU behind ``SUNLinSol_KLU``
+(idaklu_source/IDAKLUSolverOpenMP_solvers.hpp:29-33): a fill-reducing ordering and
+a pivot sequence are fixed by the first factorisation and *reused* by every later
+``klu_refactor``.  Here the same idea is taken to its end for a batch of systems
+that share one sparsity pattern: the pivot order is chosen once, at code
+generation time, from sample matrices ``J - cj*M``; the fill pattern, the
+dependency levels and every index the numeric phase needs are emitted as tables,
+so that the device kernels contain no searching, no pivoting and no indirection
+beyond one table look-up per multiply-add.
+
+Numeric phase the tables describe (all in one value array ``lu`` of length nnz_lu,
+slot order chosen here):
+
+factor:   entry-parallel left-looking LU.  The task for entry (i, j) of
+          B = P A Q computes  v = b_ij - sum_{k<min(i,j)} l_ik u_kj ;
+          U entries store v (the diagonal stores 1/v), L entries store v/u_jj.
+          Tasks are grouped in dependency levels; inside a level they are
+          sorted by length and their operand lists are stored jagged-diagonal
+          (JDS) so that lanes read consecutive table entries.
+solve:    row tasks of the unit-lower and upper triangular solves, again in
+          levels with JDS operand lists; the row/column permutations are folded
+          into the first gather and the last scatter.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+import scipy.sparse as sp
+import scipy.sparse.linalg as spla
+
+
+@dataclass
+class JDS:
+    """Jagged-diagonal task tables for a sequence of levels."""
+    n_levels: int
+    lev_task: np.ndarray     # (n_levels+1,) task range per level
+    lev_row: np.ndarray      # (n_levels+1,) jagged-row range per level
+    row_start: np.ndarray    # (n_rows,) offset into the operand arrays
+    row_cnt: np.ndarray      # (n_rows,) number of tasks that have this operand
+    op_a: np.ndarray         # operand A (lu slot)
+    op_b: np.ndarray         # operand B (lu slot for factor, w index for solves)
+    task_out: np.ndarray     # per task: output slot / row
+    task_aux: np.ndarray     # per task: aux (factor: diag slot or code; solve: diag slot / gather index)
+    sync: np.ndarray         # (n_levels,) 1 = team barrier after the level, 0 = warp barrier suffices
+
+    @property
+    def n_tasks(self):
+        return len(self.task_out)
+
+    @property
+    def n_ops(self):
+        return len(self.op_a)
+
+
+@dataclass
+class SymbolicLU:
+    n: int
+    nnz_lu: int
+    perm_r: np.ndarray       # B[i, :] = A[perm_r[i], :]
+    perm_c: np.ndarray       # B[:, j] = A[:, perm_c[j]]
+    slot_of: dict            # (i, j) in B coordinates -> slot
+    a_slot: np.ndarray       # for each input entry k of A (rows[k], cols[k]) its slot
+    diag_slot: np.ndarray    # (n,) slot of u_ii (holds 1/u_ii after factor)
+    factor: JDS
+    fwd: JDS
+    bwd: JDS
+    flops_factor: int
+    flops_solve: int
+    ordering: str
+
+    def summary(self):
+        return (f"n={self.n} nnz_lu={self.nnz_lu} ordering={self.ordering} "
+                f"factor: {self.factor.n_levels} levels/{self.factor.n_tasks} tasks/{self.factor.n_ops} ops "
+                f"(team syncs {int(self.factor.sync.sum())}); fwd {self.fwd.n_levels} lv, bwd {self.bwd.n_levels} lv "
+                f"(team syncs {int(self.fwd.sync.sum())}+{int(self.bwd.sync.sum())})")
+
+
+# ---------------------------------------------------------------------------
+# orderings
+# ---------------------------------------------------------------------------
+def _nested_dissection(adj: sp.csr_matrix, leaf=8):
+    """Simple recursive BFS-level-set nested dissection of a symmetric graph.
+
+    Returns an elimination order (separators last).  Good for the chain- and
+    thick-chain-like graphs of 1-D(+1-D) discretisations: elimination-tree height
+    O(log n * separator size) instead of O(n)."""
+    n = adj.shape[0]
+    indptr, indices = adj.indptr, adj.indices
+    order = []
+
+    def bfs_levels(nodes_mask, start):
+        level = {start: 0}
+        frontier = [start]
+        levels = [[start]]
+        while frontier:
+            nxt = []
+            for u in frontier:
+                for v in indices[indptr[u]:indptr[u + 1]]:
+                    if nodes_mask[v] and v not in level:
+                        level[v] = level[u] + 1
+                        nxt.append(v)
+            if nxt:
+                levels.append(nxt)
+            frontier = nxt
+        return levels
+
+    def components(nodes):
+        mask = np.zeros(n, dtype=bool)
+        mask[nodes] = True
+        seen = set()
+        comps = []
+        for s in nodes:
+            if s in seen:
+                continue
+            comp = [s]
+            seen.add(s)
+            stack = [s]
+            while stack:
+                u = stack.pop()
+                for v in indices[indptr[u]:indptr[u + 1]]:
+                    if mask[v] and v not in seen:
+                        seen.add(v)
+                        comp.append(v)
+                        stack.append(v)
+            comps.append(comp)
+        return comps
+
+    def dissect(nodes):
+        """returns list of nodes in elimination order"""
+        if len(nodes) <= leaf:
+            return list(nodes)
+        mask = np.zeros(n, dtype=bool)
+        mask[nodes] = True
+        # pseudo-peripheral start
+        start = nodes[0]
+        for _ in range(3):
+            lv = bfs_levels(mask, start)
+            start = min(lv[-1], key=lambda u: indptr[u + 1] - indptr[u])
+        lv = bfs_levels(mask, start)
+        if len(lv) < 3:
+            return list(nodes)
+        # separator = level closest to balancing the two halves, prefer small levels
+        sizes = np.array([len(x) for x in lv])
+        cum = np.cumsum(sizes)
+        total = cum[-1]
+        best, best_score = None, None
+        for k in range(1, len(lv) - 1):
+            left = cum[k - 1]
+            right = total - cum[k]
+            score = max(left, right) + 4 * sizes[k]
+            if best_score is None or score < best_score:
+                best, best_score = k, score
+        sep = lv[best]
+        rest = [u for k, l in enumerate(lv) if k != best for u in l]
+        out = []
+        for comp in components(rest):
+            out.extend(dissect(comp))
+        out.extend(sep)
+        return out
+
+    all_nodes = list(range(n))
+    for comp in components(all_nodes):
+        order.extend(dissect(comp))
+    return np.asarray(order, dtype=np.int64)
+
+
+def _symbolic_fill(B: sp.csr_matrix):
+    """Row patterns of L (strict lower) and U (upper incl. diagonal) of B without pivoting."""
+    n = B.shape[0]
+    B = B.tocsr()
+    Lrows, Urows = [], []
+    for i in range(n):
+        cols = set(B.indices[B.indptr[i]:B.indptr[i + 1]].tolist())
+        cols.add(i)
+        # up-looking: for k in ascending order of current lower pattern, merge U row k
+        lower = sorted(c for c in cols if c < i)
+        done = set()
+        import heapq
+
+        heap = list(lower)
+        heapq.heapify(heap)
+        while heap:
+            k = heapq.heappop(heap)
+            if k in done:
+                continue
+            done.add(k)
+            for c in Urows[k]:
+                if c > k and c not in cols:
+                    cols.add(c)
+                    if c < i:
+                        heapq.heappush(heap, c)
+        Lrows.append(sorted(c for c in cols if c < i))
+        Urows.append(sorted(c for c in cols if c >= i))
+    return Lrows, Urows
+
+
+def _jds(levels_tasks, n_total_levels=None, warp=32):
+    """levels_tasks: list (per level) of tasks (out, aux, [(a, b), ...])."""
+    lev_task = [0]
+    lev_row = [0]
+    row_start, row_cnt = [], []
+    op_a, op_b = [], []
+    task_out, task_aux = [], []
+    sync = []
+    for li, tasks in enumerate(levels_tasks):
+        tasks = sorted(tasks, key=lambda t: -len(t[2]))
+        for t in tasks:
+            task_out.append(t[0])
+            task_aux.append(t[1])
+        maxlen = len(tasks[0][2]) if tasks else 0
+        for p in range(maxlen):
+            cnt = sum(1 for t in tasks if len(t[2]) > p)
+            row_start.append(len(op_a))
+            row_cnt.append(cnt)
+            for t in tasks[:cnt]:
+                op_a.append(t[2][p][0])
+                op_b.append(t[2][p][1])
+        lev_task.append(len(task_out))
+        lev_row.append(len(row_start))
+        nxt = len(levels_tasks[li + 1]) if li + 1 < len(levels_tasks) else 10 ** 9
+        sync.append(0 if (len(tasks) <= warp and nxt <= warp) else 1)
+    i32 = np.int32
+    return JDS(len(levels_tasks), np.asarray(lev_task, i32), np.asarray(lev_row, i32),
+               np.asarray(row_start, i32), np.asarray(row_cnt, i32), np.asarray(op_a, i32),
+               np.asarray(op_b, i32), np.asarray(task_out, i32), np.asarray(task_aux, i32),
+               np.asarray(sync, np.uint8))
+
+
+AUX_U = 0xFFFF      # factor task writes an off-diagonal U entry
+AUX_DIAG = 0xFFFE   # factor task writes a diagonal entry (stores the reciprocal)
+
+
+def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01) -> SymbolicLU:
+    """rows/cols: structural pattern of A (every entry the numeric phase may set).
+    samples: list of value arrays (same order as rows/cols) used to pick the pivot order
+    and to validate it."""
+    rows = np.asarray(rows, np.int64)
+    cols = np.asarray(cols, np.int64)
+    candidates = []
+    names = ["nd", "COLAMD", "MMD_AT_PLUS_A"] if ordering == "auto" else [ordering]
+    A0 = sp.csc_matrix((np.asarray(samples[0], float), (rows, cols)), shape=(n, n))
+    pat = sp.csr_matrix((np.ones(len(rows)), (rows, cols)), shape=(n, n))
+    for name in names:
+        try:
+            if name == "nd":
+                # row permutation first: a maximum transversal from a pivoting LU so that the
+                # diagonal of A[perm_r] is structurally and numerically sound, then a symmetric ND
+                lu0 = spla.splu(A0, permc_spec="NATURAL", diag_pivot_thresh=diag_pivot_thresh)
+                # SuperLU: Pr A Pc = L U with perm_r[i] = new position of row i
+                pr = np.empty(n, np.int64)
+                pr[lu0.perm_r] = np.arange(n)
+                Bp = pat[pr, :]
+                sym = (Bp + Bp.T).tocsr()
+                sym.setdiag(0)
+                sym.eliminate_zeros()
+                q = _nested_dissection(sym)
+                perm_r = pr[q]
+                perm_c = q
+            else:
+                lu0 = spla.splu(A0, permc_spec=name, diag_pivot_thresh=diag_pivot_thresh)
+                perm_c = np.asarray(lu0.perm_c, np.int64)   # column j of A -> position perm_c[j]
+                pc = np.empty(n, np.int64)
+                pc[perm_c] = np.arange(n)
+                pr = np.empty(n, np.int64)
+                pr[lu0.perm_r] = np.arange(n)
+                perm_r, perm_c = pr, pc
+            candidates.append((name, perm_r, perm_c))
+        except Exception as e:  # pragma: no cover
+            print(f"[symbolic_lu] ordering {name} failed: {e}")
+    best = None
+    for name, perm_r, perm_c in candidates:
+        s = _build(n, rows, cols, perm_r, perm_c, name)
+        # cost proxy: team barriers dominate the numeric phase
+        score = (s.factor.sync.sum() + 4 * (s.fwd.sync.sum() + s.bwd.sync.sum())) * 60 \
+            + (s.factor.n_levels + 4 * (s.fwd.n_levels + s.bwd.n_levels)) * 40 + s.flops_factor / 8 + s.flops_solve / 2
+        ok = all(_validate(s, rows, cols, np.asarray(v, float)) < 1e-6 for v in samples)
+        if not ok:
+            continue
+        if best is None or score < best[0]:
+            best = (score, s)
+    if best is None:
+        raise RuntimeError("no static pivot order passed validation on the sample matrices")
+    return best[1]
+
+
+def _build(n, rows, cols, perm_r, perm_c, name) -> SymbolicLU:
+    inv_r = np.empty(n, np.int64)
+    inv_r[perm_r] = np.arange(n)
+    inv_c = np.empty(n, np.int64)
+    inv_c[perm_c] = np.arange(n)
+    bi, bj = inv_r[rows], inv_c[cols]
+    B = sp.csr_matrix((np.ones(len(rows)), (bi, bj)), shape=(n, n))
+    Lrows, Urows = _symbolic_fill(B)
+    # slots: row-major over (L row, U row)
+    slot_of = {}
+    for i in range(n):
+        for j in Lrows[i]:
+            slot_of[(i, j)] = len(slot_of)
+        for j in Urows[i]:
+            slot_of[(i, j)] = len(slot_of)
+    nnz_lu = len(slot_of)
+    diag_slot = np.array([slot_of[(i, i)] for i in range(n)], np.int64)
+    a_slot = np.array([slot_of[(int(i), int(j))] for i, j in zip(bi, bj)], np.int64)
+
+    # column structure of U for pairing: Ucols[j] = {k: (k, j) in U}
+    Lset = [set(r) for r in Lrows]
+    Ucol = [[] for _ in range(n)]
+    for k in range(n):
+        for j in Urows[k]:
+            Ucol[j].append(k)
+    # factor tasks with levels
+    level = {}
+    tasks_by_level = {}
+    flops = 0
+    for i in range(n):
+        row_entries = [(i, j) for j in Lrows[i]] + [(i, j) for j in Urows[i]]
+        for (_, j) in row_entries:
+            m = min(i, j)
+            pairs = []
+            lv = 0
+            # k in L-pattern of row i with k < m and (k, j) in U
+            for k in Lrows[i]:
+                if k >= m:
+                    break
+                if (k, j) in slot_of:
+                    pairs.append((slot_of[(i, k)], slot_of[(k, j)]))
+                    lv = max(lv, level[(i, k)] + 1, level[(k, j)] + 1)
+            if i > j:
+                lv = max(lv, level[(j, j)] + 1)
+                aux = slot_of[(j, j)]
+            elif i == j:
+                aux = AUX_DIAG
+            else:
+                aux = AUX_U
+            level[(i, j)] = lv
+            tasks_by_level.setdefault(lv, []).append((slot_of[(i, j)], aux, pairs))
+            flops += 2 * len(pairs) + 1
+    nlev = max(tasks_by_level) + 1
+    factor = _jds([tasks_by_level.get(l, []) for l in range(nlev)])
+
+    # forward solve: w[i] = b[perm_r[i]] - sum_k L[i,k] w[k]
+    rl = np.zeros(n, np.int64)
+    fl = {}
+    sflops = 0
+    for i in range(n):
+        lv = 0
+        ops = []
+        for k in Lrows[i]:
+            ops.append((slot_of[(i, k)], k))
+            lv = max(lv, rl[k] + 1)
+        rl[i] = lv
+        fl.setdefault(lv, []).append((i, int(perm_r[i]), ops))
+        sflops += 2 * len(ops)
+    fwd = _jds([fl.get(l, []) for l in range(max(fl) + 1)])
+    # backward solve: w[i] = (w[i] - sum_{j>i} U[i,j] w[j]) * lu[diag_i]; x[perm_c[i]] = w[i]
+    rb = np.zeros(n, np.int64)
+    blv = {}
+    for i in range(n - 1, -1, -1):
+        lv = 0
+        ops = []
+        for j in Urows[i]:
+            if j == i:
+                continue
+            ops.append((slot_of[(i, j)], j))
+            lv = max(lv, rb[j] + 1)
+        rb[i] = lv
+        blv.setdefault(lv, []).append((i, int(perm_c[i]), ops))
+        sflops += 2 * len(ops) + 1
+    bwd = _jds([blv.get(l, []) for l in range(max(blv) + 1)])
+    return SymbolicLU(n, nnz_lu, np.asarray(perm_r), np.asarray(perm_c), slot_of, a_slot, diag_slot,
+                      factor, fwd, bwd, flops, sflops, name)
+
+
+# ---------------------------------------------------------------------------
+# numpy emulation of the numeric phase (validation of tables; tests)
+# ---------------------------------------------------------------------------
+def numeric_factor(s: SymbolicLU, a_vals):
+    lu = np.zeros(s.nnz_lu)
+    np.add.at(lu, s.a_slot, a_vals)
+    f = s.factor
+    for lv in range(f.n_levels):
+        t0, t1 = f.lev_task[lv], f.lev_task[lv + 1]
+        nt = t1 - t0
+        acc = lu[f.task_out[t0:t1]].copy()
+        for r in range(f.lev_row[lv], f.lev_row[lv + 1]):
+            c = f.row_cnt[r]
+            st = f.row_start[r]
+            acc[:c] -= lu[f.op_a[st:st + c]] * lu[f.op_b[st:st + c]]
+        aux = f.task_aux[t0:t1]
+        out = f.task_out[t0:t1]
+        for q in range(nt):
+            if aux[q] == AUX_U:
+                lu[out[q]] = acc[q]
+            elif aux[q] == AUX_DIAG:
+                lu[out[q]] = 1.0 / acc[q]
+            else:
+                lu[out[q]] = acc[q] * lu[aux[q]]
+    return lu
+
+
+def numeric_solve(s: SymbolicLU, lu, b):
+    w = np.zeros(s.n)
+    for jds, back in ((s.fwd, False), (s.bwd, True)):
+        for lv in range(jds.n_levels):
+            t0, t1 = jds.lev_task[lv], jds.lev_task[lv + 1]
+            rows_ = jds.task_out[t0:t1]
+            acc = w[rows_].copy() if back else b[jds.task_aux[t0:t1]].copy()
+            for r in range(jds.lev_row[lv], jds.lev_row[lv + 1]):
+                c = jds.row_cnt[r]
+                st = jds.row_start[r]
+                acc[:c] -= lu[jds.op_a[st:st + c]] * w[jds.op_b[st:st + c]]
+            if back:
+                acc *= lu[s.diag_slot[rows_]]
+            w[rows_] = acc
+    x = np.empty(s.n)
+    x[s.bwd.task_aux] = w[s.bwd.task_out]
+    return x
+
+
+def _validate(s: SymbolicLU, rows, cols, vals):
+    A = sp.csc_matrix((vals, (rows, cols)), shape=(s.n, s.n))
+    rng = np.random.default_rng(1)
+    xref = rng.standard_normal(s.n)
+    b = A @ xref
+    with np.errstate(all="ignore"):
+        lu = numeric_factor(s, vals)
+        x = numeric_solve(s, lu, b)
+    if not np.all(np.isfinite(x)):
+        return np.inf
+    return float(np.max(np.abs(x - xref)) / np.max(np.abs(xref)))
