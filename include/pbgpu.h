@@ -1,0 +1,168 @@
+/*
+ * pbgpu.h -- C ABI of the B200-native batched DAE solver behind pybamm.IDAKLUSolver.
+ *
+ * Drop-in boundary.  These entry points replace, for the batched
+ * solve path, what the reference binds through pybind11:
+ *
+ *   pbgpu_model_load / pbgpu_solver_create   <->  idaklu.create_casadi_solver_group(...)
+ *        packages/pybammsolvers/src/pybammsolvers/idaklu.cpp:30-124,149-175
+ *        (CasADi Function arguments cannot cross a C ABI: a *compiled model image* --
+ *         residual, J - cj*M, events, initial conditions, output variables and the static
+ *         sparse-LU tables lowered to sm_100a by pybamm_b200.codegen -- takes their place)
+ *   pbgpu_solve                              <->  IDAKLUSolverGroup.solve(t_eval, t_interp, y0, yp0, inputs)
+ *        packages/pybammsolvers/src/pybammsolvers/idaklu.cpp:138-147,
+ *        idaklu_source/IDAKLUSolverGroup.cpp:6-170
+ *   pbgpu_result                             <->  struct solution {flag, t, y, yp, yS, ypS, y_term}
+ *        idaklu_source/Solution.hpp:9-39, SolutionData.hpp:75-86
+ *   pbgpu_options                            <->  SolverOptions (idaklu_source/Options.cpp:9-206,
+ *        defaults packages/pybamm/src/pybamm/solvers/idaklu_solver.py:286-325)
+ *   per-system flag values                   <->  IDA return codes (idaklu_source/sundials_error_handler.hpp:11-61):
+ *        0 success, 1 tstop (final t_eval reached), 2 root (termination event), <0 failure
+ *
+ * All arrays are C-contiguous float64 / int32 / int64 exactly as the pybind11 side requires
+ * (np_array is c_style|forcecast, idaklu_source/common.hpp:35).  Output buffers are caller-owned
+ * (no ownership crosses the ABI).  Every function returns 0 on success, non-zero on error with a
+ * message available from pbgpu_last_error() (argument/shape errors mirror the std::domain_error /
+ * invalid_argument texts of IDAKLUSolverGroup.cpp:46-97).  Integration failures are NOT errors:
+ * they are reported per system in flag[] with the partial solution, as the reference does
+ * (IDAKLUSolverOpenMP.inl:401-406,443).
+ *
+ * There is no CPU fallback: pbgpu_model_load fails when no CUDA device is usable.
+ */
+#ifndef PBGPU_H
+#define PBGPU_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PBGPU_ABI_VERSION 1
+
+typedef struct pbgpu_model_s* pbgpu_model_t;
+typedef struct pbgpu_solver_s* pbgpu_solver_t;
+
+typedef struct {
+  int abi_version;
+  int n_states;       /* number_of_states */
+  int n_diff;         /* len_rhs: states [0, n_diff) are differential, the rest algebraic */
+  int n_inputs;       /* number_of_parameters (flattened inputs) */
+  int n_events;       /* number_of_events (TERMINATION events) */
+  int nnz_jac;        /* structural nnz of J - cj*M */
+  int nnz_lu;         /* nnz of the static L+U pattern */
+  int n_vars;         /* total length of the compiled output variables */
+  int team_size;      /* threads cooperating on one system */
+  int smem_bytes;     /* dynamic shared memory per team */
+  int n_tmp;          /* scratch temporaries of the generated functions */
+  int lu_levels[3];   /* dependency levels: factor, forward, backward */
+  long long flops[6]; /* static work model: res, jac, factor, solve, events, vars (DFMA-equivalents / flops) */
+  char name[64];
+} pbgpu_model_desc;
+
+/* Solver options: same names and defaults as IDAKLUSolver's options dict (idaklu_solver.py:286-325). */
+typedef struct {
+  double rtol;
+  int max_order_bdf;                            /* 5 */
+  long long max_num_steps;                      /* 100000 */
+  int max_error_test_failures;                  /* 10 */
+  int max_nonlinear_iterations;                 /* 40 */
+  int max_convergence_failures;                 /* 100 */
+  double nonlinear_convergence_coefficient;     /* 0.33 */
+  double nonlinear_convergence_coefficient_ic;  /* 0.0033 */
+  double newton_step_tol;                       /* 1e-4 */
+  int max_num_iterations_ic;                    /* 100 */
+  int max_linesearch_backtracks_ic;             /* 5 */
+  int linear_solution_scaling;                  /* 1 */
+  int calc_ic;                                  /* 1 */
+  double dt_init;                               /* 0 -> IDA heuristic */
+  double dt_max;                                /* 0 -> unbounded */
+} pbgpu_options;
+
+/* Caller-owned output block of one batch (host pointers for pbgpu_solve, device for pbgpu_solve_device). */
+typedef struct {
+  int n_max;            /* capacity (time points) per system */
+  int n_ret;            /* row length: n_states (output_mode 0) or n_vars (output_mode 1) */
+  double* t;            /* [n_sys][n_max]  */
+  double* y;            /* [n_sys][n_max][n_ret], time-major rows like solution.y */
+  int* n_t;             /* [n_sys] number of stored time points */
+  int* flag;            /* [n_sys] IDA-style return code */
+  double* y_term;       /* [n_sys][n_states] final state (y_event), may be NULL */
+  long long* stats;     /* [n_sys][8]: nsteps nrevals nlinsetups netfails nniters nncfails njevals nge; may be NULL */
+  float kernel_ms;      /* out: device time of the integration kernel (CUDA events) */
+  float total_ms;       /* out: device time including copies (pbgpu_solve only) */
+} pbgpu_result;
+
+#define PBGPU_OUTPUT_STATES 0
+#define PBGPU_OUTPUT_VARS 1
+
+void pbgpu_default_options(pbgpu_options* opt);
+
+/* Load a compiled model image (pbgpu_model_<name>.so built by pybamm_b200.build.build_model). */
+int pbgpu_model_load(const char* path, pbgpu_model_t* model);
+int pbgpu_model_describe(pbgpu_model_t model, pbgpu_model_desc* desc);
+int pbgpu_model_unload(pbgpu_model_t model);
+
+/* atol: [n_states].  device: CUDA ordinal.  One solver <-> one model, as in the reference
+ * (base_solver.py:970-977). */
+int pbgpu_solver_create(pbgpu_model_t model, const double* atol, const pbgpu_options* opt, int device,
+                        pbgpu_solver_t* solver);
+int pbgpu_solver_destroy(pbgpu_solver_t solver);
+
+/* Number of time points a result block must hold per system for these grids. */
+int pbgpu_result_capacity(int n_teval, int n_tinterp);
+
+/*
+ * Integrate n_sys independent systems.  Host buffers in, host buffers out (H2D, kernel, D2H inside).
+ *   t_eval   [n_teval]   sorted, unique, >= 2 entries (breakpoints; IDA stop times)
+ *   t_interp [n_tinterp] sorted, unique, t_eval values removed (may be empty: n_tinterp = 0 -> adaptive steps stored)
+ *   y0       [n_sys][n_states] or NULL (-> the model's initial conditions y0(p) evaluated on device)
+ *   inputs   [n_sys][n_inputs]
+ */
+int pbgpu_solve(pbgpu_solver_t solver, int n_sys, const double* t_eval, int n_teval, const double* t_interp,
+                int n_tinterp, const double* y0, const double* inputs, int output_mode, pbgpu_result* out);
+
+/* Same, but every pointer (inputs and the result block's arrays) is device memory on the solver's
+ * device; nothing is copied.  stream: a cudaStream_t (NULL = default stream).  Asynchronous unless
+ * sync != 0; kernel_ms is only filled when sync != 0. */
+int pbgpu_solve_device(pbgpu_solver_t solver, int n_sys, const double* t_eval, int n_teval, const double* t_interp,
+                       int n_tinterp, const double* y0, const double* inputs, int output_mode, pbgpu_result* out,
+                       void* stream, int sync);
+
+/* Evaluate generated model functions / the sparse LU on the device for n_sys (y, p) pairs (parity tests
+ * of the code generator).  which: 0 res, 1 jac (bundle CSC order), 2 events, 3 ic, 4 vars,
+ * 5 solve (J - cj*M) x = rhs with rhs = y2.  Host pointers. */
+int pbgpu_model_eval(pbgpu_solver_t solver, int which, int n_sys, const double* y, const double* p, double t,
+                     double cj, const double* y2, double* out, int out_len);
+
+const char* pbgpu_last_error(void);
+
+/* ---- interface between libpbgpu and a compiled model image (not for end users) ---- */
+typedef struct {
+  int n_sys, n_eval, n_interp, n_max, save_vars, n_ret;
+  const double* t_eval;
+  const double* t_interp;
+  const double* inputs;
+  const double* y0;
+  const double* atol;
+  double* t_out;
+  double* y_out;
+  int* n_out;
+  int* flag;
+  double* y_term;
+  long long* stats;
+  unsigned int* queue;
+  pbgpu_options opt;
+} pbgpu_launch;
+
+typedef struct {
+  int which, n_sys, out_len;
+  const double* y;
+  const double* p;
+  const double* y2;
+  double t, cj;
+  double* out;
+} pbgpu_eval_launch;
+
+#ifdef __cplusplus
+}
+#endif
+#endif

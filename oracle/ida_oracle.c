@@ -701,7 +701,7 @@ static int newton_ic(ida_t* S, double t, double* y, double* init_norm, double* f
         memcpy(y + nd, S->xa, sizeof(double) * na);
         return 1;
       }
-      if (iter > 0 && res_norm >= prev_res_norm) { memcpy(y + nd, S->xa, sizeof(double) * na); return 1; }
+      if (iter > 0 && res_norm >= prev_res_norm) { memcpy(S->xa, S->xsave, sizeof(double) * na); memcpy(y + nd, S->xa, sizeof(double) * na); return 1; }
     }
     prev_res_norm = res_norm;
     memcpy(S->xsave, S->xa, sizeof(double) * na);

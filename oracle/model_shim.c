@@ -3,6 +3,7 @@
 #include <math.h>
 #include "pbo_model.h"
 #define PB_TABLE
+#define PB_ALIGN16
 #define PB_FN static
 #define PB_RESTRICT restrict
 #define PB_TID 0

@@ -25,7 +25,7 @@ MODELS = os.path.join(PKG, "models")
 ORACLE = os.path.join(ROOT, "oracle")
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--cudart", "shared",
               "-Xcompiler", "-fPIC", "--shared", "-Xptxas", "-v"]
 
 
@@ -92,7 +92,7 @@ def build_model(bundle: ModelBundle, force=False, team=None, verbose=False):
     srcs = kernel_srcs + [header, os.path.join(inc, "pbgpu.h")]
     if team is None:
         team = default_team(bundle)
-    dig = _src_digest(srcs) + f"-t{team}"
+    dig = _src_digest(srcs) + f"-t{team}-" + hashlib.sha256(" ".join(NVCC_FLAGS).encode()).hexdigest()[:8]
     stamp = out + ".stamp"
     if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:
         return out

@@ -195,21 +195,17 @@ def emit_program(prog: Program, fname: str, prefix: str):
 def _emit_jds(em_lines, name, j: slu.JDS, slot_max):
     it = _itype(slot_max)
 
-    def arr(ctype, suffix, vals):
+    def arr(ctype, suffix, vals, align=""):
         vals = list(np.asarray(vals).reshape(-1))
         body = ", ".join(str(int(v)) for v in vals) if vals else "0"
-        em_lines.append(f"static PB_TABLE const {ctype} {name}_{suffix}[{max(len(vals), 1)}] = {{{body}}};")
+        em_lines.append(f"static PB_TABLE {align}const {ctype} {name}_{suffix}[{max(len(vals), 1)}] = {{{body}}};")
 
     em_lines.append(f"#define {name.upper()}_NLEV {j.n_levels}")
-    arr("int", "lev_task", j.lev_task)
-    arr("int", "lev_row", j.lev_row)
-    arr("int", "row_start", j.row_start)
-    arr(it, "row_cnt", j.row_cnt)
+    arr("int", "lev_meta", j.lev_meta, "PB_ALIGN16 ")
     arr(it, "op_a", j.op_a)
     arr(it, "op_b", j.op_b)
     arr(it, "task_out", j.task_out)
     arr(it, "task_aux", j.task_aux)
-    arr("unsigned char", "sync", j.sync)
 
 
 def model_functions(bundle, sym: slu.SymbolicLU | None, dialect: str):

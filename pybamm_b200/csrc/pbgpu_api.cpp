@@ -1,0 +1,367 @@
+// pbgpu_api.cpp -- libpbgpu.so: the C-ABI host library (include/pbgpu.h).
+//
+// Generic host side of the batched solver: loads compiled model images, owns device buffers and the
+// stream, validates arguments the way IDAKLUSolverGroup::solve does
+// (packages/pybammsolvers/src/pybammsolvers/idaklu_source/IDAKLUSolverGroup.cpp:46-97), moves the batch
+// to the device, launches the image's persistent integration kernel and brings the results back.
+// It contains no numerical code and no CPU fallback: every path ends in a kernel of the model image.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "pbgpu.h"
+
+namespace {
+thread_local std::string g_err;
+
+int fail(const std::string& msg) {
+  g_err = msg;
+  return 1;
+}
+int cuda_fail(const char* what, cudaError_t e) { return fail(std::string(what) + ": " + cudaGetErrorString(e)); }
+
+#define CK(call)                                    \
+  do {                                              \
+    cudaError_t e__ = (call);                       \
+    if (e__ != cudaSuccess) return cuda_fail(#call, e__); \
+  } while (0)
+
+typedef int (*describe_fn)(pbgpu_model_desc*);
+typedef int (*launch_fn)(const pbgpu_launch*, void*, int*, char*, size_t);
+typedef int (*eval_fn)(const pbgpu_eval_launch*, void*, char*, size_t);
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return cuda_fail("cudaMalloc", e);
+    cap = bytes;
+    return 0;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+}  // namespace
+
+struct pbgpu_model_s {
+  void* handle = nullptr;
+  describe_fn describe = nullptr;
+  launch_fn launch = nullptr;
+  eval_fn eval = nullptr;
+  pbgpu_model_desc desc;
+  std::string path;
+};
+
+struct pbgpu_solver_s {
+  pbgpu_model_s* model = nullptr;
+  int device = 0;
+  pbgpu_options opt;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  DevBuf atol, t_eval, t_interp, inputs, y0, t_out, y_out, n_out, flag, y_term, stats, queue, scratch_a, scratch_b;
+  int last_grid = 0;
+};
+
+extern "C" {
+
+const char* pbgpu_last_error(void) { return g_err.c_str(); }
+
+void pbgpu_default_options(pbgpu_options* o) {
+  o->rtol = 1e-4;
+  o->max_order_bdf = 5;
+  o->max_num_steps = 100000;
+  o->max_error_test_failures = 10;
+  o->max_nonlinear_iterations = 40;
+  o->max_convergence_failures = 100;
+  o->nonlinear_convergence_coefficient = 0.33;
+  o->nonlinear_convergence_coefficient_ic = 0.0033;
+  o->newton_step_tol = 1e-4;
+  o->max_num_iterations_ic = 100;
+  o->max_linesearch_backtracks_ic = 5;
+  o->linear_solution_scaling = 1;
+  o->calc_ic = 1;
+  o->dt_init = 0.0;
+  o->dt_max = 0.0;
+}
+
+int pbgpu_model_load(const char* path, pbgpu_model_t* model) {
+  if (!path || !model) return fail("pbgpu_model_load: null argument");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev < 1)
+    return fail(std::string("pbgpu_model_load: no usable CUDA device (") + (e != cudaSuccess ? cudaGetErrorString(e) : "0 devices") +
+                "); this solver has no CPU fallback");
+  void* h = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+  if (!h) return fail(std::string("pbgpu_model_load: ") + dlerror());
+  pbgpu_model_s* m = new pbgpu_model_s();
+  m->handle = h;
+  m->path = path;
+  m->describe = (describe_fn)dlsym(h, "pbgpu_image_describe");
+  m->launch = (launch_fn)dlsym(h, "pbgpu_image_launch");
+  m->eval = (eval_fn)dlsym(h, "pbgpu_image_eval");
+  if (!m->describe || !m->launch || !m->eval) {
+    dlclose(h);
+    delete m;
+    return fail(std::string("pbgpu_model_load: '") + path + "' is not a pbgpu model image");
+  }
+  m->describe(&m->desc);
+  if (m->desc.abi_version != PBGPU_ABI_VERSION) {
+    dlclose(h);
+    delete m;
+    return fail("pbgpu_model_load: model image was built against a different ABI version");
+  }
+  *model = m;
+  return 0;
+}
+
+int pbgpu_model_describe(pbgpu_model_t model, pbgpu_model_desc* desc) {
+  if (!model || !desc) return fail("pbgpu_model_describe: null argument");
+  *desc = model->desc;
+  return 0;
+}
+
+int pbgpu_model_unload(pbgpu_model_t model) {
+  if (!model) return 0;
+  // the image stays mapped (its kernels may still be registered with the CUDA runtime)
+  delete model;
+  return 0;
+}
+
+int pbgpu_solver_create(pbgpu_model_t model, const double* atol, const pbgpu_options* opt, int device,
+                        pbgpu_solver_t* solver) {
+  if (!model || !atol || !solver) return fail("pbgpu_solver_create: null argument");
+  int ndev = 0;
+  CK(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) return fail("pbgpu_solver_create: invalid device ordinal " + std::to_string(device));
+  CK(cudaSetDevice(device));
+  pbgpu_solver_s* s = new pbgpu_solver_s();
+  s->model = model;
+  s->device = device;
+  if (opt) s->opt = *opt;
+  else pbgpu_default_options(&s->opt);
+  for (int i = 0; i < model->desc.n_states; i++)
+    if (!(atol[i] >= 0.0)) {
+      delete s;
+      return fail("pbgpu_solver_create: absolute tolerances must be non-negative");
+    }
+  if (!(s->opt.rtol >= 0.0)) {
+    delete s;
+    return fail("pbgpu_solver_create: rtol must be non-negative");
+  }
+  cudaError_t e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) {
+    delete s;
+    return cuda_fail("cudaStreamCreate", e);
+  }
+  for (int i = 0; i < 4; i++) cudaEventCreate(&s->ev[i]);
+  if (s->atol.ensure(sizeof(double) * model->desc.n_states)) {
+    delete s;
+    return 1;
+  }
+  e = cudaMemcpy(s->atol.p, atol, sizeof(double) * model->desc.n_states, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    delete s;
+    return cuda_fail("cudaMemcpy(atol)", e);
+  }
+  if (s->queue.ensure(sizeof(unsigned int))) {
+    delete s;
+    return 1;
+  }
+  *solver = s;
+  return 0;
+}
+
+int pbgpu_solver_destroy(pbgpu_solver_t s) {
+  if (!s) return 0;
+  cudaSetDevice(s->device);
+  if (s->stream) cudaStreamSynchronize(s->stream);
+  DevBuf* bufs[] = {&s->atol, &s->t_eval, &s->t_interp, &s->inputs, &s->y0, &s->t_out, &s->y_out, &s->n_out,
+                    &s->flag, &s->y_term, &s->stats, &s->queue, &s->scratch_a, &s->scratch_b};
+  for (DevBuf* b : bufs) b->release();
+  for (int i = 0; i < 4; i++)
+    if (s->ev[i]) cudaEventDestroy(s->ev[i]);
+  if (s->stream) cudaStreamDestroy(s->stream);
+  delete s;
+  return 0;
+}
+
+int pbgpu_result_capacity(int n_teval, int n_tinterp) { return n_teval + n_tinterp + 2; }
+
+static int check_grids(const double* t_eval, int n_teval, const double* t_interp, int n_tinterp) {
+  if (!t_eval || n_teval < 2) return fail("t_eval must have at least 2 entries");
+  for (int i = 1; i < n_teval; i++)
+    if (!(t_eval[i] > t_eval[i - 1])) return fail("t_eval must be sorted and unique");
+  for (int i = 1; i < n_tinterp; i++)
+    if (!(t_interp[i] > t_interp[i - 1])) return fail("t_interp must be sorted and unique");
+  if (n_tinterp > 0) {
+    if (t_interp[0] < t_eval[0])
+      return fail("t_interp values must be greater than the smallest t_eval value: " + std::to_string(t_eval[0]));
+    if (t_interp[n_tinterp - 1] > t_eval[n_teval - 1])
+      return fail("t_interp values must be less than the greatest t_eval value: " + std::to_string(t_eval[n_teval - 1]));
+  }
+  return 0;
+}
+
+static int launch_common(pbgpu_solver_s* s, int n_sys, const double* d_t_eval, int n_teval, const double* d_t_interp,
+                         int n_tinterp, const double* d_y0, const double* d_inputs, int output_mode, int n_max,
+                         double* d_t, double* d_y, int* d_n, int* d_flag, double* d_yterm, long long* d_stats,
+                         cudaStream_t stream) {
+  const pbgpu_model_desc& D = s->model->desc;
+  pbgpu_launch L;
+  memset(&L, 0, sizeof(L));
+  L.n_sys = n_sys;
+  L.n_eval = n_teval;
+  L.n_interp = n_tinterp;
+  L.n_max = n_max;
+  L.save_vars = (output_mode == PBGPU_OUTPUT_VARS);
+  L.n_ret = L.save_vars ? D.n_vars : D.n_states;
+  L.t_eval = d_t_eval;
+  L.t_interp = d_t_interp;
+  L.inputs = d_inputs;
+  L.y0 = d_y0;
+  L.atol = (const double*)s->atol.p;
+  L.t_out = d_t;
+  L.y_out = d_y;
+  L.n_out = d_n;
+  L.flag = d_flag;
+  L.y_term = d_yterm;
+  L.stats = d_stats;
+  L.queue = (unsigned int*)s->queue.p;
+  L.opt = s->opt;
+  CK(cudaMemsetAsync(s->queue.p, 0, sizeof(unsigned int), stream));
+  char err[512];
+  err[0] = 0;
+  if (s->model->launch(&L, (void*)stream, &s->last_grid, err, sizeof(err))) return fail(err);
+  return 0;
+}
+
+int pbgpu_solve_device(pbgpu_solver_t s, int n_sys, const double* t_eval, int n_teval, const double* t_interp,
+                       int n_tinterp, const double* y0, const double* inputs, int output_mode, pbgpu_result* out,
+                       void* stream, int sync) {
+  if (!s || !out) return fail("pbgpu_solve_device: null argument");
+  if (n_sys < 1) return fail("pbgpu_solve_device: n_sys must be positive");
+  const pbgpu_model_desc& D = s->model->desc;
+  if (output_mode == PBGPU_OUTPUT_VARS && D.n_vars < 1) return fail("the model image has no compiled output variables");
+  if (n_teval < 2) return fail("t_eval must have at least 2 entries");
+  if (D.n_inputs > 0 && !inputs) return fail("inputs has wrong number of dimensions. Expected 2 but got 0");
+  CK(cudaSetDevice(s->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  if (sync) CK(cudaEventRecord(s->ev[0], st));
+  if (launch_common(s, n_sys, t_eval, n_teval, t_interp, n_tinterp, y0, inputs, output_mode, out->n_max, out->t, out->y,
+                    out->n_t, out->flag, out->y_term, out->stats, st))
+    return 1;
+  if (sync) {
+    CK(cudaEventRecord(s->ev[1], st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaEventElapsedTime(&out->kernel_ms, s->ev[0], s->ev[1]));
+    out->total_ms = out->kernel_ms;
+  }
+  return 0;
+}
+
+int pbgpu_solve(pbgpu_solver_t s, int n_sys, const double* t_eval, int n_teval, const double* t_interp, int n_tinterp,
+                const double* y0, const double* inputs, int output_mode, pbgpu_result* out) {
+  if (!s || !out) return fail("pbgpu_solve: null argument");
+  if (n_sys < 1) return fail("pbgpu_solve: n_sys must be positive");
+  const pbgpu_model_desc& D = s->model->desc;
+  if (check_grids(t_eval, n_teval, t_interp, n_tinterp)) return 1;
+  if (output_mode != PBGPU_OUTPUT_STATES && output_mode != PBGPU_OUTPUT_VARS) return fail("invalid output_mode");
+  if (output_mode == PBGPU_OUTPUT_VARS && D.n_vars < 1) return fail("the model image has no compiled output variables");
+  const int n_ret = output_mode == PBGPU_OUTPUT_VARS ? D.n_vars : D.n_states;
+  if (out->n_ret != n_ret)
+    return fail("result block has wrong row length. Expected " + std::to_string(n_ret) + " but got " + std::to_string(out->n_ret));
+  if (out->n_max < 1 || !out->t || !out->y || !out->n_t || !out->flag) return fail("result block is incomplete");
+  if (n_tinterp > 0 && out->n_max < pbgpu_result_capacity(n_teval, n_tinterp))
+    return fail("result block is too small for the requested t_eval/t_interp grids");
+  if (D.n_inputs > 0 && !inputs) return fail("inputs has wrong number of dimensions. Expected 2 but got 0");
+  CK(cudaSetDevice(s->device));
+  const size_t N = D.n_states, nm = out->n_max;
+  if (s->t_eval.ensure(sizeof(double) * n_teval)) return 1;
+  if (s->t_interp.ensure(sizeof(double) * (n_tinterp > 0 ? n_tinterp : 1))) return 1;
+  if (s->inputs.ensure(sizeof(double) * (size_t)n_sys * (D.n_inputs > 0 ? D.n_inputs : 1))) return 1;
+  if (y0 && s->y0.ensure(sizeof(double) * n_sys * N)) return 1;
+  if (s->t_out.ensure(sizeof(double) * n_sys * nm)) return 1;
+  if (s->y_out.ensure(sizeof(double) * n_sys * nm * n_ret)) return 1;
+  if (s->n_out.ensure(sizeof(int) * n_sys)) return 1;
+  if (s->flag.ensure(sizeof(int) * n_sys)) return 1;
+  if (out->y_term && s->y_term.ensure(sizeof(double) * n_sys * N)) return 1;
+  if (out->stats && s->stats.ensure(sizeof(long long) * n_sys * 8)) return 1;
+  cudaStream_t st = s->stream;
+  CK(cudaEventRecord(s->ev[0], st));
+  CK(cudaMemcpyAsync(s->t_eval.p, t_eval, sizeof(double) * n_teval, cudaMemcpyHostToDevice, st));
+  if (n_tinterp > 0) CK(cudaMemcpyAsync(s->t_interp.p, t_interp, sizeof(double) * n_tinterp, cudaMemcpyHostToDevice, st));
+  if (D.n_inputs > 0)
+    CK(cudaMemcpyAsync(s->inputs.p, inputs, sizeof(double) * (size_t)n_sys * D.n_inputs, cudaMemcpyHostToDevice, st));
+  if (y0) CK(cudaMemcpyAsync(s->y0.p, y0, sizeof(double) * n_sys * N, cudaMemcpyHostToDevice, st));
+  CK(cudaEventRecord(s->ev[1], st));
+  if (launch_common(s, n_sys, (const double*)s->t_eval.p, n_teval, n_tinterp > 0 ? (const double*)s->t_interp.p : nullptr,
+                    n_tinterp, y0 ? (const double*)s->y0.p : nullptr, (const double*)s->inputs.p, output_mode, out->n_max,
+                    (double*)s->t_out.p, (double*)s->y_out.p, (int*)s->n_out.p, (int*)s->flag.p,
+                    out->y_term ? (double*)s->y_term.p : nullptr, out->stats ? (long long*)s->stats.p : nullptr, st))
+    return 1;
+  CK(cudaEventRecord(s->ev[2], st));
+  CK(cudaMemcpyAsync(out->t, s->t_out.p, sizeof(double) * n_sys * nm, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out->y, s->y_out.p, sizeof(double) * n_sys * nm * n_ret, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out->n_t, s->n_out.p, sizeof(int) * n_sys, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out->flag, s->flag.p, sizeof(int) * n_sys, cudaMemcpyDeviceToHost, st));
+  if (out->y_term) CK(cudaMemcpyAsync(out->y_term, s->y_term.p, sizeof(double) * n_sys * N, cudaMemcpyDeviceToHost, st));
+  if (out->stats) CK(cudaMemcpyAsync(out->stats, s->stats.p, sizeof(long long) * n_sys * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaEventRecord(s->ev[3], st));
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) return cuda_fail("integration kernel", e);
+  CK(cudaEventElapsedTime(&out->kernel_ms, s->ev[1], s->ev[2]));
+  CK(cudaEventElapsedTime(&out->total_ms, s->ev[0], s->ev[3]));
+  return 0;
+}
+
+int pbgpu_model_eval(pbgpu_solver_t s, int which, int n_sys, const double* y, const double* p, double t, double cj,
+                     const double* y2, double* out, int out_len) {
+  if (!s || !out || n_sys < 1) return fail("pbgpu_model_eval: bad argument");
+  const pbgpu_model_desc& D = s->model->desc;
+  CK(cudaSetDevice(s->device));
+  const size_t N = D.n_states;
+  const int np = D.n_inputs > 0 ? D.n_inputs : 1;
+  if (s->y0.ensure(sizeof(double) * n_sys * N)) return 1;
+  if (s->inputs.ensure(sizeof(double) * (size_t)n_sys * np)) return 1;
+  if (s->scratch_a.ensure(sizeof(double) * n_sys * N)) return 1;
+  if (s->scratch_b.ensure(sizeof(double) * (size_t)n_sys * out_len)) return 1;
+  cudaStream_t st = s->stream;
+  if (y) CK(cudaMemcpyAsync(s->y0.p, y, sizeof(double) * n_sys * N, cudaMemcpyHostToDevice, st));
+  else CK(cudaMemsetAsync(s->y0.p, 0, sizeof(double) * n_sys * N, st));
+  if (D.n_inputs > 0) CK(cudaMemcpyAsync(s->inputs.p, p, sizeof(double) * (size_t)n_sys * D.n_inputs, cudaMemcpyHostToDevice, st));
+  if (y2) CK(cudaMemcpyAsync(s->scratch_a.p, y2, sizeof(double) * n_sys * N, cudaMemcpyHostToDevice, st));
+  else CK(cudaMemsetAsync(s->scratch_a.p, 0, sizeof(double) * n_sys * N, st));
+  CK(cudaMemsetAsync(s->scratch_b.p, 0, sizeof(double) * (size_t)n_sys * out_len, st));
+  pbgpu_eval_launch E;
+  memset(&E, 0, sizeof(E));
+  E.which = which;
+  E.n_sys = n_sys;
+  E.out_len = out_len;
+  E.y = (const double*)s->y0.p;
+  E.p = (const double*)s->inputs.p;
+  E.y2 = (const double*)s->scratch_a.p;
+  E.t = t;
+  E.cj = cj;
+  E.out = (double*)s->scratch_b.p;
+  char err[512];
+  err[0] = 0;
+  if (s->model->eval(&E, (void*)st, err, sizeof(err))) return fail(err);
+  CK(cudaMemcpyAsync(out, s->scratch_b.p, sizeof(double) * (size_t)n_sys * out_len, cudaMemcpyDeviceToHost, st));
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) return cuda_fail("evaluation kernel", e);
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,1249 @@
+// pbgpu_ida.cuh -- batched variable-order BDF (IDA-style) DAE integrator, one team per system.
+//
+// Device-side replacement of the per-system solver object of the reference:
+//   IDAKLUSolverOpenMP::solve + helpers  (idaklu_source/IDAKLUSolverOpenMP.inl:327-699, 787-928)
+//   the SUNDIALS IDAS calls it makes     (IDASolve/IDAReInit/IDAGetDky/IDASetStopTime; call sites
+//                                         IDAKLUSolverOpenMP.inl:383,431,573,632,780)
+//   SUNLinSol_KLU                        (IDAKLUSolverOpenMP_solvers.hpp:29-33) -> static-pattern sparse LU
+//   NonlinearSolver (IC Newton)          (idaklu_source/NonlinearSolver.inl:100-177, AlgebraicICBuilder.inl:52-119)
+//
+// Design (B200): every per-system vector (BDF history phi[0..5], weights, Newton work vectors,
+// the L+U values, code-generator temporaries) lives in the team's shared memory for the whole
+// integration; HBM is touched only for the inputs and the requested outputs.  Vector work is
+// strided over the team's threads, scalar control state is replicated in registers (every thread
+// takes the same decisions from bitwise-identical reductions), the BDF coefficient arrays are
+// written by thread 0.  Teams pull systems from an atomic queue, so a team that finishes (event,
+// final time, failure) immediately starts the next system: no lane idles on a terminated system.
+//
+// Included after pbgpu_team.cuh and the generated model header (PBM_* macros, pbm_* functions).
+#pragma once
+
+#define PB_MXORDP1 6
+#define PB_UROUND 2.220446049250313e-16
+
+#define PB_IDA_SUCCESS 0
+#define PB_IDA_TSTOP_RETURN 1
+#define PB_IDA_ROOT_RETURN 2
+#define PB_IDA_TOO_MUCH_WORK (-1)
+#define PB_IDA_TOO_MUCH_ACC (-2)
+#define PB_IDA_ERR_FAIL (-3)
+#define PB_IDA_CONV_FAIL (-4)
+#define PB_IDA_LSETUP_FAIL (-6)
+#define PB_IDA_ILL_INPUT (-22)
+
+#define PB_AUX_U 0xFFFF
+#define PB_AUX_DIAG 0xFFFE
+
+#define PB_NEV_PAD ((PBM_NEV > 0) ? PBM_NEV : 1)
+
+// ---- shared-memory layout (in doubles) --------------------------------------------------------
+#define PB_OFF_PHI 0
+#define PB_OFF_EWT (PB_OFF_PHI + PB_MXORDP1 * PBM_N)
+#define PB_OFF_EE (PB_OFF_EWT + PBM_N)
+#define PB_OFF_DELTA (PB_OFF_EE + PBM_N)
+#define PB_OFF_YYPRED (PB_OFF_DELTA + PBM_N)
+#define PB_OFF_YPPRED (PB_OFF_YYPRED + PBM_N)
+#define PB_OFF_YY (PB_OFF_YPPRED + PBM_N)
+#define PB_OFF_W (PB_OFF_YY + PBM_N)
+#define PB_OFF_TMP (PB_OFF_W + PBM_N + 1)
+#define PB_OFF_LU (PB_OFF_TMP + PBM_NTMP)
+#define PB_OFF_P (PB_OFF_LU + PBM_NNZ_LU + 1)
+#define PB_OFF_G (PB_OFF_P + PBM_NP)
+#define PB_OFF_COEF (PB_OFF_G + 3 * PB_NEV_PAD)
+#define PB_OFF_RED (PB_OFF_COEF + 32)
+#define PB_OFF_STATS (PB_OFF_RED + 64)
+#define PB_SMEM_DOUBLES (PB_OFF_STATS + 8)
+#define PB_SMEM_BYTES (PB_SMEM_DOUBLES * 8)
+
+enum { PB_ST_NST, PB_ST_NRE, PB_ST_NSETUPS, PB_ST_NETF, PB_ST_NNI, PB_ST_NCFN, PB_ST_NJE, PB_ST_NGE };
+
+struct pb_sys {
+  double* sm;          // base of the team's shared memory
+  pb_team_ctx team;
+  const double* atol;  // global
+  // options (copied from pbgpu_options)
+  double rtol, epcon, epsNewtIC, step_tol_ic, dt_init, hmax_inv;
+  int maxord, maxnef, maxcor, maxncf, max_iter_ic, max_backtracks_ic, scalesol;
+  long long max_num_steps;
+  // IDA scalar memory (replicated in every thread)
+  double tn, hh, hused, cj, cjlast, cjold, cjratio, ss, rr, epsNewt, toldel;
+  double tstop, tretlast, tlo, thi, trout, ttol;
+  int kk, kused, knew, phase, ns, tstopset;
+  long long nst;
+  unsigned gactive;
+};
+
+#define S_PHI(S, j) ((S).sm + PB_OFF_PHI + (j) * PBM_N)
+#define S_EWT(S) ((S).sm + PB_OFF_EWT)
+#define S_EE(S) ((S).sm + PB_OFF_EE)
+#define S_DELTA(S) ((S).sm + PB_OFF_DELTA)
+#define S_YYPRED(S) ((S).sm + PB_OFF_YYPRED)
+#define S_YPPRED(S) ((S).sm + PB_OFF_YPPRED)
+#define S_YY(S) ((S).sm + PB_OFF_YY)
+#define S_W(S) ((S).sm + PB_OFF_W)
+#define S_TMP(S) ((S).sm + PB_OFF_TMP)
+#define S_LU(S) ((S).sm + PB_OFF_LU)
+#define S_P(S) ((S).sm + PB_OFF_P)
+#define S_GLO(S) ((S).sm + PB_OFF_G)
+#define S_GHI(S) ((S).sm + PB_OFF_G + PB_NEV_PAD)
+#define S_GROUT(S) ((S).sm + PB_OFF_G + 2 * PB_NEV_PAD)
+#define S_PSI(S) ((S).sm + PB_OFF_COEF)
+#define S_ALPHA(S) ((S).sm + PB_OFF_COEF + 6)
+#define S_BETA(S) ((S).sm + PB_OFF_COEF + 12)
+#define S_SIGMA(S) ((S).sm + PB_OFF_COEF + 18)
+#define S_GAMMA(S) ((S).sm + PB_OFF_COEF + 24)
+#define S_STATS(S) ((S).sm + PB_OFF_STATS)
+
+#define PB_STAT(S, k)                        \
+  do {                                       \
+    if (PB_TID == 0) S_STATS(S)[k] += 1.0;   \
+  } while (0)
+
+// ---- static-pattern sparse LU (tables from pybamm_b200/symbolic_lu.py) ---------------------------
+// Level-scheduled, operands in ELL layout: operand p of task q of a level sits at op_base + p*nt + q,
+// short tasks are padded with the constant-zero slots lu[PBM_NNZ_LU] / w[PBM_N].  The 4-int level
+// record of the next level is fetched while the current level computes.
+struct pb_level {
+  int t0, nt, ob, ml, sync;
+};
+#define PB_LEVEL_LOAD(L, meta, lev)                 \
+  do {                                              \
+    const int* m__ = (meta) + 4 * (lev);            \
+    (L).t0 = PB_LDU(m__[0]);                        \
+    (L).nt = PB_LDU(m__[1]);                        \
+    (L).ob = PB_LDU(m__[2]);                        \
+    const int w__ = PB_LDU(m__[3]);                 \
+    (L).ml = w__ & 0xFFFF;                          \
+    (L).sync = w__ >> 16;                           \
+  } while (0)
+
+// Entry-parallel left-looking factorisation of the values already scattered into lu[] by pbm_jac.
+// Returns non-zero (team-uniform) when a pivot is zero / not finite.
+static PB_DEV int pb_lu_factor(pb_sys& S) {
+  double* lu = S_LU(S);
+  double bad = 0.0;
+  pb_level L, Ln;
+  PB_LEVEL_LOAD(L, pbm_fac_lev_meta, 0);
+  for (int lev = 0; lev < PBM_FAC_NLEV; lev++) {
+    Ln = L;
+    if (lev + 1 < PBM_FAC_NLEV) PB_LEVEL_LOAD(Ln, pbm_fac_lev_meta, lev + 1);
+    for (int q = PB_TID; q < L.nt; q += PB_TEAM) {
+      const int out = (int)PB_LD(pbm_fac_task_out[L.t0 + q]);
+      const int aux = (int)PB_LD(pbm_fac_task_aux[L.t0 + q]);
+      double acc = lu[out];
+#pragma unroll 4
+      for (int p = 0; p < L.ml; p++) {
+        const int idx = L.ob + p * L.nt + q;
+        acc -= lu[(int)PB_LD(pbm_fac_op_a[idx])] * lu[(int)PB_LD(pbm_fac_op_b[idx])];
+      }
+      if (aux == PB_AUX_U) {
+        lu[out] = acc;
+      } else if (aux == PB_AUX_DIAG) {
+        const double inv = 1.0 / acc;
+        if (!(fabs(inv) <= 1.7e308) || acc == 0.0) bad = 1.0;
+        lu[out] = inv;
+      } else {
+        lu[out] = acc * lu[aux];
+      }
+    }
+    if (L.sync) PB_SYNC();
+    else PB_SYNCWARP();
+    L = Ln;
+  }
+  return pb_team_max(S.team, bad) != 0.0;
+}
+
+// Solve (J - cj M) x = b in place (b: shared vector), w = S_W scratch. Ends with a team barrier.
+static PB_DEV void pb_lu_solve(pb_sys& S, double* b) {
+  const double* lu = S_LU(S);
+  double* w = S_W(S);
+  pb_level L, Ln;
+  PB_LEVEL_LOAD(L, pbm_fwd_lev_meta, 0);
+  for (int lev = 0; lev < PBM_FWD_NLEV; lev++) {
+    Ln = L;
+    if (lev + 1 < PBM_FWD_NLEV) PB_LEVEL_LOAD(Ln, pbm_fwd_lev_meta, lev + 1);
+    for (int q = PB_TID; q < L.nt; q += PB_TEAM) {
+      const int row = (int)PB_LD(pbm_fwd_task_out[L.t0 + q]);
+      double acc = b[(int)PB_LD(pbm_fwd_task_aux[L.t0 + q])];
+#pragma unroll 4
+      for (int p = 0; p < L.ml; p++) {
+        const int idx = L.ob + p * L.nt + q;
+        acc -= lu[(int)PB_LD(pbm_fwd_op_a[idx])] * w[(int)PB_LD(pbm_fwd_op_b[idx])];
+      }
+      w[row] = acc;
+    }
+    if (L.sync) PB_SYNC();
+    else PB_SYNCWARP();
+    L = Ln;
+  }
+  PB_LEVEL_LOAD(L, pbm_bwd_lev_meta, 0);
+  for (int lev = 0; lev < PBM_BWD_NLEV; lev++) {
+    Ln = L;
+    if (lev + 1 < PBM_BWD_NLEV) PB_LEVEL_LOAD(Ln, pbm_bwd_lev_meta, lev + 1);
+    for (int q = PB_TID; q < L.nt; q += PB_TEAM) {
+      const int row = (int)PB_LD(pbm_bwd_task_out[L.t0 + q]);
+      const int dst = (int)PB_LD(pbm_bwd_task_aux[L.t0 + q]);
+      const double dinv = lu[(int)PB_LD(pbm_diag_slot[row])];
+      double acc = w[row];
+#pragma unroll 4
+      for (int p = 0; p < L.ml; p++) {
+        const int idx = L.ob + p * L.nt + q;
+        acc -= lu[(int)PB_LD(pbm_bwd_op_a[idx])] * w[(int)PB_LD(pbm_bwd_op_b[idx])];
+      }
+      acc *= dinv;
+      w[row] = acc;
+      b[dst] = acc;
+    }
+    if (L.sync) PB_SYNC();
+    else PB_SYNCWARP();
+    L = Ln;
+  }
+}
+
+// Evaluate J - cj*M at (t, y) into the LU value array and factor it.  ic_mode: replace the
+// differential rows by identity rows (the algebraic sub-block system of the IC Newton,
+// AlgebraicICBuilder.inl:52-119, solved through the same static LU).
+static PB_DEV int pb_lsetup(pb_sys& S, double t, const double* y, double cj, int ic_mode) {
+  double* lu = S_LU(S);
+  for (int i = PB_TID; i < PBM_NFILL; i += PB_TEAM) lu[(int)PB_LD(pbm_fill[i])] = 0.0;
+  pbm_jac(y, S_P(S), t, cj, lu, S_TMP(S));
+  PB_SYNC();
+  if (ic_mode) {
+    for (int k = PB_TID; k < PBM_NNZ; k += PB_TEAM) {
+      const int kind = (int)PB_LD(pbm_ent_kind[k]);
+      if (kind) lu[(int)PB_LD(pbm_ent_slot[k])] = (kind == 2) ? 1.0 : 0.0;
+    }
+    PB_SYNC();
+  }
+  PB_STAT(S, PB_ST_NJE);
+  PB_STAT(S, PB_ST_NSETUPS);
+  return pb_lu_factor(S);
+}
+
+static PB_DEV double pb_wrms(pb_sys& S, const double* x) {
+  const double* ewt = S_EWT(S);
+  double acc = 0.0;
+  for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
+    const double v = x[i] * ewt[i];
+    acc += v * v;
+  }
+  return sqrt(pb_team_sum(S.team, acc) / PBM_N);
+}
+
+// ewt_i = 1 / (rtol |y_i| + atol_i); returns non-zero if a weight is not positive. Ends with a barrier.
+static PB_DEV int pb_ewt_set(pb_sys& S, const double* y) {
+  double* ewt = S_EWT(S);
+  double bad = 0.0;
+  for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
+    const double w = S.rtol * fabs(y[i]) + PB_LD(S.atol[i]);
+    if (!(w > 0.0)) bad = 1.0;
+    ewt[i] = 1.0 / w;
+  }
+  PB_SYNC();
+  return pb_team_max(S.team, bad) != 0.0;
+}
+
+// ---- interpolation (IDAGetSolution / IDAGetDky k=0,1) ------------------------------------------
+struct pb_interp {
+  double c[PB_MXORDP1], d[PB_MXORDP1];
+  int kord;
+};
+static PB_DEV void pb_interp_coeffs(const pb_sys& S, double t, pb_interp& I) {
+  const double* psi = S_PSI(S);
+  int kord = S.kused;
+  if (kord == 0) kord = 1;
+  const double delt = t - S.tn;
+  double c = 1.0, d = 0.0, gam = delt / psi[0];
+  I.c[0] = c;
+  I.d[0] = 0.0;
+#pragma unroll
+  for (int j = 1; j < PB_MXORDP1; j++) {
+    if (j <= kord) {
+      d = d * gam + c / psi[j - 1];
+      c = c * gam;
+      gam = (delt + psi[j - 1]) / psi[j < PB_MXORDP1 - 1 ? j : PB_MXORDP1 - 1];
+      I.c[j] = c;
+      I.d[j] = d;   // multiplies phi[j] in y'
+    } else {
+      I.c[j] = 0.0;
+      I.d[j] = 0.0;
+    }
+  }
+  I.kord = kord;
+}
+// y(t) -> dst (shared or global). No barrier.
+static PB_DEV void pb_get_solution(const pb_sys& S, double t, double* dst) {
+  pb_interp I;
+  pb_interp_coeffs(S, t, I);
+  const double* phi = S_PHI(S, 0);
+  for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
+    double s = 0.0;
+#pragma unroll
+    for (int j = PB_MXORDP1 - 1; j >= 0; j--)
+      if (j <= I.kord) s += I.c[j] * phi[j * PBM_N + i];
+    dst[i] = s;
+  }
+}
+// y(t) -> ydst and y'(t) -> ypdst. No barrier.
+static PB_DEV void pb_get_solution2(const pb_sys& S, double t, double* ydst, double* ypdst) {
+  pb_interp I;
+  pb_interp_coeffs(S, t, I);
+  const double* phi = S_PHI(S, 0);
+  for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
+    double s = 0.0, sp = 0.0;
+#pragma unroll
+    for (int j = PB_MXORDP1 - 1; j >= 0; j--)
+      if (j <= I.kord) {
+        const double v = phi[j * PBM_N + i];
+        s += I.c[j] * v;
+        if (j >= 1) sp += I.d[j] * v;
+      }
+    ydst[i] = s;
+    ypdst[i] = sp;
+  }
+}
+
+// IDAReInit: phi[0] = y, phi[1] = y' must already be in place.
+static PB_DEV void pb_reinit(pb_sys& S, double t0) {
+  S.tn = t0;
+  S.nst = 0;
+  S.kk = 0;
+  S.kused = 0;
+  S.hused = 0.0;
+  S.hh = 0.0;
+  S.tstopset = 0;
+  S.tretlast = t0;
+  S.epsNewt = S.epcon;
+  S.toldel = 1e-4 * S.epsNewt;
+}
+
+// IDASetCoeffs: thread 0 updates the coefficient arrays, everybody gets cj / ck. Ends with a barrier.
+// The phi -> phi* scaling (phi[i] *= beta[i], i >= ns) is folded into the predictor pass of pb_nls.
+static PB_DEV void pb_set_coeffs(pb_sys& S, double* ck) {
+  const int kk = S.kk;
+  if (S.hh != S.hused || kk != S.kused) S.ns = 0;
+  S.ns = (S.ns + 1 < S.kused + 2) ? S.ns + 1 : S.kused + 2;
+  double* psi = S_PSI(S);
+  double* alpha = S_ALPHA(S);
+  double* beta = S_BETA(S);
+  double* sigma = S_SIGMA(S);
+  double* gamma = S_GAMMA(S);
+  if (PB_TID == 0) {
+    if (kk + 1 >= S.ns) {
+      beta[0] = 1.0;
+      alpha[0] = 1.0;
+      gamma[0] = 0.0;
+      sigma[0] = 1.0;
+      double temp1 = S.hh;
+      for (int i = 1; i <= kk; i++) {
+        const double temp2 = psi[i - 1];
+        psi[i - 1] = temp1;
+        beta[i] = beta[i - 1] * psi[i - 1] / temp2;
+        temp1 = temp2 + S.hh;
+        alpha[i] = S.hh / temp1;
+        sigma[i] = i * sigma[i - 1] * alpha[i];
+        gamma[i] = gamma[i - 1] + alpha[i - 1] / S.hh;
+      }
+      psi[kk] = temp1;
+    }
+  }
+  PB_SYNC();
+  double alphas = 0.0, alpha0 = 0.0;
+  for (int i = 0; i < kk; i++) {
+    alphas -= 1.0 / (i + 1);
+    alpha0 -= alpha[i];
+  }
+  S.cjlast = S.cj;
+  S.cj = -alphas / S.hh;
+  double c = fabs(alpha[kk] + alphas - alpha0);
+  if (alpha[kk] > c) c = alpha[kk];
+  *ck = c;
+  S.tn += S.hh;
+}
+
+// IDARestore. phi_scaled: whether the predictor pass (and so the phi* scaling) ran. Ends with a barrier.
+static PB_DEV void pb_restore(pb_sys& S, double saved_t, int phi_scaled) {
+  S.tn = saved_t;
+  double* psi = S_PSI(S);
+  const double* beta = S_BETA(S);
+  PB_SYNC();
+  if (PB_TID == 0)
+    for (int j = 1; j <= S.kk; j++) psi[j - 1] = psi[j] - S.hh;
+  if (phi_scaled)
+    for (int j = S.ns; j <= S.kk; j++) {
+      const double r = 1.0 / beta[j];
+      double* ph = S_PHI(S, j);
+      for (int i = PB_TID; i < PBM_N; i += PB_TEAM) ph[i] *= r;
+    }
+  PB_SYNC();
+}
+
+#define PB_NLS_SUCCESS 0
+#define PB_NLS_CONV_RECVR 1
+#define PB_NLS_LSETUP_RECVR 2
+#define PB_ERROR_TEST_FAIL 7
+#define PB_PREDICT_AGAIN 20
+
+// IDANls + Newton iteration + idaNlsConvTest (modified Newton, J held between lsetups).
+static PB_DEV int pb_nls(pb_sys& S) {
+  int callLSetup = 0;
+  if (S.nst == 0) {
+    S.cjold = S.cj;
+    S.ss = 20.0;
+    callLSetup = 1;
+  }
+  S.cjratio = S.cj / S.cjold;
+  {
+    const double temp1 = (1.0 - 0.25) / (1.0 + 0.25), temp2 = 1.0 / temp1;
+    if (S.cjratio < temp1 || S.cjratio > temp2) callLSetup = 1;
+    if (S.cj != S.cjlast) S.ss = 100.0;
+  }
+  double* ee = S_EE(S);
+  double* delta = S_DELTA(S);
+  double* yypred = S_YYPRED(S);
+  double* yppred = S_YPPRED(S);
+  double* yy = S_YY(S);
+  const double* ewt = S_EWT(S);
+  {  // phi -> phi* and predictor
+    const double* beta = S_BETA(S);
+    const double* gamma = S_GAMMA(S);
+    double* phi = S_PHI(S, 0);
+    const int kk = S.kk, ns = S.ns;
+    double bj[PB_MXORDP1], gj[PB_MXORDP1];
+#pragma unroll
+    for (int j = 0; j < PB_MXORDP1; j++) {
+      bj[j] = (j <= kk) ? beta[j] : 0.0;
+      gj[j] = (j <= kk) ? gamma[j] : 0.0;
+    }
+    for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
+      double a = 0.0, b = 0.0;
+#pragma unroll
+      for (int j = PB_MXORDP1 - 1; j >= 0; j--) {
+        if (j <= kk) {
+          double v = phi[j * PBM_N + i];
+          if (j >= ns) {
+            v *= bj[j];
+            phi[j * PBM_N + i] = v;
+          }
+          a += v;
+          if (j >= 1) b += gj[j] * v;
+        }
+      }
+      yypred[i] = a;
+      yppred[i] = b;
+      ee[i] = 0.0;
+      yy[i] = a;
+    }
+    PB_SYNC();
+  }
+  int jcur = 0, retval = 0;
+  double oldnrm = 0.0;
+  for (;;) {
+    pbm_res(yy, S_P(S), S.tn, 0.0, delta, S_TMP(S));
+    PB_STAT(S, PB_ST_NRE);
+    PB_SYNC();
+    int fail = 0;
+    if (callLSetup) {
+      const int ier = pb_lsetup(S, S.tn, yy, S.cj, 0);
+      S.cjold = S.cj;
+      S.cjratio = 1.0;
+      S.ss = 20.0;
+      jcur = 1;
+      if (ier != 0) {
+        retval = PB_NLS_LSETUP_RECVR;
+        fail = 1;
+      }
+    }
+    if (!fail) {
+      int mnewt = 0;
+      for (;;) {
+        PB_STAT(S, PB_ST_NNI);
+        // rhs = -F = -(f - M y'),  y' = yppred + cj * ee on the differential rows
+        for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
+          double r = delta[i];
+          if (i < PBM_NDIFF) r -= yppred[i] + S.cj * ee[i];
+          delta[i] = -r;
+        }
+        PB_SYNC();
+        pb_lu_solve(S, delta);
+        const double scale = (S.scalesol && S.cjratio != 1.0) ? 2.0 / (1.0 + S.cjratio) : 1.0;
+        double acc = 0.0;
+        for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
+          const double d = delta[i] * scale;
+          const double e = ee[i] + d;
+          ee[i] = e;
+          yy[i] = yypred[i] + e;
+          const double v = d * ewt[i];
+          acc += v * v;
+        }
+        PB_SYNC();
+        const double delnrm = sqrt(pb_team_sum(S.team, acc) / PBM_N);
+        retval = -99;
+        if (!(delnrm == delnrm)) {
+          retval = PB_NLS_CONV_RECVR;
+          break;
+        }
+        if (mnewt == 0) {
+          oldnrm = delnrm;
+          if (delnrm <= 1e-4 * S.toldel) retval = PB_NLS_SUCCESS;
+        } else {
+          const double rate = pow(delnrm / oldnrm, 1.0 / mnewt);
+          if (rate > 0.9) {
+            retval = PB_NLS_CONV_RECVR;
+            break;
+          }
+          S.ss = rate / (1.0 - rate);
+        }
+        if (retval != PB_NLS_SUCCESS && S.ss * delnrm <= S.epsNewt) retval = PB_NLS_SUCCESS;
+        if (retval == PB_NLS_SUCCESS) return PB_NLS_SUCCESS;
+        mnewt++;
+        if (mnewt >= S.maxcor) {
+          retval = PB_NLS_CONV_RECVR;
+          break;
+        }
+        pbm_res(yy, S_P(S), S.tn, 0.0, delta, S_TMP(S));
+        PB_STAT(S, PB_ST_NRE);
+        PB_SYNC();
+      }
+    }
+    if (retval > 0 && !jcur) {
+      callLSetup = 1;
+      for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
+        ee[i] = 0.0;
+        yy[i] = yypred[i];
+      }
+      PB_SYNC();
+      continue;
+    }
+    return retval;
+  }
+}
+
+// IDATestError
+static PB_DEV int pb_test_error(pb_sys& S, double ck, double* err_k, double* err_km1) {
+  const int kk = S.kk;
+  const double* ee = S_EE(S);
+  const double* ewt = S_EWT(S);
+  const double* sigma = S_SIGMA(S);
+  const double* phik = S_PHI(S, kk);
+  const double* phikm1 = S_PHI(S, kk > 0 ? kk - 1 : 0);
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0;
+  for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
+    const double w = ewt[i];
+    double v = ee[i];
+    a0 += (v * w) * (v * w);
+    if (kk > 1) {
+      v += phik[i];
+      a1 += (v * w) * (v * w);
+      if (kk > 2) {
+        v += phikm1[i];
+        a2 += (v * w) * (v * w);
+      }
+    }
+  }
+  const double enorm_k = sqrt(pb_team_sum(S.team, a0) / PBM_N);
+  *err_k = sigma[kk] * enorm_k;
+  const double terr_k = (kk + 1) * (*err_k);
+  S.knew = kk;
+  if (kk > 1) {
+    *err_km1 = sigma[kk - 1] * sqrt(pb_team_sum(S.team, a1) / PBM_N);
+    const double terr_km1 = kk * (*err_km1);
+    if (kk > 2) {
+      const double err_km2 = sigma[kk - 2] * sqrt(pb_team_sum(S.team, a2) / PBM_N);
+      const double terr_km2 = (kk - 1) * err_km2;
+      if (fmax(terr_km1, terr_km2) <= terr_k) S.knew = kk - 1;
+    } else if (terr_km1 <= 0.5 * terr_k) {
+      S.knew = kk - 1;
+    }
+  }
+  return (ck * enorm_k > 1.0) ? PB_ERROR_TEST_FAIL : 0;
+}
+
+// IDAHandleNFlag
+static PB_DEV int pb_handle_nflag(pb_sys& S, int nflag, double err_k, double err_km1, int* ncf, int* nef) {
+  S.phase = 1;
+  if (nflag != PB_ERROR_TEST_FAIL) {
+    (*ncf)++;
+    PB_STAT(S, PB_ST_NCFN);
+    if (nflag < 0) return nflag;
+    S.rr = 0.25;
+    S.hh *= S.rr;
+    if (*ncf < S.maxncf) return PB_PREDICT_AGAIN;
+    return (nflag == PB_NLS_LSETUP_RECVR) ? PB_IDA_LSETUP_FAIL : PB_IDA_CONV_FAIL;
+  }
+  (*nef)++;
+  PB_STAT(S, PB_ST_NETF);
+  if (*nef == 1) {
+    const double err_knew = (S.kk == S.knew) ? err_k : err_km1;
+    S.kk = S.knew;
+    S.rr = 0.9 * pow(2.0 * err_knew + 0.0001, -1.0 / (S.kk + 1));
+    S.rr = fmax(0.25, fmin(0.9, S.rr));
+    S.hh *= S.rr;
+    return PB_PREDICT_AGAIN;
+  } else if (*nef == 2) {
+    S.kk = S.knew;
+    S.rr = 0.25;
+    S.hh *= S.rr;
+    return PB_PREDICT_AGAIN;
+  } else if (*nef < S.maxnef) {
+    S.kk = 1;
+    S.rr = 0.25;
+    S.hh *= S.rr;
+    return PB_PREDICT_AGAIN;
+  }
+  return PB_IDA_ERR_FAIL;
+}
+
+// IDACompleteStep. Ends with a barrier.
+static PB_DEV void pb_complete_step(pb_sys& S, double err_k, double err_km1) {
+  const double* ee = S_EE(S);
+  S.nst++;
+  PB_STAT(S, PB_ST_NST);
+  const int kdiff = S.kk - S.kused;
+  S.kused = S.kk;
+  S.hused = S.hh;
+  if (S.knew == S.kk - 1 || S.kk == S.maxord) S.phase = 1;
+  if (S.phase == 0) {
+    S.kk++;
+    double hnew = 2.0 * S.hh;
+    const double tmp = fabs(hnew) * S.hmax_inv;
+    if (tmp > 1.0) hnew /= tmp;
+    S.hh = hnew;
+  } else {
+    int action = 0;  // 0 unset, 1 lower, 2 maintain, 3 raise
+    double err_kp1 = 0.0, err_knew;
+    if (S.knew == S.kk - 1) action = 1;
+    else if (S.kk == S.maxord) action = 2;
+    else if (S.kk + 1 >= S.ns || kdiff == 1) action = 2;
+    if (action == 0) {
+      const double* phikp1 = S_PHI(S, S.kk + 1);
+      const double* ewt = S_EWT(S);
+      double acc = 0.0;
+      for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
+        const double v = (ee[i] - phikp1[i]) * ewt[i];
+        acc += v * v;
+      }
+      const double enorm = sqrt(pb_team_sum(S.team, acc) / PBM_N);
+      err_kp1 = enorm / (S.kk + 2);
+      const double terr_k = (S.kk + 1) * err_k, terr_kp1 = (S.kk + 2) * err_kp1;
+      if (S.kk == 1) {
+        action = (terr_kp1 >= 0.5 * terr_k) ? 2 : 3;
+      } else {
+        const double terr_km1 = S.kk * err_km1;
+        if (terr_km1 <= fmin(terr_k, terr_kp1)) action = 1;
+        else if (terr_kp1 >= terr_k) action = 2;
+        else action = 3;
+      }
+    }
+    if (action == 3) {
+      S.kk++;
+      err_knew = err_kp1;
+    } else if (action == 1) {
+      S.kk--;
+      err_knew = err_km1;
+    } else {
+      err_knew = err_k;
+    }
+    double hnew = S.hh;
+    S.rr = pow(2.0 * err_knew + 0.0001, -1.0 / (S.kk + 1));
+    if (S.rr >= 2.0) {
+      hnew = 2.0 * S.hh;
+      const double tmp = fabs(hnew) * S.hmax_inv;
+      if (tmp > 1.0) hnew /= tmp;
+    } else if (S.rr <= 1.0) {
+      S.rr = fmax(0.5, fmin(0.9, S.rr));
+      hnew = S.hh * S.rr;
+    }
+    S.hh = hnew;
+  }
+  // history update: phi[kused+1] = ee (if kused < maxord); phi[kused] += ee; phi[j] += phi[j+1]
+  {
+    double* phi = S_PHI(S, 0);
+    const int ku = S.kused, save = (ku < S.maxord);
+    for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
+      const double e = ee[i];
+      if (save) phi[(ku + 1) * PBM_N + i] = e;
+      double run = phi[ku * PBM_N + i] + e;
+      phi[ku * PBM_N + i] = run;
+      for (int j = ku - 1; j >= 0; j--) {
+        run += phi[j * PBM_N + i];
+        phi[j * PBM_N + i] = run;
+      }
+    }
+  }
+  PB_SYNC();
+}
+
+// IDAStep
+static PB_DEV int pb_ida_step(pb_sys& S) {
+  const double saved_t = S.tn;
+  double ck = 0.0, err_k = 0.0, err_km1 = 0.0;
+  int ncf = 0, nef = 0;
+  if (S.nst == 0) {
+    S.kk = 1;
+    S.kused = 0;
+    S.hused = 0.0;
+    if (PB_TID == 0) S_PSI(S)[0] = S.hh;
+    S.cj = 1.0 / S.hh;
+    S.phase = 0;
+    S.ns = 0;
+    PB_SYNC();
+  }
+  for (;;) {
+    pb_set_coeffs(S, &ck);
+    int nflag = pb_nls(S);
+    if (nflag == PB_NLS_SUCCESS) nflag = pb_test_error(S, ck, &err_k, &err_km1);
+    if (nflag != 0) {
+      pb_restore(S, saved_t, 1);
+      const int kflag = pb_handle_nflag(S, nflag, err_k, err_km1, &ncf, &nef);
+      if (kflag != PB_PREDICT_AGAIN) return kflag;
+      if (S.nst == 0) {
+        if (PB_TID == 0) S_PSI(S)[0] = S.hh;
+        double* phi1 = S_PHI(S, 1);
+        for (int i = PB_TID; i < PBM_N; i += PB_TEAM) phi1[i] *= S.rr;
+        PB_SYNC();
+      }
+      if (!(fabs(S.hh) > 0.0) || S.tn + S.hh == S.tn) return PB_IDA_ERR_FAIL;
+      continue;
+    }
+    break;
+  }
+  pb_complete_step(S, err_k, err_km1);
+  return PB_IDA_SUCCESS;
+}
+
+// ---- termination events: IDARcheck1 / IDARcheck3 / IDARootfind (Illinois) on the BDF interpolant ----
+static PB_DEV void pb_gfun(pb_sys& S, double t, const double* y, double* g) {
+#if PBM_NEV > 0
+  pbm_events(y, S_P(S), t, 0.0, g, S_TMP(S));
+  PB_STAT(S, PB_ST_NGE);
+  PB_SYNC();
+#endif
+}
+
+#if PBM_NEV > 0
+static PB_DEV int pb_rootfind(pb_sys& S) {
+  double* glo = S_GLO(S);
+  double* ghi = S_GHI(S);
+  double* grout = S_GROUT(S);
+  int imax = 0, zroot = 0, sgnchg = 0, side = 0, sideprev = -1;
+  double maxfrac = 0.0, alph = 1.0;
+  for (int i = 0; i < PBM_NEV; i++) {
+    if (!((S.gactive >> i) & 1u)) continue;
+    if (fabs(ghi[i]) == 0.0) zroot = 1;
+    else if (glo[i] * ghi[i] < 0.0) {
+      const double gfrac = fabs(ghi[i] / (ghi[i] - glo[i]));
+      if (gfrac > maxfrac) {
+        sgnchg = 1;
+        maxfrac = gfrac;
+        imax = i;
+      }
+    }
+  }
+  if (!sgnchg) {
+    S.trout = S.thi;
+    PB_SYNC();
+    if (PB_TID == 0)
+      for (int i = 0; i < PBM_NEV; i++) grout[i] = ghi[i];
+    PB_SYNC();
+    return zroot;
+  }
+  for (;;) {
+    if (fabs(S.thi - S.tlo) <= S.ttol) break;
+    if (sideprev == side) alph = (side == 2) ? alph * 2.0 : alph * 0.5;
+    else alph = 1.0;
+    double tmid = S.thi - (S.thi - S.tlo) * ghi[imax] / (ghi[imax] - alph * glo[imax]);
+    if (fabs(tmid - S.tlo) < 0.5 * S.ttol) {
+      const double fracint = fabs(S.thi - S.tlo) / S.ttol;
+      const double fracsub = (fracint > 5.0) ? 0.1 : 0.5 / fracint;
+      tmid = S.tlo + fracsub * (S.thi - S.tlo);
+    }
+    if (fabs(S.thi - tmid) < 0.5 * S.ttol) {
+      const double fracint = fabs(S.thi - S.tlo) / S.ttol;
+      const double fracsub = (fracint > 5.0) ? 0.1 : 0.5 / fracint;
+      tmid = S.thi - fracsub * (S.thi - S.tlo);
+    }
+    pb_get_solution(S, tmid, S_YY(S));
+    PB_SYNC();
+    pb_gfun(S, tmid, S_YY(S), grout);
+    maxfrac = 0.0;
+    zroot = 0;
+    sgnchg = 0;
+    sideprev = side;
+    for (int i = 0; i < PBM_NEV; i++) {
+      if (!((S.gactive >> i) & 1u)) continue;
+      if (fabs(grout[i]) == 0.0) zroot = 1;
+      else if (glo[i] * grout[i] < 0.0) {
+        const double gfrac = fabs(grout[i] / (grout[i] - glo[i]));
+        if (gfrac > maxfrac) {
+          sgnchg = 1;
+          maxfrac = gfrac;
+          imax = i;
+        }
+      }
+    }
+    PB_SYNC();  // everybody has read grout/glo/ghi before thread 0 shuffles them
+    if (sgnchg) {
+      S.thi = tmid;
+      if (PB_TID == 0)
+        for (int i = 0; i < PBM_NEV; i++) ghi[i] = grout[i];
+      PB_SYNC();
+      side = 1;
+      if (fabs(S.thi - S.tlo) <= S.ttol) break;
+      continue;
+    }
+    if (zroot) {
+      S.thi = tmid;
+      if (PB_TID == 0)
+        for (int i = 0; i < PBM_NEV; i++) ghi[i] = grout[i];
+      PB_SYNC();
+      break;
+    }
+    S.tlo = tmid;
+    if (PB_TID == 0)
+      for (int i = 0; i < PBM_NEV; i++) glo[i] = grout[i];
+    PB_SYNC();
+    side = 2;
+    if (fabs(S.thi - S.tlo) <= S.ttol) break;
+  }
+  S.trout = S.thi;
+  PB_SYNC();
+  if (PB_TID == 0)
+    for (int i = 0; i < PBM_NEV; i++) grout[i] = ghi[i];
+  PB_SYNC();
+  return 1;
+}
+
+// IDARcheck3 for the ONE_STEP task (thi = tn). Returns 1 when a root was found; y(trout) is then in S_YY.
+static PB_DEV int pb_rcheck3(pb_sys& S) {
+  double* glo = S_GLO(S);
+  double* grout = S_GROUT(S);
+  S.thi = S.tn;
+  pb_get_solution(S, S.thi, S_YY(S));
+  PB_SYNC();
+  pb_gfun(S, S.thi, S_YY(S), S_GHI(S));
+  S.ttol = (fabs(S.tn) + fabs(S.hh)) * PB_UROUND * 100.0;
+  const int ier = pb_rootfind(S);
+  for (int i = 0; i < PBM_NEV; i++)
+    if (!((S.gactive >> i) & 1u) && grout[i] != 0.0) S.gactive |= (1u << i);
+  S.tlo = S.trout;
+  PB_SYNC();
+  if (PB_TID == 0)
+    for (int i = 0; i < PBM_NEV; i++) glo[i] = grout[i];
+  PB_SYNC();
+  if (!ier) return 0;
+  pb_get_solution(S, S.trout, S_YY(S));
+  PB_SYNC();
+  return 1;
+}
+#endif
+
+// IDASolve(tout, ONE_STEP). On return *tret is the time reached; for ROOT returns y(tret) is in S_YY.
+static PB_DEV int pb_ida_solve_one_step(pb_sys& S, double tout, double* tret) {
+  if (S.nst == 0) {
+    if (pb_ewt_set(S, S_PHI(S, 0))) return PB_IDA_ILL_INPUT;
+    const double tdist = fabs(tout - S.tn);
+    if (S.dt_init != 0.0) {
+      S.hh = S.dt_init;
+    } else {
+      S.hh = 0.001 * tdist;
+      const double ypnorm = pb_wrms(S, S_PHI(S, 1));
+      if (ypnorm > 0.5 / S.hh) S.hh = 0.5 / ypnorm;
+      if (tout < S.tn) S.hh = -S.hh;
+    }
+    {
+      const double rh = fabs(S.hh) * S.hmax_inv;
+      if (rh > 1.0) S.hh /= rh;
+    }
+    if (S.tstopset && (S.tn + S.hh - S.tstop) * S.hh > 0.0) S.hh = (S.tstop - S.tn) * (1.0 - 4.0 * PB_UROUND);
+    S.kk = 0;
+    S.kused = 0;
+    {
+      double* phi1 = S_PHI(S, 1);
+      for (int i = PB_TID; i < PBM_N; i += PB_TEAM) phi1[i] *= S.hh;
+      PB_SYNC();
+    }
+#if PBM_NEV > 0
+    {  // IDARcheck1
+      double* glo = S_GLO(S);
+      double* ghi = S_GHI(S);
+      S.tlo = S.tn;
+      S.ttol = (fabs(S.tn) + fabs(S.hh)) * PB_UROUND * 100.0;
+      pb_gfun(S, S.tlo, S_PHI(S, 0), glo);
+      int zroot = 0;
+      S.gactive = 0u;
+      for (int i = 0; i < PBM_NEV; i++) {
+        if (fabs(glo[i]) == 0.0) zroot = 1;
+        else S.gactive |= (1u << i);
+      }
+      if (zroot) {
+        const double hratio = fmax(S.ttol / fabs(S.hh), 0.1), smallh = hratio * S.hh;
+        const double* phi0 = S_PHI(S, 0);
+        const double* phi1 = S_PHI(S, 1);
+        double* yy = S_YY(S);
+        for (int i = PB_TID; i < PBM_N; i += PB_TEAM) yy[i] = phi0[i] + hratio * phi1[i];
+        PB_SYNC();
+        pb_gfun(S, S.tlo + smallh, yy, ghi);
+        unsigned act = S.gactive;
+        for (int i = 0; i < PBM_NEV; i++)
+          if (!((act >> i) & 1u) && fabs(ghi[i]) != 0.0) act |= (1u << i);
+        PB_SYNC();
+        if (PB_TID == 0)
+          for (int i = 0; i < PBM_NEV; i++)
+            if (!((S.gactive >> i) & 1u) && ((act >> i) & 1u)) glo[i] = ghi[i];
+        PB_SYNC();
+        S.gactive = act;
+      }
+    }
+#endif
+  } else {
+    // IDAStopTest1, ONE_STEP
+    if ((S.tn - S.tretlast) * S.hh > 0.0) {
+      *tret = S.tretlast = S.tn;
+      return PB_IDA_SUCCESS;
+    }
+    if (S.tstopset) {
+      const double troundoff = 100.0 * PB_UROUND * (fabs(S.tn) + fabs(S.hh));
+      if (fabs(S.tn - S.tstop) <= troundoff) {
+        *tret = S.tretlast = S.tstop;
+        S.tstopset = 0;
+        return PB_IDA_TSTOP_RETURN;
+      }
+      if ((S.tn + S.hh - S.tstop) * S.hh > 0.0) S.hh = (S.tstop - S.tn) * (1.0 - 4.0 * PB_UROUND);
+    }
+  }
+  if (S.nst > 0 && pb_ewt_set(S, S_PHI(S, 0))) return PB_IDA_ILL_INPUT;
+  {
+    const double nrm = pb_wrms(S, S_PHI(S, 0));
+    if (PB_UROUND * nrm > 1.0) return PB_IDA_TOO_MUCH_ACC;
+  }
+  const int sflag = pb_ida_step(S);
+  if (sflag != PB_IDA_SUCCESS) {
+    *tret = S.tretlast = S.tn;
+    return sflag;
+  }
+  if (S.tstopset) {
+    const double troundoff = 100.0 * PB_UROUND * (fabs(S.tn) + fabs(S.hh));
+    if (fabs(S.tn - S.tstop) <= troundoff) S.tn = S.tstop;
+  }
+#if PBM_NEV > 0
+  if (pb_rcheck3(S)) {
+    *tret = S.tretlast = S.tlo;
+    return PB_IDA_ROOT_RETURN;
+  }
+#endif
+  // IDAStopTest2, ONE_STEP
+  if (S.tstopset) {
+    const double troundoff = 100.0 * PB_UROUND * (fabs(S.tn) + fabs(S.hh));
+    if (fabs(S.tn - S.tstop) <= troundoff) {
+      *tret = S.tretlast = S.tstop;
+      S.tstopset = 0;
+      return PB_IDA_TSTOP_RETURN;
+    }
+    if ((S.tn + S.hh - S.tstop) * S.hh > 0.0) S.hh = (S.tstop - S.tn) * (1.0 - 4.0 * PB_UROUND);
+  }
+  *tret = S.tretlast = S.tn;
+  return PB_IDA_SUCCESS;
+}
+
+// ---- consistent initialisation (IDAKLUSolverOpenMP.inl:787-873) ---------------------------------
+// y' = f(t, y) on the differential rows, 0 on the algebraic rows: phi[1] <- y'(phi[0]). Ends with a barrier.
+static PB_DEV void pb_recover_yp(pb_sys& S, double t) {
+  double* phi1 = S_PHI(S, 1);
+  pbm_res(S_PHI(S, 0), S_P(S), t, 0.0, phi1, S_TMP(S));
+  PB_SYNC();
+  for (int i = PBM_NDIFF + PB_TID; i < PBM_N; i += PB_TEAM) phi1[i] = 0.0;
+  PB_SYNC();
+}
+
+#if PBM_N > PBM_NDIFF
+#define PB_NALG (PBM_N - PBM_NDIFF)
+// max-norm of the algebraic residual at y (result also left in S_DELTA). Ends with a barrier.
+static PB_DEV double pb_alg_res_norm(pb_sys& S, double t, const double* y) {
+  double* res = S_DELTA(S);
+  pbm_res(y, S_P(S), t, 0.0, res, S_TMP(S));
+  PB_SYNC();
+  double mx = 0.0;
+  for (int i = PBM_NDIFF + PB_TID; i < PBM_N; i += PB_TEAM) {
+    const double a = fabs(res[i]);
+    mx = (a != a || mx != mx) ? PB_NAN : fmax(mx, a);
+  }
+  mx = pb_team_max(S.team, mx);
+  PB_SYNC();
+  return mx;
+}
+
+// NonlinearSolver::RunNewtonLoop (NonlinearSolver.inl:100-177) on the algebraic sub-block; the
+// sub-block system J_aa d = g is solved through the full static LU with identity differential rows.
+// y (= S_YY) is updated in place.  Returns 1 on success.
+static PB_DEV int pb_newton_ic(pb_sys& S, double t, double* init_norm, double* final_norm) {
+  double* y = S_YY(S);
+  double* xsave = S_EE(S);
+  double* res = S_DELTA(S);
+  double* del = S_YYPRED(S);
+  double* ewt = S_EWT(S);
+  double delnorm = PB_INF, prev_res_norm = PB_INF;
+  int converged = 0;
+  for (int i = PBM_NDIFF + PB_TID; i < PBM_N; i += PB_TEAM) {
+    ewt[i] = 1.0 / (S.rtol * fabs(y[i]) + PB_LD(S.atol[i]));
+    xsave[i] = y[i];
+  }
+  PB_SYNC();
+  for (int iter = 0; iter < S.max_iter_ic; iter++) {
+    const double res_norm = pb_alg_res_norm(S, t, y);
+    if (iter == 0) *init_norm = res_norm;
+    *final_norm = res_norm;
+    if (pb_lsetup(S, t, y, 0.0, 1)) return 0;
+    for (int i = PB_TID; i < PBM_NDIFF; i += PB_TEAM) res[i] = 0.0;
+    PB_SYNC();
+    pb_lu_solve(S, res);
+    double acc = 0.0;
+    for (int i = PBM_NDIFF + PB_TID; i < PBM_N; i += PB_TEAM) {
+      const double d = res[i];
+      del[i] = d;
+      const double v = d * ewt[i];
+      acc += v * v;
+    }
+    PB_SYNC();
+    delnorm = sqrt(pb_team_sum(S.team, acc) / PB_NALG);
+    if (delnorm <= S.epsNewtIC) {
+      converged = 1;
+      if (delnorm <= S.step_tol_ic) {
+        for (int i = PBM_NDIFF + PB_TID; i < PBM_N; i += PB_TEAM) y[i] -= del[i];
+        PB_SYNC();
+        return 1;
+      }
+      if (iter > 0 && res_norm >= prev_res_norm) {
+        for (int i = PBM_NDIFF + PB_TID; i < PBM_N; i += PB_TEAM) y[i] = xsave[i];
+        PB_SYNC();
+        return 1;
+      }
+    }
+    if (!(delnorm == delnorm)) return 0;
+    prev_res_norm = res_norm;
+    for (int i = PBM_NDIFF + PB_TID; i < PBM_N; i += PB_TEAM) xsave[i] = y[i];
+    PB_SYNC();
+    double alpha = 1.0;
+    for (int ls = 0; ls < S.max_backtracks_ic; ls++) {
+      for (int i = PBM_NDIFF + PB_TID; i < PBM_N; i += PB_TEAM) y[i] = xsave[i] - alpha * del[i];
+      PB_SYNC();
+      const double trial = pb_alg_res_norm(S, t, y);
+      if (trial <= (1.0 - alpha * 0.5) * res_norm) break;
+      if (alpha * delnorm <= S.step_tol_ic) break;
+      alpha *= 0.5;
+    }
+  }
+  return converged;
+}
+#endif
+
+// ConsistentInitialization + IDAReInit at time t; on entry phi[0] holds y.
+static PB_DEV void pb_consistent_init(pb_sys& S, double t, int calc_ic) {
+#if PBM_N > PBM_NDIFF
+  if (calc_ic) {
+    double* phi0 = S_PHI(S, 0);
+    double* y = S_YY(S);
+    double* backup = S_YPPRED(S);
+    for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
+      y[i] = phi0[i];
+      backup[i] = phi0[i];
+    }
+    PB_SYNC();
+    double in = 0.0, fn = 0.0;
+    const int ok = pb_newton_ic(S, t, &in, &fn);
+    if (ok || fn <= in) {
+      for (int i = PB_TID; i < PBM_N; i += PB_TEAM) phi0[i] = y[i];
+      PB_SYNC();
+    }
+  }
+#endif
+  pb_recover_yp(S, t);
+  pb_reinit(S, t);
+}
+
+// ---- the PyBaMM driver loop (IDAKLUSolverOpenMP::solve, IDAKLUSolverOpenMP.inl:327-444) ----------
+static PB_DEV double pb_perturb_time(double t) {
+  const double delta = 1.4901161193847656e-08;  // sqrt(DBL_EPSILON)
+  return (1.0 + delta) * t + delta;
+}
+
+static PB_DEV void pb_store_point(pb_sys& S, const pbgpu_launch& L, int sys, double t, int* i_save, double* t_last) {
+  if (*i_save >= L.n_max) return;
+  *t_last = t;
+  const size_t slot = (size_t)sys * L.n_max + *i_save;
+  double* row = L.y_out + slot * L.n_ret;
+  if (L.save_vars) {
+#if PBM_NVAR > 0
+    pb_get_solution(S, t, S_YY(S));
+    PB_SYNC();
+    pbm_vars(S_YY(S), S_P(S), t, 0.0, row, S_TMP(S));
+    PB_SYNC();
+#endif
+  } else {
+    pb_get_solution(S, t, row);
+  }
+  if (PB_TID == 0) L.t_out[slot] = t;
+  (*i_save)++;
+}
+
+static PB_DEV void pb_solve_system(pb_sys& S, const pbgpu_launch& L, int sys) {
+  const double t0 = PB_LDU(L.t_eval[0]), tf = PB_LDU(L.t_eval[L.n_eval - 1]);
+  const double tf_perturbed = pb_perturb_time(tf);
+  PB_SYNC();
+  for (int k = PB_TID; k < PBM_NP_REAL; k += PB_TEAM) S_P(S)[k] = L.inputs[(size_t)sys * PBM_NP_REAL + k];
+  for (int k = PB_TID; k < 8; k += PB_TEAM) S_STATS(S)[k] = 0.0;
+  PB_SYNC();
+  if (L.y0) {
+    double* phi0 = S_PHI(S, 0);
+    for (int i = PB_TID; i < PBM_N; i += PB_TEAM) phi0[i] = L.y0[(size_t)sys * PBM_N + i];
+  } else {
+    pbm_ic(S_YY(S), S_P(S), t0, 0.0, S_PHI(S, 0), S_TMP(S));
+  }
+  PB_SYNC();
+  pb_consistent_init(S, t0, L.opt.calc_ic);
+  int i_save = 0, i_eval = 1, i_interp = 0;
+  double t_eval_next = PB_LDU(L.t_eval[1]);
+  S.tstop = t_eval_next;
+  S.tstopset = 1;
+  int retval = PB_IDA_SUCCESS;
+  double t_val = t0, t_prev = t0, t_last = t0;
+  int done = 0;
+#if PBM_NEV > 0
+  {
+    double* g = S_GHI(S);
+    pb_gfun(S, t0, S_PHI(S, 0), g);
+    int trig = 0;
+    for (int i = 0; i < PBM_NEV; i++) trig |= (g[i] <= 0.0);
+    PB_SYNC();
+    if (trig) {
+      // IDA has not stepped: psi is not set, store phi[0] directly
+      if (i_save < L.n_max) {
+        const size_t slot = (size_t)sys * L.n_max;
+        double* row = L.y_out + slot * L.n_ret;
+        if (L.save_vars) {
+#if PBM_NVAR > 0
+          pbm_vars(S_PHI(S, 0), S_P(S), t0, 0.0, row, S_TMP(S));
+          PB_SYNC();
+#endif
+        } else {
+          const double* phi0 = S_PHI(S, 0);
+          for (int i = PB_TID; i < PBM_N; i += PB_TEAM) row[i] = phi0[i];
+        }
+        if (PB_TID == 0) L.t_out[slot] = t0;
+        i_save = 1;
+      }
+      retval = PB_IDA_ROOT_RETURN;
+      done = 1;
+      if (L.y_term) {
+        const double* phi0 = S_PHI(S, 0);
+        for (int i = PB_TID; i < PBM_N; i += PB_TEAM) L.y_term[(size_t)sys * PBM_N + i] = phi0[i];
+      }
+    }
+  }
+#endif
+  if (!done) {
+    retval = pb_ida_solve_one_step(S, tf_perturbed, &t_val);
+    if (retval >= 0) pb_store_point(S, L, sys, t0, &i_save, &t_last);
+    long long guard = 0;
+    for (;;) {
+      if (retval < 0) break;
+      if (t_prev == t_val) {
+        retval = PB_IDA_ERR_FAIL;
+        break;
+      }
+      const int hit_teval = retval == PB_IDA_TSTOP_RETURN;
+      const int hit_final = t_val >= tf || (hit_teval && i_eval == L.n_eval);
+      const int hit_event = retval == PB_IDA_ROOT_RETURN;
+      const int hit_adaptive = (L.n_interp == 0) && retval == PB_IDA_SUCCESS;
+      const int final_step = hit_final || hit_event;
+      if (L.n_interp > 0 && i_interp < L.n_interp && PB_LDU(L.t_interp[i_interp]) >= t_prev) {
+        while (i_interp < L.n_interp) {
+          const double ti = PB_LDU(L.t_interp[i_interp]);
+          if (!(ti <= t_val)) break;
+          pb_store_point(S, L, sys, ti, &i_save, &t_last);
+          i_interp++;
+        }
+      }
+      if (hit_adaptive || hit_teval || hit_event || hit_final) {
+        // duplicate check against the last stored time (SavePoint, IDAKLUSolverOpenMP.inl:608-616)
+        if (i_save == 0 || t_val != t_last) pb_store_point(S, L, sys, t_val, &i_save, &t_last);
+      }
+      if (final_step) break;
+      if (hit_teval) {
+        i_eval++;
+        t_eval_next = PB_LDU(L.t_eval[i_eval]);
+        PB_SYNC();
+        pb_get_solution2(S, t_val, S_YY(S), S_YPPRED(S));
+        PB_SYNC();
+        {
+          double* phi0 = S_PHI(S, 0);
+          const double* yy = S_YY(S);
+          for (int i = PB_TID; i < PBM_N; i += PB_TEAM) phi0[i] = yy[i];
+          PB_SYNC();
+        }
+        pb_consistent_init(S, t_val, 1);
+        S.tstop = t_eval_next;
+        S.tstopset = 1;
+      }
+      t_prev = t_val;
+      if (++guard > S.max_num_steps) {
+        retval = PB_IDA_TOO_MUCH_WORK;
+        break;
+      }
+      retval = pb_ida_solve_one_step(S, tf_perturbed, &t_val);
+    }
+    if (L.y_term) {
+      PB_SYNC();
+      if (S.nst > 0 || S.kused > 0) pb_get_solution(S, t_val, L.y_term + (size_t)sys * PBM_N);
+      else {
+        const double* phi0 = S_PHI(S, 0);
+        for (int i = PB_TID; i < PBM_N; i += PB_TEAM) L.y_term[(size_t)sys * PBM_N + i] = phi0[i];
+      }
+    }
+  }
+  PB_SYNC();
+  if (PB_TID == 0) {
+    L.n_out[sys] = i_save;
+    L.flag[sys] = retval;
+    if (L.stats)
+      for (int k = 0; k < 8; k++) L.stats[(size_t)sys * 8 + k] = (long long)S_STATS(S)[k];
+  }
+}
+
+static PB_DEV void pb_sys_init(pb_sys& S, double* sm, const pbgpu_launch& L) {
+  S.sm = sm;
+  S.team.red = sm + PB_OFF_RED;
+  if (PB_TID == 0) {
+    S_LU(S)[PBM_NNZ_LU] = 0.0;  // constant-zero padding operands of the ELL tables
+    S_W(S)[PBM_N] = 0.0;
+  }
+#ifndef PB_EMU
+  S.team.red_phase = 0;
+#endif
+  S.atol = L.atol;
+  S.rtol = L.opt.rtol;
+  S.epcon = L.opt.nonlinear_convergence_coefficient;
+  S.epsNewtIC = L.opt.nonlinear_convergence_coefficient_ic;
+  S.step_tol_ic = L.opt.newton_step_tol;
+  S.dt_init = L.opt.dt_init;
+  S.hmax_inv = (L.opt.dt_max > 0.0) ? 1.0 / L.opt.dt_max : 0.0;
+  S.maxord = L.opt.max_order_bdf < 5 ? (L.opt.max_order_bdf < 1 ? 1 : L.opt.max_order_bdf) : 5;
+  S.maxnef = L.opt.max_error_test_failures;
+  S.maxcor = L.opt.max_nonlinear_iterations;
+  S.maxncf = L.opt.max_convergence_failures;
+  S.max_iter_ic = L.opt.max_num_iterations_ic;
+  S.max_backtracks_ic = L.opt.max_linesearch_backtracks_ic;
+  S.scalesol = L.opt.linear_solution_scaling;
+  S.max_num_steps = L.opt.max_num_steps;
+  S.cj = 0.0;
+  S.cjlast = 0.0;
+  S.cjold = 1.0;
+  S.cjratio = 1.0;
+  S.ss = 20.0;
+  S.rr = 0.0;
+  S.gactive = 0u;
+  S.ns = 0;
+  S.knew = 0;
+  S.phase = 0;
+  S.tlo = S.thi = S.trout = S.ttol = 0.0;
+}

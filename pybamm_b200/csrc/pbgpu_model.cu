@@ -1,0 +1,203 @@
+// pbgpu_model.cu -- translation unit of ONE compiled model image (sm_100a).
+//
+// nvcc -gencode arch=compute_100a,code=sm_100a -DPBM_HEADER="<generated header>" -DPB_TEAM_SIZE=<32|64|128|256>
+//
+// Contains the generated model functions (residual, J - cj*M into the static LU slots, events, initial
+// conditions, output variables), the sparse-LU tables and the batched BDF integrator specialised for them,
+// plus the three host entry points libpbgpu.so binds with dlsym.  Role in the reference: the per-solver
+// CasadiFunctions + IDAKLUSolverOpenMP_KLU objects built by create_casadi_solver_group
+// (packages/pybammsolvers/src/pybammsolvers/idaklu.cpp:30-124).
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "pbgpu.h"
+#include "pbgpu_team.cuh"
+#include PBM_HEADER
+#include "pbgpu_ida.cuh"
+
+extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE) pbgpu_solve_kernel(const pbgpu_launch L) {
+  extern __shared__ double pb_smem[];
+  __shared__ unsigned int next_sys;
+  pb_sys S;
+  pb_sys_init(S, pb_smem, L);
+  for (;;) {
+    if (threadIdx.x == 0) next_sys = atomicAdd(L.queue, 1u);
+    __syncthreads();
+    const unsigned int sys = next_sys;
+    __syncthreads();
+    if (sys >= (unsigned int)L.n_sys) break;
+    pb_solve_system(S, L, (int)sys);
+  }
+}
+
+// Evaluate generated functions / the LU for parity tests of the code generator (one team per system).
+extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE) pbgpu_eval_kernel(const pbgpu_eval_launch E) {
+  extern __shared__ double pb_smem[];
+  pb_sys S;
+  S.sm = pb_smem;
+  S.team.red = pb_smem + PB_OFF_RED;
+  S.team.red_phase = 0;
+  if (PB_TID == 0) {
+    S_LU(S)[PBM_NNZ_LU] = 0.0;
+    S_W(S)[PBM_N] = 0.0;
+  }
+  for (int sys = blockIdx.x; sys < E.n_sys; sys += gridDim.x) {
+    __syncthreads();
+    double* y = S_YY(S);
+    double* out = S_DELTA(S);
+    for (int i = PB_TID; i < PBM_N; i += PB_TEAM) y[i] = E.y ? E.y[(size_t)sys * PBM_N + i] : 0.0;
+    for (int k = PB_TID; k < PBM_NP_REAL; k += PB_TEAM) S_P(S)[k] = E.p[(size_t)sys * PBM_NP_REAL + k];
+    for (int k = PB_TID; k < 8; k += PB_TEAM) S_STATS(S)[k] = 0.0;
+    __syncthreads();
+    double* gout = E.out + (size_t)sys * E.out_len;
+    switch (E.which) {
+      case 0:
+        pbm_res(y, S_P(S), E.t, E.cj, out, S_TMP(S));
+        PB_SYNC();
+        for (int i = PB_TID; i < PBM_N && i < E.out_len; i += PB_TEAM) gout[i] = out[i];
+        break;
+      case 1: {
+        double* lu = S_LU(S);
+        for (int i = PB_TID; i < PBM_NNZ_LU; i += PB_TEAM) lu[i] = 0.0;
+        PB_SYNC();
+        pbm_jac(y, S_P(S), E.t, E.cj, lu, S_TMP(S));
+        PB_SYNC();
+        for (int k = PB_TID; k < PBM_NNZ && k < E.out_len; k += PB_TEAM) gout[k] = lu[(int)pbm_ent_slot[k]];
+      } break;
+      case 2:
+#if PBM_NEV > 0
+        pbm_events(y, S_P(S), E.t, E.cj, S_GHI(S), S_TMP(S));
+        PB_SYNC();
+        for (int i = PB_TID; i < PBM_NEV && i < E.out_len; i += PB_TEAM) gout[i] = S_GHI(S)[i];
+#endif
+        break;
+      case 3:
+        pbm_ic(y, S_P(S), E.t, E.cj, out, S_TMP(S));
+        PB_SYNC();
+        for (int i = PB_TID; i < PBM_N && i < E.out_len; i += PB_TEAM) gout[i] = out[i];
+        break;
+      case 4:
+#if PBM_NVAR > 0
+        pbm_vars(y, S_P(S), E.t, E.cj, gout, S_TMP(S));
+#endif
+        break;
+      case 5: {
+        const int bad = pb_lsetup(S, E.t, y, E.cj, 0);
+        for (int i = PB_TID; i < PBM_N; i += PB_TEAM) out[i] = E.y2[(size_t)sys * PBM_N + i];
+        PB_SYNC();
+        pb_lu_solve(S, out);
+        for (int i = PB_TID; i < PBM_N && i < E.out_len; i += PB_TEAM) gout[i] = bad ? CUDART_NAN : out[i];
+      } break;
+      default:
+        break;
+    }
+  }
+}
+
+static int g_configured_device = -1;
+static int g_blocks_per_sm = 0, g_num_sms = 0;
+
+static int pb_configure(char* err, size_t errlen) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    snprintf(err, errlen, "cudaGetDevice: %s", cudaGetErrorString(e));
+    return 1;
+  }
+  if (dev == g_configured_device) return 0;
+  e = cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
+  if (e != cudaSuccess) {
+    snprintf(err, errlen, "model '%s' needs %d bytes of shared memory per team: %s", PBM_NAME, (int)PB_SMEM_BYTES,
+             cudaGetErrorString(e));
+    return 1;
+  }
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, dev);
+  g_num_sms = prop.multiProcessorCount;
+  // Shared-memory carve-out: the per-team state lives in shared memory, but the index tables of the
+  // generated functions and of the sparse LU are read through L1 -- leave it room.  By default at most
+  // 164 KB of the SM's 228 KB go to shared memory (=> >= 64 KB of L1) unless one team needs more.
+  int carve_kb = 164;
+  if (const char* env = getenv("PBGPU_SMEM_CARVEOUT_KB")) carve_kb = atoi(env);
+  const int per_team = (int)PB_SMEM_BYTES + 1024;  // + the per-CTA reservation
+  if (carve_kb * 1024 < per_team) carve_kb = (per_team + 1023) / 1024;
+  if (carve_kb > 227) carve_kb = 227;
+  const int total_kb = (int)(prop.sharedMemPerMultiprocessor / 1024);
+  int pct = (carve_kb * 100 + total_kb - 1) / total_kb;
+  if (pct > 100) pct = 100;
+  cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+  cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_blocks_per_sm, pbgpu_solve_kernel, PB_TEAM_SIZE, PB_SMEM_BYTES);
+  if (e != cudaSuccess || g_blocks_per_sm < 1) {
+    snprintf(err, errlen, "occupancy query failed for model '%s': %s", PBM_NAME, cudaGetErrorString(e));
+    return 1;
+  }
+  int by_carve = carve_kb * 1024 / per_team;
+  if (by_carve < 1) by_carve = 1;
+  if (g_blocks_per_sm > by_carve) g_blocks_per_sm = by_carve;
+  if (const char* env = getenv("PBGPU_TEAMS_PER_SM")) {
+    const int v = atoi(env);
+    if (v >= 1 && v < g_blocks_per_sm) g_blocks_per_sm = v;
+  }
+  g_configured_device = dev;
+  return 0;
+}
+
+extern "C" int pbgpu_image_describe(pbgpu_model_desc* d) {
+  memset(d, 0, sizeof(*d));
+  d->abi_version = PBGPU_ABI_VERSION;
+  d->n_states = PBM_N;
+  d->n_diff = PBM_NDIFF;
+  d->n_inputs = PBM_NP_REAL;
+  d->n_events = PBM_NEV;
+  d->nnz_jac = PBM_NNZ;
+  d->nnz_lu = PBM_NNZ_LU;
+  d->n_vars = PBM_NVAR;
+  d->team_size = PB_TEAM_SIZE;
+  d->smem_bytes = PB_SMEM_BYTES;
+  d->n_tmp = PBM_NTMP;
+  d->lu_levels[0] = PBM_FAC_NLEV;
+  d->lu_levels[1] = PBM_FWD_NLEV;
+  d->lu_levels[2] = PBM_BWD_NLEV;
+  d->flops[0] = PBM_FLOPS_RES;
+  d->flops[1] = PBM_FLOPS_JAC;
+  d->flops[2] = PBM_FLOPS_FACTOR;
+  d->flops[3] = PBM_FLOPS_SOLVE;
+  d->flops[4] = PBM_FLOPS_EVENTS;
+  d->flops[5] = PBM_FLOPS_VARS;
+  strncpy(d->name, PBM_NAME, sizeof(d->name) - 1);
+  return 0;
+}
+
+// All pointers in L are device pointers on the current device. grid_out: teams launched.
+extern "C" int pbgpu_image_launch(const pbgpu_launch* L, void* stream, int* grid_out, char* err, size_t errlen) {
+  if (pb_configure(err, errlen)) return 1;
+  int grid = g_blocks_per_sm * g_num_sms;
+  if (grid > L->n_sys) grid = L->n_sys;
+  if (grid < 1) grid = 1;
+  pbgpu_solve_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*L);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    snprintf(err, errlen, "pbgpu_solve_kernel launch: %s", cudaGetErrorString(e));
+    return 1;
+  }
+  if (grid_out) *grid_out = grid;
+  return 0;
+}
+
+extern "C" int pbgpu_image_eval(const pbgpu_eval_launch* E, void* stream, char* err, size_t errlen) {
+  if (pb_configure(err, errlen)) return 1;
+  int grid = g_blocks_per_sm * g_num_sms;
+  if (grid > E->n_sys) grid = E->n_sys;
+  if (grid < 1) grid = 1;
+  pbgpu_eval_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*E);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    snprintf(err, errlen, "pbgpu_eval_kernel launch: %s", cudaGetErrorString(e));
+    return 1;
+  }
+  return 0;
+}

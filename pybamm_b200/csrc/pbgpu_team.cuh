@@ -1,0 +1,108 @@
+// pbgpu_team.cuh -- team (one warp or one CTA per system) primitives for sm_100a.
+//
+// A *team* of PB_TEAM_SIZE threads integrates one system; all per-system vectors live in the
+// team's shared memory.  The generated model code (pybamm_b200/codegen.py, CUDA dialect) and
+// the integrator (pbgpu_ida.cuh) are written against the macros below.
+//
+// PB_EMU: single-"thread" host build of the very same sources (TEAM = 1, barriers are no-ops).
+// It exists so that tests/ can exercise the device integrator's control flow on a CPU-only
+// machine; it is never compiled into the product libraries.
+#pragma once
+
+#ifdef PB_EMU
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#define PB_DEV
+#define PB_ALIGN16
+#define PB_TABLE
+#define PB_FN static inline
+#define PB_RESTRICT __restrict__
+#define PB_TEAM 1
+#define PB_TID 0
+#define PB_WARP 0
+#define PB_NWARPS 1
+#define PB_LANE 0
+#define PB_LANES 1
+#define PB_SYNC() ((void)0)
+#define PB_SYNCWARP() ((void)0)
+#define PB_LD(x) (x)
+#define PB_LDU(x) (x)
+#define PB_NAN NAN
+#define PB_INF INFINITY
+struct pb_team_ctx {
+  double* red;  // unused
+};
+PB_FN double pb_team_sum(pb_team_ctx&, double x) { return x; }
+PB_FN double pb_team_max(pb_team_ctx&, double x) { return x; }
+#else
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#ifndef PB_TEAM_SIZE
+#define PB_TEAM_SIZE 32
+#endif
+#define PB_DEV __device__ __forceinline__
+#define PB_ALIGN16 __align__(16)
+#define PB_TABLE __device__
+#define PB_FN static __device__ __noinline__
+#define PB_RESTRICT __restrict__
+#define PB_TEAM PB_TEAM_SIZE
+#define PB_TID ((int)threadIdx.x)
+#define PB_WARP ((int)(threadIdx.x >> 5))
+#define PB_NWARPS (PB_TEAM_SIZE / 32)
+#define PB_LANE ((int)(threadIdx.x & 31))
+#define PB_LANES 32
+#if PB_TEAM_SIZE == 32
+#define PB_SYNC() __syncwarp()
+#else
+#define PB_SYNC() __syncthreads()
+#endif
+#define PB_SYNCWARP() __syncwarp()
+#define PB_LD(x) __ldg(&(x))
+#define PB_LDU(x) __ldg(&(x))
+#define PB_NAN CUDART_NAN
+#define PB_INF CUDART_INF
+
+struct pb_team_ctx {
+  double* red;   // 2 * 32 doubles of shared memory for cross-warp reductions (double buffered)
+  int red_phase;
+};
+
+// Team-wide sum; every thread returns the bitwise-identical value (butterfly inside the warp,
+// fixed-order sum of the per-warp partials across warps).
+static __device__ __forceinline__ double pb_team_sum(pb_team_ctx& c, double x) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+#if PB_TEAM_SIZE > 32
+  double* buf = c.red + 32 * (c.red_phase & 1);
+  c.red_phase++;
+  if (PB_LANE == 0) buf[PB_WARP] = x;
+  __syncthreads();
+  x = buf[0];
+#pragma unroll
+  for (int w = 1; w < PB_NWARPS; w++) x += buf[w];
+#endif
+  return x;
+}
+static __device__ __forceinline__ double pb_team_max(pb_team_ctx& c, double x) {
+  // NaN-propagating max (a NaN anywhere must poison the result so that failures are seen)
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    double y = __shfl_xor_sync(0xffffffffu, x, o);
+    x = (x != x || y != y) ? CUDART_NAN : fmax(x, y);
+  }
+#if PB_TEAM_SIZE > 32
+  double* buf = c.red + 32 * (c.red_phase & 1);
+  c.red_phase++;
+  if (PB_LANE == 0) buf[PB_WARP] = x;
+  __syncthreads();
+  x = buf[0];
+#pragma unroll
+  for (int w = 1; w < PB_NWARPS; w++) {
+    double y = buf[w];
+    x = (x != x || y != y) ? CUDART_NAN : fmax(x, y);
+  }
+#endif
+  return x;
+}
+#endif

@@ -1,0 +1,346 @@
+"""Host front end of the B200 batched DAE solver (no pybamm import needed).
+
+``BatchedIDASolver`` mirrors the data contract of ``IDAKLUSolver._integrate`` /
+``IDAKLUSolverGroup.solve`` (packages/pybamm/src/pybamm/solvers/idaklu_solver.py:665-718,
+packages/pybammsolvers/src/pybammsolvers/idaklu_source/IDAKLUSolverGroup.cpp:6-170): one blocking
+call per batch, inputs ``(n_sys, n_p)`` ordered by sorted input name, results per system as
+``t (n_t,)``, ``y (n_t, n_ret)`` time-major, ``flag``, ``y_term``.  It reaches CUDA through the C ABI
+of ``include/pbgpu.h`` with ctypes.  There is no CPU fallback: constructing the solver without a
+usable GPU (or without the compiled libraries) raises ``SolverError``.
+
+``pybamm_b200.idaklu_solver.IDAKLUSolver`` wraps this class behind ``pybamm.BaseSolver`` where pybamm
+is importable.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import warnings
+
+import numpy as np
+
+from . import build
+from .bundle import ModelBundle
+from .host import ModelDesc, Options, Result, canonical_time_grids, default_options, OPTION_DEFAULTS
+
+IDA_ROOT_RETURN = 2
+
+# flag -> message table of the reference (idaklu_source/sundials_error_handler.hpp:11-61), the codes this path can return
+IDA_MESSAGES = {
+    -1: "IDA_TOO_MUCH_WORK: The solver took mxstep internal steps but could not reach tout.",
+    -2: "IDA_TOO_MUCH_ACC: The solver could not satisfy the accuracy demanded by the user for some internal step.",
+    -3: "IDA_ERR_FAIL: Error test failures occurred too many times during one internal time step or minimum step size was reached.",
+    -4: "IDA_CONV_FAIL: Convergence test failures occurred too many times during one internal time step or minimum step size was reached.",
+    -6: "IDA_LSETUP_FAIL: The linear solver's setup function failed in an unrecoverable manner.",
+    -22: "IDA_ILL_INPUT: One of the function inputs is illegal.",
+}
+
+STAT_NAMES = ("nsteps", "nrevals", "nlinsetups", "netfails", "nniters", "nncfails", "njevals", "nge")
+
+
+class SolverError(Exception):
+    """Same role as pybamm.SolverError (raised for argument errors and on_failure='error')."""
+
+
+def sundials_error_message(flag: int) -> str:
+    return IDA_MESSAGES.get(int(flag), f"IDA failure (flag: {int(flag)})")
+
+
+class Solution:
+    """Minimal stand-in for pybamm.Solution holding one system's result.
+
+    Field meaning follows the arguments ``_post_process_solution`` passes to ``pybamm.Solution``
+    (idaklu_solver.py:809-822): ``t``, ``y`` with shape (n_states, n_t) (the transpose view of the
+    time-major block), ``t_event``, ``y_event``, ``termination``.
+    """
+
+    def __init__(self, t, y_rows, inputs, flag, y_term, stats, variables, event_names, closest_event_idx):
+        self.t = t
+        self._rows = y_rows
+        self.all_inputs = [inputs]
+        self.flag = int(flag)
+        self.y_event = y_term
+        self.t_event = np.array([t[-1]]) if len(t) else np.array([])
+        self.stats = dict(zip(STAT_NAMES, (int(s) for s in stats))) if stats is not None else {}
+        self._variables = variables
+        self.closest_event_idx = closest_event_idx
+        if self.flag == IDA_ROOT_RETURN:
+            name = event_names[closest_event_idx] if closest_event_idx is not None else "?"
+            self.termination = f"event: {name}"
+        elif self.flag >= 0:
+            self.termination = "final time"
+        else:
+            self.termination = "failure"
+
+    @property
+    def y(self):
+        if self._variables is not None:
+            raise KeyError("full state was not stored (output_variables mode); use solution[name]")
+        return self._rows.T
+
+    def __getitem__(self, name):
+        if self._variables is None:
+            raise KeyError(f"variable '{name}' was not requested through output_variables")
+        sl = self._variables[name]
+        return self._rows[:, sl]
+
+
+def _pinned_empty(shape, dtype):
+    """Page-locked host array (through torch) so that H2D/D2H copies run at full PCIe speed."""
+    try:
+        import torch
+
+        if torch.cuda.is_available():
+            tdt = {np.float64: torch.float64, np.int32: torch.int32, np.int64: torch.int64}[np.dtype(dtype).type]
+            t = torch.empty(tuple(int(s) for s in shape), dtype=tdt, pin_memory=True)
+            return t.numpy(), t
+    except Exception:
+        pass
+    return np.empty(shape, dtype=dtype), None
+
+
+class _Lib:
+    _inst = None
+
+    @classmethod
+    def get(cls):
+        if cls._inst is None:
+            path = os.path.join(build.BUILD, "libpbgpu.so")
+            if not os.path.exists(path):
+                try:
+                    path = build.build_api()
+                except Exception as e:
+                    raise SolverError(f"libpbgpu.so is not built and cannot be built here: {e}") from None
+            try:
+                lib = C.CDLL(path)
+            except OSError as e:
+                raise SolverError(f"cannot load {path}: {e}") from None
+            lib.pbgpu_last_error.restype = C.c_char_p
+            vp = C.c_void_p
+            lib.pbgpu_model_load.argtypes = [C.c_char_p, C.POINTER(vp)]
+            lib.pbgpu_model_describe.argtypes = [vp, C.POINTER(ModelDesc)]
+            lib.pbgpu_model_unload.argtypes = [vp]
+            lib.pbgpu_solver_create.argtypes = [vp, vp, C.POINTER(Options), C.c_int, C.POINTER(vp)]
+            lib.pbgpu_solver_destroy.argtypes = [vp]
+            lib.pbgpu_result_capacity.argtypes = [C.c_int, C.c_int]
+            lib.pbgpu_solve.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int, vp, vp, C.c_int, C.POINTER(Result)]
+            lib.pbgpu_solve_device.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int, vp, vp, C.c_int,
+                                               C.POINTER(Result), vp, C.c_int]
+            lib.pbgpu_model_eval.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_double, C.c_double, vp, vp, C.c_int]
+            cls._inst = lib
+        return cls._inst
+
+
+def _err(lib):
+    return lib.pbgpu_last_error().decode(errors="replace")
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class BatchedIDASolver:
+    """Batched IDA-style BDF solver on one B200.
+
+    Parameters mirror ``pybamm.IDAKLUSolver`` (idaklu_solver.py:240-252): ``rtol``, ``atol`` (float or
+    (n_states,) array), ``options`` (same option names; options that select other linear solvers or
+    threading are accepted and ignored), ``output_variables`` (names compiled into the bundle),
+    ``on_failure`` in {"warn", "error", "ignore"}.
+    """
+
+    IGNORED_OPTIONS = {"print_stats", "compile", "jacobian", "preconditioner", "precon_half_bandwidth",
+                       "precon_half_bandwidth_keep", "num_threads", "num_solvers", "linear_solver",
+                       "linsol_max_iterations", "epsilon_linear_tolerance", "increment_factor",
+                       "silence_sundials_errors", "suppress_algebraic_error", "hermite_interpolation",
+                       "hermite_reduction_factor", "max_num_steps_ic", "max_num_jacobians_ic", "linesearch_off_ic",
+                       "init_all_y_ic", "newton_mode", "num_steps_no_progress", "t_no_progress", "dt_min"}
+
+    def __init__(self, model, rtol=1e-4, atol=1e-6, options=None, output_variables=None, device=0,
+                 on_failure="warn", image_path=None):
+        self.bundle: ModelBundle = model if isinstance(model, ModelBundle) else build.load_bundle(model)
+        self.rtol = float(rtol)
+        self.atol = atol
+        self.on_failure = on_failure or "warn"
+        if self.on_failure not in ("warn", "error", "ignore"):
+            raise SolverError("on_failure must be 'warn', 'error' or 'ignore'")
+        self.output_variables = list(output_variables or [])
+        for v in self.output_variables:
+            if v not in self.bundle.variables:
+                raise SolverError(f"output variable '{v}' is not compiled into model bundle '{self.bundle.name}'")
+        options = dict(options or {})
+        unknown = [k for k in options if k not in OPTION_DEFAULTS and k not in self.IGNORED_OPTIONS]
+        if unknown:
+            raise SolverError(f"unknown IDAKLU option(s): {unknown}")
+        if options.get("num_solvers", 1) > options.get("num_threads", options.get("num_solvers", 1)):
+            raise SolverError("Number of solvers must be less than or equal to the number of threads")
+        self.options = options
+        self.device = int(device)
+        self._image_path = image_path
+        self._lib = None
+        self._model = None
+        self._solver = None
+        self.desc = None
+        self.last_kernel_ms = None
+        self.last_total_ms = None
+
+    # -- native handles ---------------------------------------------------------------------
+    def _ensure(self):
+        if self._solver is not None:
+            return
+        lib = _Lib.get()
+        path = self._image_path or os.path.join(build.BUILD, f"pbgpu_model_{self.bundle.name}.so")
+        if not os.path.exists(path):
+            try:
+                path = build.build_model(self.bundle)
+            except Exception as e:
+                raise SolverError(f"model image for '{self.bundle.name}' is not built and cannot be built here: {e}") from None
+        mh = C.c_void_p()
+        if lib.pbgpu_model_load(path.encode(), C.byref(mh)):
+            raise SolverError(_err(lib))
+        desc = ModelDesc()
+        lib.pbgpu_model_describe(mh, C.byref(desc))
+        if desc.n_states != self.bundle.n_states or desc.n_inputs != self.bundle.n_inputs:
+            raise SolverError("model image does not match the bundle (rebuild with pybamm_b200.build.build_model)")
+        atol = np.ascontiguousarray(np.broadcast_to(np.asarray(self.atol, dtype=np.float64), (desc.n_states,)).copy())
+        opt = default_options(rtol=self.rtol, **self.options)
+        sh = C.c_void_p()
+        if lib.pbgpu_solver_create(mh, _ptr(atol), C.byref(opt), self.device, C.byref(sh)):
+            raise SolverError(_err(lib))
+        self._lib, self._model, self._solver, self.desc = lib, mh, sh, desc
+
+    def close(self):
+        if self._solver is not None:
+            self._lib.pbgpu_solver_destroy(self._solver)
+            self._lib.pbgpu_model_unload(self._model)
+            self._solver = self._model = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # pickling drops native state and rebuilds lazily (idaklu_solver.py:645-659)
+    def __getstate__(self):
+        d = dict(self.__dict__)
+        d["_lib"] = d["_model"] = d["_solver"] = d["desc"] = None
+        return d
+
+    # -- batch solve --------------------------------------------------------------------------
+    def solve_arrays(self, t_eval, inputs, t_interp=None, y0=None, output_mode=None, want_stats=True):
+        """Array-level entry: returns dict(t, y, n_t, flag, y_term, stats) of padded arrays."""
+        self._ensure()
+        lib, D = self._lib, self.desc
+        try:
+            t_eval, t_interp = canonical_time_grids(t_eval, t_interp)
+        except ValueError as e:
+            raise SolverError(str(e)) from None
+        inputs = np.asarray(inputs, dtype=np.float64)
+        if inputs.ndim != 2:
+            raise SolverError(f"inputs has wrong number of dimensions. Expected 2 but got {inputs.ndim}")
+        n_sys = inputs.shape[0]
+        if inputs.shape[1] != D.n_inputs:
+            raise SolverError(f"inputs has wrong number of cols. Expected {D.n_inputs} but got {inputs.shape[1]}")
+        inputs = np.ascontiguousarray(inputs)
+        if y0 is not None:
+            y0 = np.asarray(y0, dtype=np.float64)
+            if y0.ndim != 2:
+                raise SolverError(f"y0 has wrong number of dimensions. Expected 2 but got {y0.ndim}")
+            if y0.shape[1] != D.n_states:
+                raise SolverError(f"y0 has wrong number of cols. Expected {D.n_states} but got {y0.shape[1]}")
+            if y0.shape[0] != n_sys:
+                raise SolverError(f"y0 has wrong number of rows. Expected {n_sys} but got {y0.shape[0]}")
+            y0 = np.ascontiguousarray(y0)
+        if output_mode is None:
+            output_mode = 1 if self.output_variables else 0
+        n_ret = D.n_vars if output_mode == 1 else D.n_states
+        if len(t_interp):
+            n_max = lib.pbgpu_result_capacity(len(t_eval), len(t_interp))
+        else:
+            n_max = int(self.options.get("max_saved_steps", 4096))
+        t_out, k1 = _pinned_empty((n_sys, n_max), np.float64)
+        y_out, k2 = _pinned_empty((n_sys, n_max, n_ret), np.float64)
+        n_t = np.zeros(n_sys, np.int32)
+        flag = np.zeros(n_sys, np.int32)
+        y_term = np.zeros((n_sys, D.n_states))
+        stats = np.zeros((n_sys, 8), np.int64) if want_stats else None
+        res = Result()
+        res.n_max, res.n_ret = n_max, n_ret
+        res.t, res.y, res.n_t, res.flag = _ptr(t_out), _ptr(y_out), _ptr(n_t), _ptr(flag)
+        res.y_term, res.stats = _ptr(y_term), _ptr(stats)
+        rc = lib.pbgpu_solve(self._solver, n_sys, _ptr(t_eval), len(t_eval), _ptr(t_interp) if len(t_interp) else None,
+                             len(t_interp), _ptr(y0), _ptr(inputs), output_mode, C.byref(res))
+        if rc:
+            raise SolverError(_err(lib))
+        self.last_kernel_ms, self.last_total_ms = float(res.kernel_ms), float(res.total_ms)
+        return dict(t=t_out, y=y_out, n_t=n_t, flag=flag, y_term=y_term, stats=stats, n_max=n_max, _keep=(k1, k2))
+
+    def solve(self, t_eval, inputs=None, t_interp=None, y0=None):
+        """solve(t_eval, inputs=[{...}, ...]) -> list[Solution] (a single Solution for a single dict)."""
+        single = isinstance(inputs, dict) or inputs is None
+        inputs_list = [inputs or {}] if single else list(inputs)
+        try:
+            p = self.bundle.flatten_inputs(inputs_list)
+        except ValueError as e:
+            raise SolverError(str(e)) from None
+        r = self.solve_arrays(t_eval, p, t_interp=t_interp, y0=y0)
+        variables = None
+        if self.output_variables:
+            variables, off = {}, 0
+            for name in self.bundle.variables:
+                n = len(self.bundle.variables[name])
+                variables[name] = slice(off, off + n)
+                off += n
+        sols = []
+        ev_vals = None
+        if self.bundle.n_events and np.any(r["flag"] == IDA_ROOT_RETURN):
+            # which event fired: argmin |g| at the final state (idaklu_solver.py:826-834)
+            t_end = np.array([r["t"][i, max(r["n_t"][i] - 1, 0)] for i in range(len(inputs_list))])
+            ev_vals = np.abs(self.eval("events", r["y_term"], p, t_end))
+        for i, d in enumerate(inputs_list):
+            n = int(r["n_t"][i])
+            flag = int(r["flag"][i])
+            if flag < 0:
+                msg = sundials_error_message(flag)
+                if self.on_failure == "error":
+                    raise SolverError(msg)
+                if self.on_failure == "warn":
+                    warnings.warn(msg + ", returning a partial solution.", stacklevel=2)
+            idx = int(np.nanargmin(ev_vals[i])) if (flag == IDA_ROOT_RETURN and ev_vals is not None) else None
+            if n == 1 and flag == IDA_ROOT_RETURN:
+                names = [self.bundle.event_names[k] for k in range(self.bundle.n_events)]
+                raise SolverError(f"Events {names} are non-positive at initial conditions")
+            sols.append(Solution(r["t"][i, :n], r["y"][i, :n], d, flag, r["y_term"][i],
+                                 r["stats"][i] if r["stats"] is not None else None, variables,
+                                 self.bundle.event_names, idx))
+        return sols[0] if single else sols
+
+    # -- device evaluation of the generated functions (parity tests, event identification) ---------
+    def eval(self, which, y, p, t=0.0, cj=0.0, y2=None):
+        self._ensure()
+        D = self.desc
+        idx = {"res": 0, "jac": 1, "events": 2, "ic": 3, "vars": 4, "solve": 5}[which]
+        out_len = {"res": D.n_states, "jac": D.nnz_jac, "events": max(D.n_events, 1), "ic": D.n_states,
+                   "vars": max(D.n_vars, 1), "solve": D.n_states}[which]
+        p = np.ascontiguousarray(np.atleast_2d(np.asarray(p, dtype=np.float64)))
+        n_sys = p.shape[0]
+        if y is not None:
+            y = np.ascontiguousarray(np.atleast_2d(np.asarray(y, dtype=np.float64)))
+        if y2 is not None:
+            y2 = np.ascontiguousarray(np.atleast_2d(np.asarray(y2, dtype=np.float64)))
+        t_arr = np.broadcast_to(np.asarray(t, dtype=np.float64), (n_sys,))
+        out = np.zeros((n_sys, out_len))
+        if np.all(t_arr == t_arr[0]):
+            if self._lib.pbgpu_model_eval(self._solver, idx, n_sys, _ptr(y), _ptr(p), float(t_arr[0]), float(cj),
+                                          _ptr(y2), _ptr(out), out_len):
+                raise SolverError(_err(self._lib))
+        else:
+            for i in range(n_sys):
+                oi = np.zeros((1, out_len))
+                if self._lib.pbgpu_model_eval(self._solver, idx, 1, _ptr(np.ascontiguousarray(y[i:i + 1])) if y is not None else None,
+                                              _ptr(np.ascontiguousarray(p[i:i + 1])), float(t_arr[i]), float(cj),
+                                              _ptr(np.ascontiguousarray(y2[i:i + 1])) if y2 is not None else None,
+                                              _ptr(oi), out_len):
+                    raise SolverError(_err(self._lib))
+                out[i] = oi[0]
+        return out

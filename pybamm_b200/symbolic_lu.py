@@ -34,17 +34,18 @@ import scipy.sparse.linalg as spla
 
 @dataclass
 class JDS:
-    """Jagged-diagonal task tables for a sequence of levels."""
+    """Level-scheduled task tables, operands in ELL layout per level.
+
+    Level l has nt tasks and maxlen operand rows; operand p of task q sits at op_base + p*nt + q, so
+    lanes read consecutive entries and no address depends on another table look-up.  Short tasks are
+    padded with a (zero slot, zero slot) operand pair."""
     n_levels: int
-    lev_task: np.ndarray     # (n_levels+1,) task range per level
-    lev_row: np.ndarray      # (n_levels+1,) jagged-row range per level
-    row_start: np.ndarray    # (n_rows,) offset into the operand arrays
-    row_cnt: np.ndarray      # (n_rows,) number of tasks that have this operand
+    lev_meta: np.ndarray     # (n_levels, 4) int32: task_base, nt, op_base, maxlen | (sync << 16)
     op_a: np.ndarray         # operand A (lu slot)
     op_b: np.ndarray         # operand B (lu slot for factor, w index for solves)
     task_out: np.ndarray     # per task: output slot / row
-    task_aux: np.ndarray     # per task: aux (factor: diag slot or code; solve: diag slot / gather index)
-    sync: np.ndarray         # (n_levels,) 1 = team barrier after the level, 0 = warp barrier suffices
+    task_aux: np.ndarray     # per task: aux (factor: diag slot or code; fwd: gather index; bwd: scatter index)
+    n_real_ops: int
 
     @property
     def n_tasks(self):
@@ -52,7 +53,11 @@ class JDS:
 
     @property
     def n_ops(self):
-        return len(self.op_a)
+        return self.n_real_ops
+
+    @property
+    def sync(self):
+        return (self.lev_meta[:, 3] >> 16) & 1
 
 
 @dataclass
@@ -73,7 +78,7 @@ class SymbolicLU:
 
     def summary(self):
         return (f"n={self.n} nnz_lu={self.nnz_lu} ordering={self.ordering} "
-                f"factor: {self.factor.n_levels} levels/{self.factor.n_tasks} tasks/{self.factor.n_ops} ops "
+                f"factor: {self.factor.n_levels} levels/{self.factor.n_tasks} tasks/{self.factor.n_ops} ops ({len(self.factor.op_a)} padded) "
                 f"(team syncs {int(self.factor.sync.sum())}); fwd {self.fwd.n_levels} lv, bwd {self.bwd.n_levels} lv "
                 f"(team syncs {int(self.fwd.sync.sum())}+{int(self.bwd.sync.sum())})")
 
@@ -197,36 +202,34 @@ def _symbolic_fill(B: sp.csr_matrix):
     return Lrows, Urows
 
 
-def _jds(levels_tasks, n_total_levels=None, warp=32):
+def _jds(levels_tasks, pad_a, pad_b, warp=32):
     """levels_tasks: list (per level) of tasks (out, aux, [(a, b), ...])."""
-    lev_task = [0]
-    lev_row = [0]
-    row_start, row_cnt = [], []
+    meta = []
     op_a, op_b = [], []
     task_out, task_aux = [], []
-    sync = []
+    n_real = 0
     for li, tasks in enumerate(levels_tasks):
         tasks = sorted(tasks, key=lambda t: -len(t[2]))
+        nt = len(tasks)
+        maxlen = len(tasks[0][2]) if tasks else 0
+        nxt = len(levels_tasks[li + 1]) if li + 1 < len(levels_tasks) else 10 ** 9
+        sync = 0 if (nt <= warp and nxt <= warp) else 1
+        meta.append((len(task_out), nt, len(op_a), maxlen | (sync << 16)))
         for t in tasks:
             task_out.append(t[0])
             task_aux.append(t[1])
-        maxlen = len(tasks[0][2]) if tasks else 0
+            n_real += len(t[2])
         for p in range(maxlen):
-            cnt = sum(1 for t in tasks if len(t[2]) > p)
-            row_start.append(len(op_a))
-            row_cnt.append(cnt)
-            for t in tasks[:cnt]:
-                op_a.append(t[2][p][0])
-                op_b.append(t[2][p][1])
-        lev_task.append(len(task_out))
-        lev_row.append(len(row_start))
-        nxt = len(levels_tasks[li + 1]) if li + 1 < len(levels_tasks) else 10 ** 9
-        sync.append(0 if (len(tasks) <= warp and nxt <= warp) else 1)
+            for t in tasks:
+                if len(t[2]) > p:
+                    op_a.append(t[2][p][0])
+                    op_b.append(t[2][p][1])
+                else:
+                    op_a.append(pad_a)
+                    op_b.append(pad_b)
     i32 = np.int32
-    return JDS(len(levels_tasks), np.asarray(lev_task, i32), np.asarray(lev_row, i32),
-               np.asarray(row_start, i32), np.asarray(row_cnt, i32), np.asarray(op_a, i32),
-               np.asarray(op_b, i32), np.asarray(task_out, i32), np.asarray(task_aux, i32),
-               np.asarray(sync, np.uint8))
+    return JDS(len(levels_tasks), np.asarray(meta, i32).reshape(-1, 4), np.asarray(op_a, i32), np.asarray(op_b, i32),
+               np.asarray(task_out, i32), np.asarray(task_aux, i32), n_real)
 
 
 AUX_U = 0xFFFF      # factor task writes an off-diagonal U entry
@@ -274,8 +277,10 @@ def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01) -> 
     for name, perm_r, perm_c in candidates:
         s = _build(n, rows, cols, perm_r, perm_c, name)
         # cost proxy: team barriers dominate the numeric phase
-        score = (s.factor.sync.sum() + 4 * (s.fwd.sync.sum() + s.bwd.sync.sum())) * 60 \
-            + (s.factor.n_levels + 4 * (s.fwd.n_levels + s.bwd.n_levels)) * 40 + s.flops_factor / 8 + s.flops_solve / 2
+        # cost proxy (cycles per step): ~10 triangular solves per factorisation; a level costs a barrier plus a
+        # shared-memory round trip, the values and tables must stay on chip (nnz_lu weighs heavily)
+        score = (s.factor.n_levels + 10 * (s.fwd.n_levels + s.bwd.n_levels)) * 80 \
+            + (len(s.factor.op_a) + 10 * (len(s.fwd.op_a) + len(s.bwd.op_a))) / 4 + 40.0 * s.nnz_lu
         ok = all(_validate(s, rows, cols, np.asarray(v, float)) < 1e-6 for v in samples)
         if not ok:
             continue
@@ -339,7 +344,7 @@ def _build(n, rows, cols, perm_r, perm_c, name) -> SymbolicLU:
             tasks_by_level.setdefault(lv, []).append((slot_of[(i, j)], aux, pairs))
             flops += 2 * len(pairs) + 1
     nlev = max(tasks_by_level) + 1
-    factor = _jds([tasks_by_level.get(l, []) for l in range(nlev)])
+    factor = _jds([tasks_by_level.get(l, []) for l in range(nlev)], nnz_lu, nnz_lu)
 
     # forward solve: w[i] = b[perm_r[i]] - sum_k L[i,k] w[k]
     rl = np.zeros(n, np.int64)
@@ -354,7 +359,7 @@ def _build(n, rows, cols, perm_r, perm_c, name) -> SymbolicLU:
         rl[i] = lv
         fl.setdefault(lv, []).append((i, int(perm_r[i]), ops))
         sflops += 2 * len(ops)
-    fwd = _jds([fl.get(l, []) for l in range(max(fl) + 1)])
+    fwd = _jds([fl.get(l, []) for l in range(max(fl) + 1)], nnz_lu, n)
     # backward solve: w[i] = (w[i] - sum_{j>i} U[i,j] w[j]) * lu[diag_i]; x[perm_c[i]] = w[i]
     rb = np.zeros(n, np.int64)
     blv = {}
@@ -369,7 +374,7 @@ def _build(n, rows, cols, perm_r, perm_c, name) -> SymbolicLU:
         rb[i] = lv
         blv.setdefault(lv, []).append((i, int(perm_c[i]), ops))
         sflops += 2 * len(ops) + 1
-    bwd = _jds([blv.get(l, []) for l in range(max(blv) + 1)])
+    bwd = _jds([blv.get(l, []) for l in range(max(blv) + 1)], nnz_lu, n)
     return SymbolicLU(n, nnz_lu, np.asarray(perm_r), np.asarray(perm_c), slot_of, a_slot, diag_slot,
                       factor, fwd, bwd, flops, sflops, name)
 
@@ -378,19 +383,19 @@ def _build(n, rows, cols, perm_r, perm_c, name) -> SymbolicLU:
 # numpy emulation of the numeric phase (validation of tables; tests)
 # ---------------------------------------------------------------------------
 def numeric_factor(s: SymbolicLU, a_vals):
-    lu = np.zeros(s.nnz_lu)
+    """lu has nnz_lu + 1 entries: the last one is the constant-zero padding slot."""
+    lu = np.zeros(s.nnz_lu + 1)
     np.add.at(lu, s.a_slot, a_vals)
     f = s.factor
     for lv in range(f.n_levels):
-        t0, t1 = f.lev_task[lv], f.lev_task[lv + 1]
-        nt = t1 - t0
-        acc = lu[f.task_out[t0:t1]].copy()
-        for r in range(f.lev_row[lv], f.lev_row[lv + 1]):
-            c = f.row_cnt[r]
-            st = f.row_start[r]
-            acc[:c] -= lu[f.op_a[st:st + c]] * lu[f.op_b[st:st + c]]
-        aux = f.task_aux[t0:t1]
-        out = f.task_out[t0:t1]
+        t0, nt, ob, ml = (int(x) for x in f.lev_meta[lv])
+        ml &= 0xFFFF
+        out = f.task_out[t0:t0 + nt]
+        aux = f.task_aux[t0:t0 + nt]
+        acc = lu[out].copy()
+        for p in range(ml):
+            sl = slice(ob + p * nt, ob + (p + 1) * nt)
+            acc -= lu[f.op_a[sl]] * lu[f.op_b[sl]]
         for q in range(nt):
             if aux[q] == AUX_U:
                 lu[out[q]] = acc[q]
@@ -402,16 +407,16 @@ def numeric_factor(s: SymbolicLU, a_vals):
 
 
 def numeric_solve(s: SymbolicLU, lu, b):
-    w = np.zeros(s.n)
+    w = np.zeros(s.n + 1)
     for jds, back in ((s.fwd, False), (s.bwd, True)):
         for lv in range(jds.n_levels):
-            t0, t1 = jds.lev_task[lv], jds.lev_task[lv + 1]
-            rows_ = jds.task_out[t0:t1]
-            acc = w[rows_].copy() if back else b[jds.task_aux[t0:t1]].copy()
-            for r in range(jds.lev_row[lv], jds.lev_row[lv + 1]):
-                c = jds.row_cnt[r]
-                st = jds.row_start[r]
-                acc[:c] -= lu[jds.op_a[st:st + c]] * w[jds.op_b[st:st + c]]
+            t0, nt, ob, ml = (int(x) for x in jds.lev_meta[lv])
+            ml &= 0xFFFF
+            rows_ = jds.task_out[t0:t0 + nt]
+            acc = w[rows_].copy() if back else b[jds.task_aux[t0:t0 + nt]].copy()
+            for p in range(ml):
+                sl = slice(ob + p * nt, ob + (p + 1) * nt)
+                acc -= lu[jds.op_a[sl]] * w[jds.op_b[sl]]
             if back:
                 acc *= lu[s.diag_slot[rows_]]
             w[rows_] = acc
