@@ -1,0 +1,57 @@
+"""Batch sharding across GPUs: systems are independent, so the N_sys rows of
+``inputs`` are split across devices / ranks with no collective inside the integration.
+
+The reference splits the batch into contiguous static chunks, one per OpenMP solver, and solves the
+remainder serially (idaklu_source/IDAKLUSolverGroup.cpp:99-160); step counts vary several-fold
+across a C-rate sweep, so contiguous chunks load-balance badly.  Here rows are dealt round-robin
+after sorting by a cost proxy (snake order), and every shard keeps its rows in ascending original
+order so that gathers are monotone copies.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def cost_proxy(inputs: np.ndarray, input_names=None) -> np.ndarray:
+    """Expected work per system.  Lower |current| -> longer discharge -> more steps; falls back to
+    uniform cost when the model has no current input."""
+    inputs = np.asarray(inputs, dtype=np.float64)
+    n = inputs.shape[0]
+    if input_names is not None and "Current function [A]" in input_names and inputs.shape[1]:
+        cur = np.abs(inputs[:, list(input_names).index("Current function [A]")])
+        with np.errstate(divide="ignore"):
+            c = 1.0 / np.maximum(cur, 1e-300)
+        return np.where(np.isfinite(c), c, 0.0)
+    return np.ones(n)
+
+
+def partition(n_sys: int, n_shards: int, cost=None):
+    """Return ``n_shards`` sorted index arrays covering range(n_sys) exactly once.
+
+    Sizes differ by at most one.  With ``cost`` the rows are dealt in snake order by descending cost
+    (so that every shard gets a similar cost mix); without it the deal is plain round-robin."""
+    if n_shards < 1:
+        raise ValueError("n_shards must be positive")
+    if cost is None:
+        order = np.arange(n_sys)
+    else:
+        cost = np.asarray(cost, dtype=np.float64).reshape(-1)
+        if len(cost) != n_sys:
+            raise ValueError("cost has wrong length")
+        order = np.argsort(-cost, kind="stable")
+    shards = [[] for _ in range(n_shards)]
+    for k, idx in enumerate(order):
+        r, c = divmod(k, n_shards)
+        s = c if (r % 2 == 0) else n_shards - 1 - c
+        shards[s].append(int(idx))
+    return [np.sort(np.asarray(s, dtype=np.int64)) for s in shards]
+
+
+def gather_rows(parts, shards, n_sys):
+    """Inverse of partition for per-system arrays: parts[k] has the rows of shards[k]."""
+    first = next(p for p in parts if p is not None and len(p))
+    out = np.empty((n_sys,) + first.shape[1:], dtype=first.dtype)
+    for p, idx in zip(parts, shards):
+        if len(idx):
+            out[idx] = p
+    return out

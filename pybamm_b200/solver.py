@@ -156,7 +156,7 @@ class BatchedIDASolver:
                        "init_all_y_ic", "newton_mode", "num_steps_no_progress", "t_no_progress", "dt_min"}
 
     def __init__(self, model, rtol=1e-4, atol=1e-6, options=None, output_variables=None, device=0,
-                 on_failure="warn", image_path=None):
+                 on_failure="warn", image_path=None, devices=None, reuse_buffers=False):
         self.bundle: ModelBundle = model if isinstance(model, ModelBundle) else build.load_bundle(model)
         self.rtol = float(rtol)
         self.atol = atol
@@ -174,11 +174,18 @@ class BatchedIDASolver:
         if options.get("num_solvers", 1) > options.get("num_threads", options.get("num_solvers", 1)):
             raise SolverError("Number of solvers must be less than or equal to the number of threads")
         self.options = options
-        self.device = int(device)
+        # devices: CUDA ordinals the batch is sharded over inside this process (one solver handle and one host
+        # thread per device, no collective: SURVEY.md section 8e).  Default: the single ordinal ``device``.
+        self.devices = [int(d) for d in devices] if devices is not None else [int(device)]
+        if not self.devices:
+            raise SolverError("devices must name at least one CUDA ordinal")
+        self.device = self.devices[0]
+        self.reuse_buffers = bool(reuse_buffers)
         self._image_path = image_path
         self._lib = None
         self._model = None
         self._solver = None
+        self._solvers = []
         self.desc = None
         self.last_kernel_ms = None
         self.last_total_ms = None
@@ -203,16 +210,24 @@ class BatchedIDASolver:
             raise SolverError("model image does not match the bundle (rebuild with pybamm_b200.build.build_model)")
         atol = np.ascontiguousarray(np.broadcast_to(np.asarray(self.atol, dtype=np.float64), (desc.n_states,)).copy())
         opt = default_options(rtol=self.rtol, **self.options)
-        sh = C.c_void_p()
-        if lib.pbgpu_solver_create(mh, _ptr(atol), C.byref(opt), self.device, C.byref(sh)):
-            raise SolverError(_err(lib))
-        self._lib, self._model, self._solver, self.desc = lib, mh, sh, desc
+        handles = []
+        for dev in self.devices:
+            sh = C.c_void_p()
+            if lib.pbgpu_solver_create(mh, _ptr(atol), C.byref(opt), dev, C.byref(sh)):
+                msg = _err(lib)
+                for h in handles:
+                    lib.pbgpu_solver_destroy(h)
+                raise SolverError(msg)
+            handles.append(sh)
+        self._lib, self._model, self._solver, self._solvers, self.desc = lib, mh, handles[0], handles, desc
 
     def close(self):
         if self._solver is not None:
-            self._lib.pbgpu_solver_destroy(self._solver)
+            for h in self._solvers:
+                self._lib.pbgpu_solver_destroy(h)
             self._lib.pbgpu_model_unload(self._model)
             self._solver = self._model = None
+            self._solvers = []
 
     def __del__(self):
         try:
@@ -224,6 +239,8 @@ class BatchedIDASolver:
     def __getstate__(self):
         d = dict(self.__dict__)
         d["_lib"] = d["_model"] = d["_solver"] = d["desc"] = None
+        d["_solvers"] = []
+        d["_pinned"] = {}
         return d
 
     # -- batch solve --------------------------------------------------------------------------
@@ -258,8 +275,57 @@ class BatchedIDASolver:
             n_max = lib.pbgpu_result_capacity(len(t_eval), len(t_interp))
         else:
             n_max = int(self.options.get("max_saved_steps", 4096))
-        t_out, k1 = _pinned_empty((n_sys, n_max), np.float64)
-        y_out, k2 = _pinned_empty((n_sys, n_max, n_ret), np.float64)
+        if len(self._solvers) == 1 or n_sys < 2 * len(self._solvers):
+            r = self._solve_shard(0, t_eval, t_interp, inputs, y0, output_mode, n_ret, n_max, want_stats)
+            self.last_kernel_ms, self.last_total_ms = r.pop("kernel_ms"), r.pop("total_ms")
+            return r
+        # shard over the devices: one host thread per device (ctypes releases the GIL during pbgpu_solve)
+        import threading
+
+        from .shard import cost_proxy, gather_rows, partition
+
+        shards = partition(n_sys, len(self._solvers), cost_proxy(inputs, self.bundle.input_names))
+        parts, errors = [None] * len(shards), []
+
+        def work(k):
+            try:
+                idx = shards[k]
+                parts[k] = self._solve_shard(k, t_eval, t_interp, np.ascontiguousarray(inputs[idx]),
+                                             None if y0 is None else np.ascontiguousarray(y0[idx]), output_mode, n_ret,
+                                             n_max, want_stats)
+            except Exception as e:  # re-raised on the calling thread
+                errors.append(e)
+
+        threads = [threading.Thread(target=work, args=(k,)) for k in range(len(shards))]
+        for th in threads:
+            th.start()
+        for th in threads:
+            th.join()
+        if errors:
+            raise errors[0]
+        self.last_kernel_ms = max(p_["kernel_ms"] for p_ in parts)
+        self.last_total_ms = max(p_["total_ms"] for p_ in parts)
+        out = {k: gather_rows([p_[k] for p_ in parts], shards, n_sys) for k in ("t", "y", "n_t", "flag", "y_term")}
+        out["stats"] = gather_rows([p_["stats"] for p_ in parts], shards, n_sys) if want_stats else None
+        out["n_max"] = n_max
+        out["_keep"] = None
+        return out
+
+    def _solve_shard(self, k, t_eval, t_interp, inputs, y0, output_mode, n_ret, n_max, want_stats):
+        """One pbgpu_solve call on device slot k with host buffers (pinned result block, reused across calls)."""
+        lib, D = self._lib, self.desc
+        n_sys = inputs.shape[0]
+        if self.reuse_buffers:
+            # the returned arrays alias this cache: they are valid until the next solve on this solver
+            key = (k, n_sys, n_max, n_ret)
+            cache = self.__dict__.setdefault("_pinned", {})
+            if key not in cache:
+                for old in [q for q in cache if q[0] == k]:
+                    del cache[old]
+                cache[key] = (_pinned_empty((n_sys, n_max), np.float64), _pinned_empty((n_sys, n_max, n_ret), np.float64))
+            (t_out, k1), (y_out, k2) = cache[key]
+        else:
+            (t_out, k1), (y_out, k2) = _pinned_empty((n_sys, n_max), np.float64), _pinned_empty((n_sys, n_max, n_ret), np.float64)
         n_t = np.zeros(n_sys, np.int32)
         flag = np.zeros(n_sys, np.int32)
         y_term = np.zeros((n_sys, D.n_states))
@@ -268,12 +334,12 @@ class BatchedIDASolver:
         res.n_max, res.n_ret = n_max, n_ret
         res.t, res.y, res.n_t, res.flag = _ptr(t_out), _ptr(y_out), _ptr(n_t), _ptr(flag)
         res.y_term, res.stats = _ptr(y_term), _ptr(stats)
-        rc = lib.pbgpu_solve(self._solver, n_sys, _ptr(t_eval), len(t_eval), _ptr(t_interp) if len(t_interp) else None,
+        rc = lib.pbgpu_solve(self._solvers[k], n_sys, _ptr(t_eval), len(t_eval), _ptr(t_interp) if len(t_interp) else None,
                              len(t_interp), _ptr(y0), _ptr(inputs), output_mode, C.byref(res))
         if rc:
             raise SolverError(_err(lib))
-        self.last_kernel_ms, self.last_total_ms = float(res.kernel_ms), float(res.total_ms)
-        return dict(t=t_out, y=y_out, n_t=n_t, flag=flag, y_term=y_term, stats=stats, n_max=n_max, _keep=(k1, k2))
+        return dict(t=t_out, y=y_out, n_t=n_t, flag=flag, y_term=y_term, stats=stats, n_max=n_max, _keep=(k1, k2),
+                    kernel_ms=float(res.kernel_ms), total_ms=float(res.total_ms))
 
     def solve(self, t_eval, inputs=None, t_interp=None, y0=None):
         """solve(t_eval, inputs=[{...}, ...]) -> list[Solution] (a single Solution for a single dict)."""
