@@ -140,3 +140,21 @@ def build_api(force=False):
     with open(stamp, "w") as f:
         f.write(dig)
     return out
+
+
+def build_peak(force=False):
+    """Compile the FP64 peak microbenchmark used by bench.py's roofline (include/pbgpu_peak.h)."""
+    os.makedirs(BUILD, exist_ok=True)
+    out = os.path.join(BUILD, "libpbgpu_peak.so")
+    src = os.path.join(CSRC, "pbgpu_peak.cu")
+    inc = os.path.join(ROOT, "include")
+    dig = _src_digest([src, os.path.join(inc, "pbgpu_peak.h")])
+    stamp = out + ".stamp"
+    if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:
+        return out
+    cmd = [NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "--cudart", "shared", "-Xcompiler", "-fPIC",
+           "--shared", f"-I{inc}", src, "-o", out]
+    subprocess.run(cmd, check=True)
+    with open(stamp, "w") as f:
+        f.write(dig)
+    return out
