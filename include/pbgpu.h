@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define PBGPU_ABI_VERSION 1
+#define PBGPU_ABI_VERSION 2
 
 typedef struct pbgpu_model_s* pbgpu_model_t;
 typedef struct pbgpu_solver_s* pbgpu_solver_t;
@@ -55,6 +55,7 @@ typedef struct {
   int n_tmp;          /* scratch temporaries of the generated functions */
   int lu_levels[3];   /* dependency levels: factor, forward, backward */
   long long flops[6]; /* static work model: res, jac, factor, solve, events, vars (DFMA-equivalents / flops) */
+  long long scratch_doubles_per_team; /* global scratch a team needs (streamed vectors of large models), 0 if none */
   char name[64];
 } pbgpu_model_desc;
 
@@ -150,6 +151,7 @@ typedef struct {
   double* y_term;
   long long* stats;
   unsigned int* queue;
+  double* scratch;      /* [teams][scratch_doubles_per_team] device memory owned by the solver handle, may be NULL if 0 */
   pbgpu_options opt;
 } pbgpu_launch;
 
@@ -160,6 +162,7 @@ typedef struct {
   const double* y2;
   double t, cj;
   double* out;
+  double* scratch;      /* as in pbgpu_launch */
 } pbgpu_eval_launch;
 
 #ifdef __cplusplus

@@ -82,25 +82,26 @@ def build_oracle(bundle: ModelBundle, force=False):
     return out
 
 
-def build_model(bundle: ModelBundle, force=False, team=None, verbose=False):
+def build_model(bundle: ModelBundle, force=False, team=None, verbose=False, profile=False, tag=""):
     """Generate + nvcc-compile the sm_100a solver image of a bundle. Returns the .so path."""
     os.makedirs(BUILD, exist_ok=True)
     header, info = generate(bundle, "cuda", BUILD)
-    out = os.path.join(BUILD, f"pbgpu_model_{bundle.name}.so")
+    out = os.path.join(BUILD, f"pbgpu_model_{bundle.name}{('_prof' + (str(int(profile)) if int(profile) > 1 else '')) if profile else ''}{tag}.so")
     kernel_srcs = [os.path.join(CSRC, f) for f in ("pbgpu_model.cu", "pbgpu_ida.cuh", "pbgpu_team.cuh")]
     inc = os.path.join(ROOT, "include")
     srcs = kernel_srcs + [header, os.path.join(inc, "pbgpu.h")]
     if team is None:
         team = default_team(bundle)
-    dig = _src_digest(srcs) + f"-t{team}-" + hashlib.sha256(" ".join(NVCC_FLAGS).encode()).hexdigest()[:8]
+    gvec = 1 if bundle.n_states > 256 else 0   # streamed vectors in global scratch for large models (pbgpu_ida.cuh)
+    dig = _src_digest(srcs) + f"-t{team}-g{gvec}-p{int(profile)}-" + hashlib.sha256(" ".join(NVCC_FLAGS).encode()).hexdigest()[:8]
     stamp = out + ".stamp"
     if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:
         return out
-    cmd = [NVCC] + NVCC_FLAGS + [f"-DPBM_HEADER=\"{header}\"", f"-DPB_TEAM_SIZE={team}", f"-I{inc}", f"-I{CSRC}",
-                                 kernel_srcs[0], "-o", out]
+    cmd = [NVCC] + NVCC_FLAGS + [f"-DPBM_HEADER=\"{header}\"", f"-DPB_TEAM_SIZE={team}", f"-DPB_GLOBAL_VEC={gvec}", f"-I{inc}", f"-I{CSRC}",
+                                 kernel_srcs[0], "-o", out] + ([f"-DPB_PROFILE={int(profile)}"] if profile else [])
     r = subprocess.run(cmd, capture_output=True, text=True)
     log = r.stdout + r.stderr
-    with open(os.path.join(BUILD, f"pbgpu_model_{bundle.name}.ptxas.log"), "w") as f:
+    with open(out[:-3] + ".ptxas.log", "w") as f:
         f.write(" ".join(cmd) + "\n" + log)
     if verbose or r.returncode != 0:
         print(log)

@@ -192,20 +192,14 @@ def emit_program(prog: Program, fname: str, prefix: str):
     return "\n".join(em.tables), "\n".join(L), em.table_bytes
 
 
-def _emit_jds(em_lines, name, j: slu.JDS, slot_max):
-    it = _itype(slot_max)
+def _emit_u32(lines, name, words):
+    words = np.asarray(words, dtype=np.uint32).reshape(-1)
+    body = ", ".join(f"{int(w)}u" for w in words) if len(words) else "0u"
+    lines.append(f"static PB_TABLE PB_ALIGN16 const unsigned int {name}[{max(len(words), 1)}] = {{{body}}};")
 
-    def arr(ctype, suffix, vals, align=""):
-        vals = list(np.asarray(vals).reshape(-1))
-        body = ", ".join(str(int(v)) for v in vals) if vals else "0"
-        em_lines.append(f"static PB_TABLE {align}const {ctype} {name}_{suffix}[{max(len(vals), 1)}] = {{{body}}};")
 
-    em_lines.append(f"#define {name.upper()}_NLEV {j.n_levels}")
-    arr("int", "lev_meta", j.lev_meta, "PB_ALIGN16 ")
-    arr(it, "op_a", j.op_a)
-    arr(it, "op_b", j.op_b)
-    arr(it, "task_out", j.task_out)
-    arr(it, "task_aux", j.task_aux)
+# shared memory the team may spend on the factor stream (bytes); larger streams stay in global memory / L1
+FACTOR_STREAM_SMEM_BUDGET = 24 * 1024
 
 
 def model_functions(bundle, sym: slu.SymbolicLU | None, dialect: str):
@@ -273,6 +267,8 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
     out.append(f"#define PBM_NEV {bundle.n_events}")
     out.append(f"#define PBM_NNZ {len(bundle.jac_nodes)}")
     out.append(f"#define PBM_NTMP {max(n_tmp, 1)}")
+    out.append(f"#define PBM_NTMP_JAC {max(progs['jac'].n_tmp, 1)}")
+    out.append(f"#define PBM_NTMP_SMALL {max(max(p.n_tmp for k, p in progs.items() if k != 'jac'), 1)}")
     out.append(f"#define PBM_NVAR {n_var}")
     info = dict(n_tmp=n_tmp, n_var=n_var, table_bytes=0, programs={})
     for key in ("res", "jac", "events", "ic", "vars"):
@@ -296,17 +292,27 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
         kind = np.where(bundle.jac_rows < bundle.n_diff, np.where(bundle.jac_rows == bundle.jac_cols, 2, 1), 0)
         lines.append(f"static PB_TABLE const unsigned char pbm_ent_kind[{len(kind)}] = {{{', '.join(map(str, kind.tolist()))}}};")
         lines.append(f"static PB_TABLE const {it} pbm_ent_slot[{len(kind)}] = {{{', '.join(str(int(s)) for s in sym.a_slot)}}};")
-        lines.append(f"static PB_TABLE const {it} pbm_diag_slot[{sym.n}] = {{{', '.join(str(int(s)) for s in sym.diag_slot)}}};")
-        _emit_jds(lines, "pbm_fac", sym.factor, max(sym.nnz_lu, sym.n, 0xFFFF))
-        _emit_jds(lines, "pbm_fwd", sym.fwd, max(sym.nnz_lu, sym.n))
-        _emit_jds(lines, "pbm_bwd", sym.bwd, max(sym.nnz_lu, sym.n))
+        it_n = _itype(sym.n)
+        lines.append(f"static PB_TABLE const {it_n} pbm_perm_r[{sym.n}] = {{{', '.join(str(int(x)) for x in sym.perm_r)}}};")
+        lines.append(f"static PB_TABLE const {it_n} pbm_perm_c[{sym.n}] = {{{', '.join(str(int(x)) for x in sym.perm_c)}}};")
+        lines.append(f"#define PBM_FAC_NLEV {sym.factor.n_levels}")
+        lines.append(f"#define PBM_FWD_NLEV {sym.fwd.n_levels}")
+        lines.append(f"#define PBM_BWD_NLEV {sym.bwd.n_levels}")
+        lines.append(f"#define PBM_SLV_WORDS {len(sym.solve_stream)}")
+        lines.append(f"#define PBM_SLV_NREC {sym.n_solve_records}")
+        lines.append(f"#define PBM_FAC_WORDS {len(sym.factor_stream)}")
+        lines.append(f"#define PBM_FAC_NREC {sym.n_factor_records}")
+        lines.append(f"#define PBM_FAC_SMEM {1 if 4 * len(sym.factor_stream) <= FACTOR_STREAM_SMEM_BUDGET else 0}")
+        _emit_u32(lines, "pbm_slv_tab", sym.solve_stream)
+        _emit_u32(lines, "pbm_fac_tab", sym.factor_stream)
         out.append("\n".join(lines))
         out.append(f"#define PBM_FLOPS_FACTOR {sym.flops_factor}")
         out.append(f"#define PBM_FLOPS_SOLVE {sym.flops_solve}")
         info["lu"] = dict(nnz_lu=sym.nnz_lu, ordering=sym.ordering, factor_levels=sym.factor.n_levels,
                           fwd_levels=sym.fwd.n_levels, bwd_levels=sym.bwd.n_levels,
-                          factor_team_syncs=int(sym.factor.sync.sum()),
-                          solve_team_syncs=int(sym.fwd.sync.sum() + sym.bwd.sync.sum()),
+                          solve_stream_words=len(sym.solve_stream), factor_stream_words=len(sym.factor_stream),
+                          solve_records=sym.n_solve_records, factor_records=sym.n_factor_records,
+                          est_cycles_solve=sym.est_cycles_solve, est_cycles_factor=sym.est_cycles_factor,
                           flops_factor=sym.flops_factor, flops_solve=sym.flops_solve)
     else:
         rows = ", ".join(str(int(r)) for r in bundle.jac_rows)

@@ -33,6 +33,7 @@ int cuda_fail(const char* what, cudaError_t e) { return fail(std::string(what) +
 typedef int (*describe_fn)(pbgpu_model_desc*);
 typedef int (*launch_fn)(const pbgpu_launch*, void*, int*, char*, size_t);
 typedef int (*eval_fn)(const pbgpu_eval_launch*, void*, char*, size_t);
+typedef int (*plan_fn)(int, int*, char*, size_t);
 
 struct DevBuf {
   void* p = nullptr;
@@ -60,6 +61,7 @@ struct pbgpu_model_s {
   describe_fn describe = nullptr;
   launch_fn launch = nullptr;
   eval_fn eval = nullptr;
+  plan_fn plan = nullptr;
   pbgpu_model_desc desc;
   std::string path;
 };
@@ -70,7 +72,7 @@ struct pbgpu_solver_s {
   pbgpu_options opt;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-  DevBuf atol, t_eval, t_interp, inputs, y0, t_out, y_out, n_out, flag, y_term, stats, queue, scratch_a, scratch_b;
+  DevBuf atol, t_eval, t_interp, inputs, y0, t_out, y_out, n_out, flag, y_term, stats, queue, scratch_a, scratch_b, team_scratch;
   int last_grid = 0;
 };
 
@@ -111,7 +113,8 @@ int pbgpu_model_load(const char* path, pbgpu_model_t* model) {
   m->describe = (describe_fn)dlsym(h, "pbgpu_image_describe");
   m->launch = (launch_fn)dlsym(h, "pbgpu_image_launch");
   m->eval = (eval_fn)dlsym(h, "pbgpu_image_eval");
-  if (!m->describe || !m->launch || !m->eval) {
+  m->plan = (plan_fn)dlsym(h, "pbgpu_image_plan");
+  if (!m->describe || !m->launch || !m->eval || !m->plan) {
     dlclose(h);
     delete m;
     return fail(std::string("pbgpu_model_load: '") + path + "' is not a pbgpu model image");
@@ -188,7 +191,7 @@ int pbgpu_solver_destroy(pbgpu_solver_t s) {
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
   DevBuf* bufs[] = {&s->atol, &s->t_eval, &s->t_interp, &s->inputs, &s->y0, &s->t_out, &s->y_out, &s->n_out,
-                    &s->flag, &s->y_term, &s->stats, &s->queue, &s->scratch_a, &s->scratch_b};
+                    &s->flag, &s->y_term, &s->stats, &s->queue, &s->scratch_a, &s->scratch_b, &s->team_scratch};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 4; i++)
     if (s->ev[i]) cudaEventDestroy(s->ev[i]);
@@ -212,6 +215,17 @@ static int check_grids(const double* t_eval, int n_teval, const double* t_interp
       return fail("t_interp values must be less than the greatest t_eval value: " + std::to_string(t_eval[n_teval - 1]));
   }
   return 0;
+}
+
+// Per-team global scratch (streamed vectors of large models), sized for the grid the image will launch.
+static int ensure_team_scratch(pbgpu_solver_s* s, int n_sys) {
+  const long long per_team = s->model->desc.scratch_doubles_per_team;
+  if (per_team <= 0) return 0;
+  char err[512];
+  err[0] = 0;
+  int teams = 0;
+  if (s->model->plan(n_sys, &teams, err, sizeof(err))) return fail(err);
+  return s->team_scratch.ensure(sizeof(double) * (size_t)per_team * (size_t)teams);
 }
 
 static int launch_common(pbgpu_solver_s* s, int n_sys, const double* d_t_eval, int n_teval, const double* d_t_interp,
@@ -239,6 +253,8 @@ static int launch_common(pbgpu_solver_s* s, int n_sys, const double* d_t_eval, i
   L.y_term = d_yterm;
   L.stats = d_stats;
   L.queue = (unsigned int*)s->queue.p;
+  if (ensure_team_scratch(s, n_sys)) return 1;
+  L.scratch = (double*)s->team_scratch.p;
   L.opt = s->opt;
   CK(cudaMemsetAsync(s->queue.p, 0, sizeof(unsigned int), stream));
   char err[512];
@@ -355,6 +371,8 @@ int pbgpu_model_eval(pbgpu_solver_t s, int which, int n_sys, const double* y, co
   E.t = t;
   E.cj = cj;
   E.out = (double*)s->scratch_b.p;
+  if (ensure_team_scratch(s, n_sys)) return 1;
+  E.scratch = (double*)s->team_scratch.p;
   char err[512];
   err[0] = 0;
   if (s->model->eval(&E, (void*)st, err, sizeof(err))) return fail(err);

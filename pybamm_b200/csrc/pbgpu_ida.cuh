@@ -36,29 +36,54 @@
 
 #define PB_NEV_PAD ((PBM_NEV > 0) ? PBM_NEV : 1)
 
-// ---- shared-memory layout (in doubles) --------------------------------------------------------
-#define PB_OFF_PHI 0
-#define PB_OFF_EWT (PB_OFF_PHI + PB_MXORDP1 * PBM_N)
-#define PB_OFF_EE (PB_OFF_EWT + PBM_N)
-#define PB_OFF_DELTA (PB_OFF_EE + PBM_N)
-#define PB_OFF_YYPRED (PB_OFF_DELTA + PBM_N)
-#define PB_OFF_YPPRED (PB_OFF_YYPRED + PBM_N)
-#define PB_OFF_YY (PB_OFF_YPPRED + PBM_N)
+// ---- memory layout (in doubles) ---------------------------------------------------------------------
+// Shared memory always holds what is accessed at random inside the latency-critical loops: y (stencil reads of the
+// generated functions), delta / w (triangular solves), the L+U values, small temporaries, the packed solve stream.
+// The vectors that are only streamed (BDF history phi[0..5], ewt, ee, yypred, yppred) and the temporaries of the
+// Jacobian program live in shared memory for small models (PB_GLOBAL_VEC == 0: SPM, SPMe) and in a per-team global
+// scratch block (L2-resident: teams x ~100 KB) for large ones (PB_GLOBAL_VEC == 1: DFN), so that two teams fit per SM.
+#ifndef PB_GLOBAL_VEC
+#define PB_GLOBAL_VEC 0
+#endif
+#define PB_GOFF_PHI 0
+#define PB_GOFF_EWT (PB_GOFF_PHI + PB_MXORDP1 * PBM_N)
+#define PB_GOFF_EE (PB_GOFF_EWT + PBM_N)
+#define PB_GOFF_YYPRED (PB_GOFF_EE + PBM_N)
+#define PB_GOFF_YPPRED (PB_GOFF_YYPRED + PBM_N)
+#define PB_GOFF_TMPJ (PB_GOFF_YPPRED + PBM_N)
+#define PB_GVEC_DOUBLES (PB_GOFF_TMPJ + PBM_NTMP_JAC)
+#if PB_GLOBAL_VEC
+#define PB_OFF_DELTA 0
+#define PB_SCRATCH_DOUBLES PB_GVEC_DOUBLES
+#else
+#define PB_OFF_DELTA PB_GVEC_DOUBLES
+#define PB_SCRATCH_DOUBLES 0
+#endif
+#define PB_OFF_YY (PB_OFF_DELTA + PBM_N)
 #define PB_OFF_W (PB_OFF_YY + PBM_N)
 #define PB_OFF_TMP (PB_OFF_W + PBM_N + 1)
-#define PB_OFF_LU (PB_OFF_TMP + PBM_NTMP)
-#define PB_OFF_P (PB_OFF_LU + PBM_NNZ_LU + 1)
+#define PB_OFF_LU (PB_OFF_TMP + PBM_NTMP_SMALL)
+#define PB_OFF_P (PB_OFF_LU + PBM_NNZ_LU + 3)
 #define PB_OFF_G (PB_OFF_P + PBM_NP)
 #define PB_OFF_COEF (PB_OFF_G + 3 * PB_NEV_PAD)
 #define PB_OFF_RED (PB_OFF_COEF + 32)
 #define PB_OFF_STATS (PB_OFF_RED + 64)
-#define PB_SMEM_DOUBLES (PB_OFF_STATS + 8)
+#define PB_OFF_SLV (PB_OFF_STATS + 8)                          /* packed solve stream (u32 words) */
+#define PB_OFF_FAC (PB_OFF_SLV + (PBM_SLV_WORDS + 1) / 2)      /* packed factor stream when it fits (PBM_FAC_SMEM) */
+#if PBM_FAC_SMEM
+#define PB_SMEM_DOUBLES (PB_OFF_FAC + (PBM_FAC_WORDS + 1) / 2)
+#else
+#define PB_SMEM_DOUBLES PB_OFF_FAC
+#endif
 #define PB_SMEM_BYTES (PB_SMEM_DOUBLES * 8)
 
 enum { PB_ST_NST, PB_ST_NRE, PB_ST_NSETUPS, PB_ST_NETF, PB_ST_NNI, PB_ST_NCFN, PB_ST_NJE, PB_ST_NGE };
 
 struct pb_sys {
   double* sm;          // base of the team's shared memory
+  double* gv;          // base of the streamed vectors: == sm (PB_GLOBAL_VEC 0) or the team's global scratch block
+  const unsigned int* slv;  // solve stream (shared memory)
+  const unsigned int* fac;  // factor stream (shared memory when PBM_FAC_SMEM, else the global table)
   pb_team_ctx team;
   const double* atol;  // global
   // options (copied from pbgpu_options)
@@ -73,12 +98,13 @@ struct pb_sys {
   unsigned gactive;
 };
 
-#define S_PHI(S, j) ((S).sm + PB_OFF_PHI + (j) * PBM_N)
-#define S_EWT(S) ((S).sm + PB_OFF_EWT)
-#define S_EE(S) ((S).sm + PB_OFF_EE)
+#define S_PHI(S, j) ((S).gv + PB_GOFF_PHI + (j) * PBM_N)
+#define S_EWT(S) ((S).gv + PB_GOFF_EWT)
+#define S_EE(S) ((S).gv + PB_GOFF_EE)
+#define S_YYPRED(S) ((S).gv + PB_GOFF_YYPRED)
+#define S_YPPRED(S) ((S).gv + PB_GOFF_YPPRED)
+#define S_TMPJ(S) ((S).gv + PB_GOFF_TMPJ)
 #define S_DELTA(S) ((S).sm + PB_OFF_DELTA)
-#define S_YYPRED(S) ((S).sm + PB_OFF_YYPRED)
-#define S_YPPRED(S) ((S).sm + PB_OFF_YPPRED)
 #define S_YY(S) ((S).sm + PB_OFF_YY)
 #define S_W(S) ((S).sm + PB_OFF_W)
 #define S_TMP(S) ((S).sm + PB_OFF_TMP)
@@ -94,62 +120,181 @@ struct pb_sys {
 #define S_GAMMA(S) ((S).sm + PB_OFF_COEF + 24)
 #define S_STATS(S) ((S).sm + PB_OFF_STATS)
 
+#ifndef PB_PROFILE
 #define PB_STAT(S, k)                        \
   do {                                       \
     if (PB_TID == 0) S_STATS(S)[k] += 1.0;   \
   } while (0)
-
-// ---- static-pattern sparse LU (tables from pybamm_b200/symbolic_lu.py) ---------------------------
-// Level-scheduled, operands in ELL layout: operand p of task q of a level sits at op_base + p*nt + q,
-// short tasks are padded with the constant-zero slots lu[PBM_NNZ_LU] / w[PBM_N].  The 4-int level
-// record of the next level is fetched while the current level computes.
-struct pb_level {
-  int t0, nt, ob, ml, sync;
-};
-#define PB_LEVEL_LOAD(L, meta, lev)                 \
-  do {                                              \
-    const int* m__ = (meta) + 4 * (lev);            \
-    (L).t0 = PB_LDU(m__[0]);                        \
-    (L).nt = PB_LDU(m__[1]);                        \
-    (L).ob = PB_LDU(m__[2]);                        \
-    const int w__ = PB_LDU(m__[3]);                 \
-    (L).ml = w__ & 0xFFFF;                          \
-    (L).sync = w__ >> 16;                           \
+#define PB_T0(v) ((void)0)
+#define PB_T1(S, v, k) ((void)0)
+#else
+// Profiling build (tools/gpu_phases.py): the 8 stats slots hold clock64() cycles per phase instead of the IDA
+// counters: 0 residual, 1 triangular solves, 2 Jacobian evaluation, 3 LU factorisation, 4 Newton vector work,
+// 5 step control (coefficients, error test, history update), 6 events + root finding, 7 output points.
+#define PB_STAT(S, k) ((void)0)
+#define PB_T0(v) const long long v = clock64()
+#define PB_T1(S, v, k)                                                   \
+  do {                                                                   \
+    if (PB_TID == 0) S_STATS(S)[k] += (double)(clock64() - (v));         \
   } while (0)
+#endif
+#if defined(PB_PROFILE) && PB_PROFILE == 2
+#define PB_T1X(S, v, k) ((void)0)
+#else
+#define PB_T1X(S, v, k) PB_T1(S, v, k)
+#endif
+
+// ---- static-pattern sparse LU (packed streams from pybamm_b200/symbolic_lu.py: build_streams) -------
+// A stream is a sequence of records [meta][task x nt][operand x nt x ml] walked with one running offset:
+//   meta = nt | ml << 16 | flags << 28;  flags: 1 END of a dependency level, 2 backward record, 4 team-wide level
+//   solve : task = row | diag_slot << 16, operand = lu_slot | w_index << 16
+//   factor: task = out_slot | aux << 16,  operand = lu_slot | lu_slot << 16
+// Padding operands point at lu[PBM_NNZ_LU] = 0 / w[PBM_N] = 0; lu[PBM_NNZ_LU + 1] = 1.
+// The solve stream lives in shared memory: a dependency level costs one shared-memory round trip, not a trip
+// to L2 for its indices.  Triangular solves are narrow (tens of rows per level), so warp 0 runs them alone
+// with __syncwarp between levels; the team meets again at the end.
+#define PB_F_END 1u
+#define PB_F_BWD 2u
+#define PB_F_TEAM 4u
+#define PB_F_GROUP 8u
+
+// GROUP-mode partial sum of one record: 32/nt lanes share a task; lane l reads the operand words base + l + 32k
+// (k < ml*nt/32) and the partial sums of a task are combined with an xor-shuffle butterfly over lane strides
+// nt, 2nt, ... 16.  x is the vector the second operand index refers to (w for solves, lu for the factorisation).
+// Returns sum(lu[a] * x[b]) of the task lane & (nt - 1); valid in every lane.
+#ifndef PB_EMU
+static PB_DEV double pb_group_dot(const unsigned int* ops, const int nt, const int ml, const double* lu, const double* x) {
+  const int k_n = (ml * nt) >> 5;
+  const unsigned int* op = ops + PB_LANE;
+  double a0 = 0.0, a1 = 0.0;
+  int k = 0;
+  for (; k + 1 < k_n; k += 2) {
+    const unsigned int o0 = op[32 * k], o1 = op[32 * k + 32];
+    a0 += lu[o0 & 0xFFFFu] * x[o0 >> 16];
+    a1 += lu[o1 & 0xFFFFu] * x[o1 >> 16];
+  }
+  if (k < k_n) {
+    const unsigned int o0 = op[32 * k];
+    a0 += lu[o0 & 0xFFFFu] * x[o0 >> 16];
+  }
+  a0 += a1;
+  for (int o = nt; o < 32; o <<= 1) a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+  return a0;
+}
+#endif
+#if PBM_FAC_SMEM
+#define PB_FAC_LD(x) (x)
+#else
+#define PB_FAC_LD(x) PB_LDU(x)
+#endif
 
 // Entry-parallel left-looking factorisation of the values already scattered into lu[] by pbm_jac.
 // Returns non-zero (team-uniform) when a pivot is zero / not finite.
 static PB_DEV int pb_lu_factor(pb_sys& S) {
   double* lu = S_LU(S);
+  const unsigned int* st = S.fac;
   double bad = 0.0;
-  pb_level L, Ln;
-  PB_LEVEL_LOAD(L, pbm_fac_lev_meta, 0);
-  for (int lev = 0; lev < PBM_FAC_NLEV; lev++) {
-    Ln = L;
-    if (lev + 1 < PBM_FAC_NLEV) PB_LEVEL_LOAD(Ln, pbm_fac_lev_meta, lev + 1);
-    for (int q = PB_TID; q < L.nt; q += PB_TEAM) {
-      const int out = (int)PB_LD(pbm_fac_task_out[L.t0 + q]);
-      const int aux = (int)PB_LD(pbm_fac_task_aux[L.t0 + q]);
-      double acc = lu[out];
-#pragma unroll 4
-      for (int p = 0; p < L.ml; p++) {
-        const int idx = L.ob + p * L.nt + q;
-        acc -= lu[(int)PB_LD(pbm_fac_op_a[idx])] * lu[(int)PB_LD(pbm_fac_op_b[idx])];
+  int off = 0;
+  unsigned int meta = PB_FAC_LD(st[0]);
+  for (int rec = 0; rec < PBM_FAC_NREC; rec++) {
+    const int nt = (int)(meta & 0xFFFFu), ml = (int)((meta >> 16) & 0xFFFu);
+    const unsigned int fl = meta >> 28;
+    const int base = off + 1;
+    off = base + nt * (1 + ml);
+    if (rec + 1 < PBM_FAC_NREC) meta = PB_FAC_LD(st[off]);
+    const int wide = (fl & PB_F_TEAM) != 0;
+    if (fl & PB_F_GROUP) {   // narrow level, few long tasks: warp 0, 32/nt lanes per task
+      if (PB_WARP == 0) {
+#ifndef PB_EMU
+        const unsigned int tw = PB_FAC_LD(st[base + (PB_LANE & (nt - 1))]);
+        const unsigned int* op = st + base + nt + PB_LANE;
+        const int k_n = (ml * nt) >> 5;
+        double a0 = 0.0, a1 = 0.0;
+        int k = 0;
+        for (; k + 1 < k_n; k += 2) {
+          const unsigned int o0 = PB_FAC_LD(op[32 * k]), o1 = PB_FAC_LD(op[32 * k + 32]);
+          a0 += lu[o0 & 0xFFFFu] * lu[o0 >> 16];
+          a1 += lu[o1 & 0xFFFFu] * lu[o1 >> 16];
+        }
+        if (k < k_n) {
+          const unsigned int o0 = PB_FAC_LD(op[32 * k]);
+          a0 += lu[o0 & 0xFFFFu] * lu[o0 >> 16];
+        }
+        a0 += a1;
+        for (int o = nt; o < 32; o <<= 1) a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+        if (PB_LANE < nt) {
+          const int out = (int)(tw & 0xFFFFu), aux = (int)(tw >> 16);
+          const double acc = lu[out] - a0;
+          if (aux == PB_AUX_U) {
+            lu[out] = acc;
+          } else if (aux == PB_AUX_DIAG) {
+            const double inv = 1.0 / acc;
+            if (!(fabs(inv) <= 1.7e308) || acc == 0.0) bad = 1.0;
+            lu[out] = inv;
+          } else {
+            lu[out] = acc * lu[aux];
+          }
+        }
+#else
+        for (int q = 0; q < nt; q++) {
+          const unsigned int tw = st[base + q];
+          const int out = (int)(tw & 0xFFFFu), aux = (int)(tw >> 16);
+          double dot = 0.0;
+          for (int p = 0; p < ml; p++) {
+            const unsigned int o0 = st[base + nt + p * nt + q];
+            dot += lu[o0 & 0xFFFFu] * lu[o0 >> 16];
+          }
+          const double acc = lu[out] - dot;
+          if (aux == PB_AUX_U) {
+            lu[out] = acc;
+          } else if (aux == PB_AUX_DIAG) {
+            const double inv = 1.0 / acc;
+            if (!(fabs(inv) <= 1.7e308) || acc == 0.0) bad = 1.0;
+            lu[out] = inv;
+          } else {
+            lu[out] = acc * lu[aux];
+          }
+        }
+#endif
       }
-      if (aux == PB_AUX_U) {
-        lu[out] = acc;
-      } else if (aux == PB_AUX_DIAG) {
-        const double inv = 1.0 / acc;
-        if (!(fabs(inv) <= 1.7e308) || acc == 0.0) bad = 1.0;
-        lu[out] = inv;
-      } else {
-        lu[out] = acc * lu[aux];
+      if (fl & PB_F_END) PB_SYNCWARP();
+      continue;
+    }
+    if (wide || PB_WARP == 0) {
+      const int stride = wide ? PB_TEAM : PB_LANES;
+      for (int q = wide ? PB_TID : PB_LANE; q < nt; q += stride) {
+        const unsigned int tw = PB_FAC_LD(st[base + q]);
+        const int out = (int)(tw & 0xFFFFu), aux = (int)(tw >> 16);
+        const unsigned int* op = st + base + nt + q;
+        double acc0 = lu[out], acc1 = 0.0;
+        int p = 0;
+        for (; p + 1 < ml; p += 2) {
+          const unsigned int o0 = PB_FAC_LD(op[p * nt]), o1 = PB_FAC_LD(op[(p + 1) * nt]);
+          acc0 -= lu[o0 & 0xFFFFu] * lu[o0 >> 16];
+          acc1 -= lu[o1 & 0xFFFFu] * lu[o1 >> 16];
+        }
+        if (p < ml) {
+          const unsigned int o0 = PB_FAC_LD(op[p * nt]);
+          acc0 -= lu[o0 & 0xFFFFu] * lu[o0 >> 16];
+        }
+        const double acc = acc0 + acc1;
+        if (aux == PB_AUX_U) {
+          lu[out] = acc;
+        } else if (aux == PB_AUX_DIAG) {
+          const double inv = 1.0 / acc;
+          if (!(fabs(inv) <= 1.7e308) || acc == 0.0) bad = 1.0;
+          lu[out] = inv;
+        } else {
+          lu[out] = acc * lu[aux];
+        }
       }
     }
-    if (L.sync) PB_SYNC();
-    else PB_SYNCWARP();
-    L = Ln;
+    if (fl & PB_F_END) {
+      if (wide) PB_SYNC();
+      else PB_SYNCWARP();
+    }
   }
+  PB_SYNC();
   return pb_team_max(S.team, bad) != 0.0;
 }
 
@@ -157,47 +302,86 @@ static PB_DEV int pb_lu_factor(pb_sys& S) {
 static PB_DEV void pb_lu_solve(pb_sys& S, double* b) {
   const double* lu = S_LU(S);
   double* w = S_W(S);
-  pb_level L, Ln;
-  PB_LEVEL_LOAD(L, pbm_fwd_lev_meta, 0);
-  for (int lev = 0; lev < PBM_FWD_NLEV; lev++) {
-    Ln = L;
-    if (lev + 1 < PBM_FWD_NLEV) PB_LEVEL_LOAD(Ln, pbm_fwd_lev_meta, lev + 1);
-    for (int q = PB_TID; q < L.nt; q += PB_TEAM) {
-      const int row = (int)PB_LD(pbm_fwd_task_out[L.t0 + q]);
-      double acc = b[(int)PB_LD(pbm_fwd_task_aux[L.t0 + q])];
-#pragma unroll 4
-      for (int p = 0; p < L.ml; p++) {
-        const int idx = L.ob + p * L.nt + q;
-        acc -= lu[(int)PB_LD(pbm_fwd_op_a[idx])] * w[(int)PB_LD(pbm_fwd_op_b[idx])];
+#if defined(PB_PROFILE) && PB_PROFILE == 2
+  PB_T0(tga_);
+#endif
+  for (int i = PB_TID; i < PBM_N; i += PB_TEAM) w[i] = b[(int)PB_LD(pbm_perm_r[i])];
+  PB_SYNC();
+#if defined(PB_PROFILE) && PB_PROFILE == 2
+  PB_T1(S, tga_, 5);   // PB_PROFILE=2: slots 5/6/7 = gather / level loop / scatter of the triangular solves
+  PB_T0(tlv_);
+#endif
+  if (PB_WARP == 0) {
+    const unsigned int* st = S.slv;
+    int off = 0;
+    unsigned int meta = st[0];
+    for (int rec = 0; rec < PBM_SLV_NREC; rec++) {
+      const int nt = (int)(meta & 0xFFFFu), ml = (int)((meta >> 16) & 0xFFFu);
+      const unsigned int fl = meta >> 28;
+      const int base = off + 1;
+      off = base + nt * (1 + ml);
+      if (rec + 1 < PBM_SLV_NREC) meta = st[off];
+      if (fl & PB_F_GROUP) {
+#ifndef PB_EMU
+        const unsigned int tw = st[base + (PB_LANE & (nt - 1))];
+        const double dot = pb_group_dot(st + base + nt, nt, ml, lu, w);
+        if (PB_LANE < nt) {
+          const int row = (int)(tw & 0xFFFFu);
+          double acc = w[row] - dot;
+          if (fl & PB_F_BWD) acc *= lu[tw >> 16];
+          w[row] = acc;
+        }
+#else
+        for (int q = 0; q < nt; q++) {
+          const unsigned int tw = st[base + q];
+          const int row = (int)(tw & 0xFFFFu);
+          double dot = 0.0;
+          for (int p = 0; p < ml; p++) {
+            const unsigned int o0 = st[base + nt + p * nt + q];
+            dot += lu[o0 & 0xFFFFu] * w[o0 >> 16];
+          }
+          double acc = w[row] - dot;
+          if (fl & PB_F_BWD) acc *= lu[tw >> 16];
+          w[row] = acc;
+        }
+#endif
+        if (fl & PB_F_END) PB_SYNCWARP();
+        continue;
       }
-      w[row] = acc;
-    }
-    if (L.sync) PB_SYNC();
-    else PB_SYNCWARP();
-    L = Ln;
-  }
-  PB_LEVEL_LOAD(L, pbm_bwd_lev_meta, 0);
-  for (int lev = 0; lev < PBM_BWD_NLEV; lev++) {
-    Ln = L;
-    if (lev + 1 < PBM_BWD_NLEV) PB_LEVEL_LOAD(Ln, pbm_bwd_lev_meta, lev + 1);
-    for (int q = PB_TID; q < L.nt; q += PB_TEAM) {
-      const int row = (int)PB_LD(pbm_bwd_task_out[L.t0 + q]);
-      const int dst = (int)PB_LD(pbm_bwd_task_aux[L.t0 + q]);
-      const double dinv = lu[(int)PB_LD(pbm_diag_slot[row])];
-      double acc = w[row];
-#pragma unroll 4
-      for (int p = 0; p < L.ml; p++) {
-        const int idx = L.ob + p * L.nt + q;
-        acc -= lu[(int)PB_LD(pbm_bwd_op_a[idx])] * w[(int)PB_LD(pbm_bwd_op_b[idx])];
+      for (int q = PB_LANE; q < nt; q += PB_LANES) {
+        const unsigned int tw = st[base + q];
+        const int row = (int)(tw & 0xFFFFu);
+        const unsigned int* op = st + base + nt + q;
+        double acc0 = w[row], acc1 = 0.0;
+        int p = 0;
+        for (; p + 1 < ml; p += 2) {
+          const unsigned int o0 = op[p * nt], o1 = op[(p + 1) * nt];
+          acc0 -= lu[o0 & 0xFFFFu] * w[o0 >> 16];
+          acc1 -= lu[o1 & 0xFFFFu] * w[o1 >> 16];
+        }
+        if (p < ml) {
+          const unsigned int o0 = op[p * nt];
+          acc0 -= lu[o0 & 0xFFFFu] * w[o0 >> 16];
+        }
+        double acc = acc0 + acc1;
+        if (fl & PB_F_BWD) acc *= lu[tw >> 16];
+        w[row] = acc;
       }
-      acc *= dinv;
-      w[row] = acc;
-      b[dst] = acc;
+      if (fl & PB_F_END) PB_SYNCWARP();
     }
-    if (L.sync) PB_SYNC();
-    else PB_SYNCWARP();
-    L = Ln;
   }
+#if defined(PB_PROFILE) && PB_PROFILE == 2
+  PB_T1(S, tlv_, 6);
+#endif
+  PB_SYNC();
+#if defined(PB_PROFILE) && PB_PROFILE == 2
+  PB_T0(tsc_);
+#endif
+  for (int i = PB_TID; i < PBM_N; i += PB_TEAM) b[(int)PB_LD(pbm_perm_c[i])] = w[i];
+  PB_SYNC();
+#if defined(PB_PROFILE) && PB_PROFILE == 2
+  PB_T1(S, tsc_, 7);
+#endif
 }
 
 // Evaluate J - cj*M at (t, y) into the LU value array and factor it.  ic_mode: replace the
@@ -205,9 +389,11 @@ static PB_DEV void pb_lu_solve(pb_sys& S, double* b) {
 // AlgebraicICBuilder.inl:52-119, solved through the same static LU).
 static PB_DEV int pb_lsetup(pb_sys& S, double t, const double* y, double cj, int ic_mode) {
   double* lu = S_LU(S);
+  PB_T0(tj_);
   for (int i = PB_TID; i < PBM_NFILL; i += PB_TEAM) lu[(int)PB_LD(pbm_fill[i])] = 0.0;
-  pbm_jac(y, S_P(S), t, cj, lu, S_TMP(S));
+  pbm_jac(y, S_P(S), t, cj, lu, S_TMPJ(S));
   PB_SYNC();
+  PB_T1(S, tj_, 2);
   if (ic_mode) {
     for (int k = PB_TID; k < PBM_NNZ; k += PB_TEAM) {
       const int kind = (int)PB_LD(pbm_ent_kind[k]);
@@ -217,7 +403,10 @@ static PB_DEV int pb_lsetup(pb_sys& S, double t, const double* y, double cj, int
   }
   PB_STAT(S, PB_ST_NJE);
   PB_STAT(S, PB_ST_NSETUPS);
-  return pb_lu_factor(S);
+  PB_T0(tf_);
+  const int ier = pb_lu_factor(S);
+  PB_T1(S, tf_, 3);
+  return ier;
 }
 
 static PB_DEV double pb_wrms(pb_sys& S, const double* x) {
@@ -385,7 +574,7 @@ static PB_DEV void pb_restore(pb_sys& S, double saved_t, int phi_scaled) {
 #define PB_PREDICT_AGAIN 20
 
 // IDANls + Newton iteration + idaNlsConvTest (modified Newton, J held between lsetups).
-static PB_DEV int pb_nls(pb_sys& S) {
+static PB_DEV int pb_nls_impl(pb_sys& S) {
   int callLSetup = 0;
   if (S.nst == 0) {
     S.cjold = S.cj;
@@ -439,9 +628,13 @@ static PB_DEV int pb_nls(pb_sys& S) {
   int jcur = 0, retval = 0;
   double oldnrm = 0.0;
   for (;;) {
-    pbm_res(yy, S_P(S), S.tn, 0.0, delta, S_TMP(S));
-    PB_STAT(S, PB_ST_NRE);
-    PB_SYNC();
+    {
+      PB_T0(tr_);
+      pbm_res(yy, S_P(S), S.tn, 0.0, delta, S_TMP(S));
+      PB_STAT(S, PB_ST_NRE);
+      PB_SYNC();
+      PB_T1(S, tr_, 0);
+    }
     int fail = 0;
     if (callLSetup) {
       const int ier = pb_lsetup(S, S.tn, yy, S.cj, 0);
@@ -465,7 +658,11 @@ static PB_DEV int pb_nls(pb_sys& S) {
           delta[i] = -r;
         }
         PB_SYNC();
-        pb_lu_solve(S, delta);
+        {
+          PB_T0(ts_);
+          pb_lu_solve(S, delta);
+          PB_T1(S, ts_, 1);
+        }
         const double scale = (S.scalesol && S.cjratio != 1.0) ? 2.0 / (1.0 + S.cjratio) : 1.0;
         double acc = 0.0;
         for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
@@ -501,9 +698,13 @@ static PB_DEV int pb_nls(pb_sys& S) {
           retval = PB_NLS_CONV_RECVR;
           break;
         }
-        pbm_res(yy, S_P(S), S.tn, 0.0, delta, S_TMP(S));
-        PB_STAT(S, PB_ST_NRE);
-        PB_SYNC();
+        {
+          PB_T0(tr_);
+          pbm_res(yy, S_P(S), S.tn, 0.0, delta, S_TMP(S));
+          PB_STAT(S, PB_ST_NRE);
+          PB_SYNC();
+          PB_T1(S, tr_, 0);
+        }
       }
     }
     if (retval > 0 && !jcur) {
@@ -517,6 +718,13 @@ static PB_DEV int pb_nls(pb_sys& S) {
     }
     return retval;
   }
+}
+
+static PB_DEV int pb_nls(pb_sys& S) {
+  PB_T0(tn_);
+  const int r = pb_nls_impl(S);
+  PB_T1(S, tn_, 4);   // inclusive of phases 0-3 spent inside the Newton solve
+  return r;
 }
 
 // IDATestError
@@ -675,7 +883,7 @@ static PB_DEV void pb_complete_step(pb_sys& S, double err_k, double err_km1) {
 }
 
 // IDAStep
-static PB_DEV int pb_ida_step(pb_sys& S) {
+static PB_DEV int pb_ida_step_impl(pb_sys& S) {
   const double saved_t = S.tn;
   double ck = 0.0, err_k = 0.0, err_km1 = 0.0;
   int ncf = 0, nef = 0;
@@ -710,6 +918,13 @@ static PB_DEV int pb_ida_step(pb_sys& S) {
   }
   pb_complete_step(S, err_k, err_km1);
   return PB_IDA_SUCCESS;
+}
+
+static PB_DEV int pb_ida_step(pb_sys& S) {
+  PB_T0(tt_);
+  const int r = pb_ida_step_impl(S);
+  PB_T1X(S, tt_, 5);   // inclusive of phase 4
+  return r;
 }
 
 // ---- termination events: IDARcheck1 / IDARcheck3 / IDARootfind (Illinois) on the BDF interpolant ----
@@ -927,9 +1142,14 @@ static PB_DEV int pb_ida_solve_one_step(pb_sys& S, double tout, double* tret) {
     if (fabs(S.tn - S.tstop) <= troundoff) S.tn = S.tstop;
   }
 #if PBM_NEV > 0
-  if (pb_rcheck3(S)) {
-    *tret = S.tretlast = S.tlo;
-    return PB_IDA_ROOT_RETURN;
+  {
+    PB_T0(tg_);
+    const int root = pb_rcheck3(S);
+    PB_T1X(S, tg_, 6);
+    if (root) {
+      *tret = S.tretlast = S.tlo;
+      return PB_IDA_ROOT_RETURN;
+    }
   }
 #endif
   // IDAStopTest2, ONE_STEP
@@ -1069,6 +1289,7 @@ static PB_DEV double pb_perturb_time(double t) {
 
 static PB_DEV void pb_store_point(pb_sys& S, const pbgpu_launch& L, int sys, double t, int* i_save, double* t_last) {
   if (*i_save >= L.n_max) return;
+  PB_T0(to_);
   *t_last = t;
   const size_t slot = (size_t)sys * L.n_max + *i_save;
   double* row = L.y_out + slot * L.n_ret;
@@ -1084,6 +1305,7 @@ static PB_DEV void pb_store_point(pb_sys& S, const pbgpu_launch& L, int sys, dou
   }
   if (PB_TID == 0) L.t_out[slot] = t;
   (*i_save)++;
+  PB_T1X(S, to_, 7);
 }
 
 static PB_DEV void pb_solve_system(pb_sys& S, const pbgpu_launch& L, int sys) {
@@ -1210,13 +1432,31 @@ static PB_DEV void pb_solve_system(pb_sys& S, const pbgpu_launch& L, int sys) {
   }
 }
 
-static PB_DEV void pb_sys_init(pb_sys& S, double* sm, const pbgpu_launch& L) {
-  S.sm = sm;
-  S.team.red = sm + PB_OFF_RED;
+// Constant slots of the LU value array and the packed streams (copied to shared memory once per team). S.sm must be set.
+static PB_DEV void pb_sys_tables(pb_sys& S) {
   if (PB_TID == 0) {
-    S_LU(S)[PBM_NNZ_LU] = 0.0;  // constant-zero padding operands of the ELL tables
+    S_LU(S)[PBM_NNZ_LU] = 0.0;      // padding operands
+    S_LU(S)[PBM_NNZ_LU + 1] = 1.0;
     S_W(S)[PBM_N] = 0.0;
   }
+  unsigned int* slv = (unsigned int*)(S.sm + PB_OFF_SLV);
+  for (int i = PB_TID; i < PBM_SLV_WORDS; i += PB_TEAM) slv[i] = PB_LD(pbm_slv_tab[i]);
+  S.slv = slv;
+#if PBM_FAC_SMEM
+  unsigned int* fac = (unsigned int*)(S.sm + PB_OFF_FAC);
+  for (int i = PB_TID; i < PBM_FAC_WORDS; i += PB_TEAM) fac[i] = PB_LD(pbm_fac_tab[i]);
+  S.fac = fac;
+#else
+  S.fac = pbm_fac_tab;
+#endif
+  PB_SYNC();
+}
+
+static PB_DEV void pb_sys_init(pb_sys& S, double* sm, double* gv, const pbgpu_launch& L) {
+  S.sm = sm;
+  S.gv = gv;
+  S.team.red = sm + PB_OFF_RED;
+  pb_sys_tables(S);
 #ifndef PB_EMU
   S.team.red_phase = 0;
 #endif

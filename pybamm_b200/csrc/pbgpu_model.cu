@@ -20,7 +20,11 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE) pbgpu_solve_kernel(co
   extern __shared__ double pb_smem[];
   __shared__ unsigned int next_sys;
   pb_sys S;
-  pb_sys_init(S, pb_smem, L);
+#if PB_GLOBAL_VEC
+  pb_sys_init(S, pb_smem, L.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES, L);
+#else
+  pb_sys_init(S, pb_smem, pb_smem, L);
+#endif
   for (;;) {
     if (threadIdx.x == 0) next_sys = atomicAdd(L.queue, 1u);
     __syncthreads();
@@ -36,12 +40,14 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE) pbgpu_eval_kernel(con
   extern __shared__ double pb_smem[];
   pb_sys S;
   S.sm = pb_smem;
+#if PB_GLOBAL_VEC
+  S.gv = E.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES;
+#else
+  S.gv = pb_smem;
+#endif
   S.team.red = pb_smem + PB_OFF_RED;
   S.team.red_phase = 0;
-  if (PB_TID == 0) {
-    S_LU(S)[PBM_NNZ_LU] = 0.0;
-    S_W(S)[PBM_N] = 0.0;
-  }
+  pb_sys_tables(S);
   for (int sys = blockIdx.x; sys < E.n_sys; sys += gridDim.x) {
     __syncthreads();
     double* y = S_YY(S);
@@ -61,7 +67,7 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE) pbgpu_eval_kernel(con
         double* lu = S_LU(S);
         for (int i = PB_TID; i < PBM_NNZ_LU; i += PB_TEAM) lu[i] = 0.0;
         PB_SYNC();
-        pbm_jac(y, S_P(S), E.t, E.cj, lu, S_TMP(S));
+        pbm_jac(y, S_P(S), E.t, E.cj, lu, S_TMPJ(S));
         PB_SYNC();
         for (int k = PB_TID; k < PBM_NNZ && k < E.out_len; k += PB_TEAM) gout[k] = lu[(int)pbm_ent_slot[k]];
       } break;
@@ -117,19 +123,17 @@ static int pb_configure(char* err, size_t errlen) {
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, dev);
   g_num_sms = prop.multiProcessorCount;
-  // Shared-memory carve-out: the per-team state lives in shared memory, but the index tables of the
-  // generated functions and of the sparse LU are read through L1 -- leave it room.  By default at most
-  // 164 KB of the SM's 228 KB go to shared memory (=> >= 64 KB of L1) unless one team needs more.
-  int carve_kb = 164;
-  if (const char* env = getenv("PBGPU_SMEM_CARVEOUT_KB")) carve_kb = atoi(env);
+  // Shared-memory carve-out.  The integration is latency-bound (dependent shared-memory round trips in the
+  // triangular solves), so resident teams per SM is what buys throughput: large teams (> 48 KB: DFN) take all the
+  // shared memory they can use; small ones (SPM / SPMe: one warp per system, the CTA-per-SM limit binds first) leave
+  // at least 64 KB of L1 for the index tables of the generated functions.  PBGPU_SMEM_CARVEOUT_KB / PBGPU_TEAMS_PER_SM override.
   const int per_team = (int)PB_SMEM_BYTES + 1024;  // + the per-CTA reservation
+  int carve_kb = (per_team > 48 * 1024) ? 227 : 164;
+  if (const char* env = getenv("PBGPU_SMEM_CARVEOUT_KB")) carve_kb = atoi(env);
   if (carve_kb * 1024 < per_team) carve_kb = (per_team + 1023) / 1024;
   if (carve_kb > 227) carve_kb = 227;
   const int total_kb = (int)(prop.sharedMemPerMultiprocessor / 1024);
-  int pct = (carve_kb * 100 + total_kb - 1) / total_kb;
-  if (pct > 100) pct = 100;
-  cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-  cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+  e = cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_blocks_per_sm, pbgpu_solve_kernel, PB_TEAM_SIZE, PB_SMEM_BYTES);
   if (e != cudaSuccess || g_blocks_per_sm < 1) {
     snprintf(err, errlen, "occupancy query failed for model '%s': %s", PBM_NAME, cudaGetErrorString(e));
@@ -142,6 +146,13 @@ static int pb_configure(char* err, size_t errlen) {
     const int v = atoi(env);
     if (v >= 1 && v < g_blocks_per_sm) g_blocks_per_sm = v;
   }
+  // give the rest back to L1: carve out exactly what the resident teams use
+  int use_kb = (g_blocks_per_sm * per_team + 1023) / 1024;
+  if (use_kb > carve_kb) use_kb = carve_kb;
+  int pct = (use_kb * 100 + total_kb - 1) / total_kb;
+  if (pct > 100) pct = 100;
+  cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+  cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   g_configured_device = dev;
   return 0;
 }
@@ -168,7 +179,18 @@ extern "C" int pbgpu_image_describe(pbgpu_model_desc* d) {
   d->flops[3] = PBM_FLOPS_SOLVE;
   d->flops[4] = PBM_FLOPS_EVENTS;
   d->flops[5] = PBM_FLOPS_VARS;
+  d->scratch_doubles_per_team = PB_SCRATCH_DOUBLES;
   strncpy(d->name, PBM_NAME, sizeof(d->name) - 1);
+  return 0;
+}
+
+// Teams a launch for n_sys systems will use on the current device (the solver handle sizes its scratch block with it).
+extern "C" int pbgpu_image_plan(int n_sys, int* teams, char* err, size_t errlen) {
+  if (pb_configure(err, errlen)) return 1;
+  int grid = g_blocks_per_sm * g_num_sms;
+  if (n_sys > 0 && grid > n_sys) grid = n_sys;
+  if (grid < 1) grid = 1;
+  *teams = grid;
   return 0;
 }
 

@@ -36,7 +36,7 @@ class ModelDesc(C.Structure):
         ("abi_version", C.c_int), ("n_states", C.c_int), ("n_diff", C.c_int), ("n_inputs", C.c_int),
         ("n_events", C.c_int), ("nnz_jac", C.c_int), ("nnz_lu", C.c_int), ("n_vars", C.c_int),
         ("team_size", C.c_int), ("smem_bytes", C.c_int), ("n_tmp", C.c_int), ("lu_levels", C.c_int * 3),
-        ("flops", C.c_longlong * 6), ("name", C.c_char * 64),
+        ("flops", C.c_longlong * 6), ("scratch_doubles_per_team", C.c_longlong), ("name", C.c_char * 64),
     ]
 
 
@@ -54,7 +54,7 @@ class LaunchArgs(C.Structure):
         ("n_ret", C.c_int), ("t_eval", C.c_void_p), ("t_interp", C.c_void_p), ("inputs", C.c_void_p),
         ("y0", C.c_void_p), ("atol", C.c_void_p), ("t_out", C.c_void_p), ("y_out", C.c_void_p),
         ("n_out", C.c_void_p), ("flag", C.c_void_p), ("y_term", C.c_void_p), ("stats", C.c_void_p),
-        ("queue", C.c_void_p), ("opt", Options),
+        ("queue", C.c_void_p), ("scratch", C.c_void_p), ("opt", Options),
     ]
 
 

@@ -75,9 +75,17 @@ class SymbolicLU:
     flops_factor: int
     flops_solve: int
     ordering: str
+    solve_stream: np.ndarray = None    # uint32 words, see _solve_stream
+    factor_stream: np.ndarray = None   # uint32 words, see _factor_stream
+    n_solve_records: int = 0
+    n_factor_records: int = 0
+    est_cycles_solve: int = 0
+    est_cycles_factor: int = 0
 
     def summary(self):
-        return (f"n={self.n} nnz_lu={self.nnz_lu} ordering={self.ordering} "
+        return (f"n={self.n} nnz_lu={self.nnz_lu} ordering={self.ordering} streams: solve {len(self.solve_stream)} words/"
+                f"{self.n_solve_records} rec (~{self.est_cycles_solve} cyc), factor {len(self.factor_stream)} words/"
+                f"{self.n_factor_records} rec (~{self.est_cycles_factor} cyc); "
                 f"factor: {self.factor.n_levels} levels/{self.factor.n_tasks} tasks/{self.factor.n_ops} ops ({len(self.factor.op_a)} padded) "
                 f"(team syncs {int(self.factor.sync.sum())}); fwd {self.fwd.n_levels} lv, bwd {self.bwd.n_levels} lv "
                 f"(team syncs {int(self.fwd.sync.sum())}+{int(self.bwd.sync.sum())})")
@@ -172,6 +180,34 @@ def _nested_dissection(adj: sp.csr_matrix, leaf=8):
     return np.asarray(order, dtype=np.int64)
 
 
+def _peel_then_nd(sym: sp.csr_matrix, leaf=4):
+    """Elimination order for "chains hanging off a core" graphs (particle radial chains off the through-cell
+    variables in a DFN): repeatedly eliminate vertices of degree <= 1 (no fill, depth = chain length), then
+    nested dissection of what is left."""
+    n = sym.shape[0]
+    adj = [set(sym.indices[sym.indptr[i]:sym.indptr[i + 1]].tolist()) for i in range(n)]
+    alive = np.ones(n, bool)
+    order = []
+    stack = [i for i in range(n) if len(adj[i]) <= 1]
+    while stack:
+        u = stack.pop()
+        if not alive[u] or len(adj[u]) > 1:
+            continue
+        alive[u] = False
+        order.append(u)
+        for v in adj[u]:
+            adj[v].discard(u)
+            if alive[v] and len(adj[v]) <= 1:
+                stack.append(v)
+        adj[u] = set()
+    core = np.nonzero(alive)[0]
+    if len(core):
+        sub = sym[core][:, core].tocsr()
+        q = _nested_dissection(sub, leaf=leaf)
+        order.extend(core[q].tolist())
+    return np.asarray(order, dtype=np.int64)
+
+
 def _symbolic_fill(B: sp.csr_matrix):
     """Row patterns of L (strict lower) and U (upper incl. diagonal) of B without pivoting."""
     n = B.shape[0]
@@ -243,12 +279,12 @@ def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01) -> 
     rows = np.asarray(rows, np.int64)
     cols = np.asarray(cols, np.int64)
     candidates = []
-    names = ["nd", "COLAMD", "MMD_AT_PLUS_A"] if ordering == "auto" else [ordering]
+    names = ["peel_nd", "nd", "COLAMD", "MMD_AT_PLUS_A"] if ordering == "auto" else [ordering]
     A0 = sp.csc_matrix((np.asarray(samples[0], float), (rows, cols)), shape=(n, n))
     pat = sp.csr_matrix((np.ones(len(rows)), (rows, cols)), shape=(n, n))
     for name in names:
         try:
-            if name == "nd":
+            if name in ("nd", "peel_nd"):
                 # row permutation first: a maximum transversal from a pivoting LU so that the
                 # diagonal of A[perm_r] is structurally and numerically sound, then a symmetric ND
                 lu0 = spla.splu(A0, permc_spec="NATURAL", diag_pivot_thresh=diag_pivot_thresh)
@@ -259,7 +295,7 @@ def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01) -> 
                 sym = (Bp + Bp.T).tocsr()
                 sym.setdiag(0)
                 sym.eliminate_zeros()
-                q = _nested_dissection(sym)
+                q = _nested_dissection(sym) if name == "nd" else _peel_then_nd(sym)
                 perm_r = pr[q]
                 perm_c = q
             else:
@@ -276,11 +312,9 @@ def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01) -> 
     best = None
     for name, perm_r, perm_c in candidates:
         s = _build(n, rows, cols, perm_r, perm_c, name)
-        # cost proxy: team barriers dominate the numeric phase
-        # cost proxy (cycles per step): ~10 triangular solves per factorisation; a level costs a barrier plus a
-        # shared-memory round trip, the values and tables must stay on chip (nnz_lu weighs heavily)
-        score = (s.factor.n_levels + 10 * (s.fwd.n_levels + s.bwd.n_levels)) * 80 \
-            + (len(s.factor.op_a) + 10 * (len(s.fwd.op_a) + len(s.bwd.op_a))) / 4 + 40.0 * s.nnz_lu
+        # cost proxy (cycles per factorisation interval): ~30 triangular solves per factorisation (measured on the
+        # battery models); the L+U values and the solve stream must stay in shared memory (8 + ~6 bytes per entry)
+        score = 30.0 * s.est_cycles_solve + s.est_cycles_factor + 30.0 * s.nnz_lu
         ok = all(_validate(s, rows, cols, np.asarray(v, float)) < 1e-6 for v in samples)
         if not ok:
             continue
@@ -375,8 +409,8 @@ def _build(n, rows, cols, perm_r, perm_c, name) -> SymbolicLU:
         blv.setdefault(lv, []).append((i, int(perm_c[i]), ops))
         sflops += 2 * len(ops) + 1
     bwd = _jds([blv.get(l, []) for l in range(max(blv) + 1)], nnz_lu, n)
-    return SymbolicLU(n, nnz_lu, np.asarray(perm_r), np.asarray(perm_c), slot_of, a_slot, diag_slot,
-                      factor, fwd, bwd, flops, sflops, name)
+    return build_streams(SymbolicLU(n, nnz_lu, np.asarray(perm_r), np.asarray(perm_c), slot_of, a_slot, diag_slot,
+                                    factor, fwd, bwd, flops, sflops, name))
 
 
 # ---------------------------------------------------------------------------
@@ -431,8 +465,199 @@ def _validate(s: SymbolicLU, rows, cols, vals):
     xref = rng.standard_normal(s.n)
     b = A @ xref
     with np.errstate(all="ignore"):
-        lu = numeric_factor(s, vals)
-        x = numeric_solve(s, lu, b)
+        lu = stream_factor(s, vals)
+        x = stream_solve(s, lu, b)
     if not np.all(np.isfinite(x)):
         return np.inf
     return float(np.max(np.abs(x - xref)) / np.max(np.abs(xref)))
+
+
+# ---------------------------------------------------------------------------
+# packed 32-bit "streams" consumed by the device kernels (pbgpu_ida.cuh)
+# ---------------------------------------------------------------------------
+# A stream is a sequence of records  [meta][task word x nt][operand word x nt x ml]  (ELL inside a record:
+# operand p of task q at  base + 1 + nt + p*nt + q).  The next record starts right after, so a kernel walks the
+# stream with one running offset and no other table.  Tasks of one dependency level are split into up to three
+# records by length (bounded ELL padding); only the last record of a level carries the END flag (barrier).
+#   meta         = nt | ml << 16 | flags << 28      flags: 1 = END of level, 2 = backward-solve record (scale by 1/u_ii),
+#                                                          4 = team barrier needed after the level (factor stream),
+#                                                          8 = GROUP mode (32/nt lanes per task + shuffle reduction)
+#   solve task   = row | diag_slot << 16            operand = lu_slot | w_index << 16
+#   factor task  = out_slot | aux << 16             operand = lu_slot_a | lu_slot_b << 16
+# Padding operands are (zero slot nnz_lu, zero index n / zero slot nnz_lu).
+F_END, F_BWD, F_TEAM, F_GROUP = 1, 2, 4, 8
+MAX_GROUPS = 3
+
+
+def _split_groups(tasks, lane=32):
+    """tasks: sorted by descending operand count. Returns a list of consecutive groups minimising padded size."""
+    n = len(tasks)
+    if n == 0:
+        return []
+    lens = [len(t[2]) for t in tasks]
+    # candidate cut positions: where the operand count changes (tasks are sorted by it)
+    cuts = sorted(set([0, n] + [i for i in range(1, n) if lens[i] != lens[i - 1]]))
+    best = {(0, 0): (0, None)}   # (cut index, groups used) -> (cost, prev)
+    for gi in range(1, MAX_GROUPS + 1):
+        for ci, c in enumerate(cuts[1:], 1):
+            cand = None
+            for pi in range(ci):
+                if (pi, gi - 1) not in best:
+                    continue
+                a = cuts[pi]
+                cost = best[(pi, gi - 1)][0] + (c - a) * (1 + lens[a]) + 24
+                if cand is None or cost < cand[0]:
+                    cand = (cost, pi)
+            if cand is not None:
+                best[(ci, gi)] = cand
+    last = len(cuts) - 1
+    g = min((gi for gi in range(1, MAX_GROUPS + 1) if (last, gi) in best), key=lambda gi: best[(last, gi)][0])
+    out, ci = [], last
+    while ci > 0:
+        pi = best[(ci, g)][1]
+        out.append(tasks[cuts[pi]:cuts[ci]])
+        ci, g = pi, g - 1
+    return out[::-1]
+
+
+def _emit_records(words, level_tasks, flags, pad_word, task_word, pad_task, allow_group=True):
+    """Append the records of one dependency level. Returns (n_records, estimated cycles of the level for one warp).
+
+    Records with few long tasks use GROUP mode: nt is padded to a power of two <= 16 and 32/nt lanes share one
+    task (lane l takes operands l/nt, l/nt + 32/nt, ...: its words are base + nt + l + 32k, conflict-free),
+    followed by an xor-shuffle reduction.  ml is padded so that nt*ml is a multiple of 32."""
+    tasks = sorted(level_tasks, key=lambda t: -len(t[2]))
+    groups = _split_groups(tasks)
+    cyc = 0
+    for gi, grp in enumerate(groups):
+        nt, ml = len(grp), len(grp[0][2])
+        fl = flags | (F_END if gi == len(groups) - 1 else 0)
+        ntp = 1
+        while ntp < nt:
+            ntp *= 2
+        if allow_group and ntp <= 16 and ml >= 3:
+            g = 32 // ntp
+            mlp = ((ml + g - 1) // g) * g
+            fl |= F_GROUP
+            words.append(ntp | (mlp << 16) | (fl << 28))
+            for q in range(ntp):
+                words.append(task_word(grp[q]) if q < nt else pad_task)
+            for p in range(mlp):
+                for q in range(ntp):
+                    ops = grp[q][2] if q < nt else ()
+                    words.append((ops[p][0] | (ops[p][1] << 16)) if len(ops) > p else pad_word)
+            k = mlp // g
+            sh = {1: 5, 2: 4, 4: 3, 8: 2, 16: 1}[ntp]
+            cyc += 60 + 12 * k + 28 * sh
+            continue
+        assert nt < 65536 and ml < 4096
+        words.append(nt | (ml << 16) | (fl << 28))
+        for t in grp:
+            words.append(task_word(t))
+        for p in range(ml):
+            for t in grp:
+                words.append((t[2][p][0] | (t[2][p][1] << 16)) if len(t[2]) > p else pad_word)
+        cyc += 35 * ml + 25 * ((nt + 31) // 32)
+    return len(groups), cyc + 45
+
+
+def build_streams(s: SymbolicLU, team=128):
+    """Fill s.solve_stream / s.factor_stream (and the cycle estimates used to rank orderings)."""
+    n, nz = s.n, s.nnz_lu
+    assert nz + 3 < 0xFFFE and n + 1 < 0xFFFF, "16-bit packed indices: pattern too large"
+    one_slot = nz + 1                     # lu[nnz_lu] = 0.0, lu[nnz_lu + 1] = 1.0 (set once by the kernel)
+
+    def level_tasks(j: JDS, lv):
+        t0, nt, ob, ml = (int(x) for x in j.lev_meta[lv])
+        ml &= 0xFFFF
+        out = []
+        for q in range(nt):
+            ops = []
+            for p in range(ml):
+                a, b = int(j.op_a[ob + p * nt + q]), int(j.op_b[ob + p * nt + q])
+                if a != nz:               # drop ELL padding of the JDS tables
+                    ops.append((a, b))
+            out.append((int(j.task_out[t0 + q]), int(j.task_aux[t0 + q]), ops))
+        return out
+
+    words, nrec, cyc = [], 0, 0
+    for lv in range(s.fwd.n_levels):
+        tasks = [t for t in level_tasks(s.fwd, lv) if t[2]]   # rows without L entries: w = gathered b already
+        if not tasks:
+            continue
+        r, c = _emit_records(words, tasks, 0, nz | (n << 16), lambda t: t[0] | (one_slot << 16), n | (nz << 16))
+        nrec, cyc = nrec + r, cyc + c
+    for lv in range(s.bwd.n_levels):
+        tasks = level_tasks(s.bwd, lv)
+        r, c = _emit_records(words, tasks, F_BWD, nz | (n << 16), lambda t: t[0] | (int(s.diag_slot[t[0]]) << 16),
+                             n | (nz << 16))
+        nrec, cyc = nrec + r, cyc + c
+    s.solve_stream = np.asarray(words, dtype=np.uint32)
+    s.n_solve_records, s.est_cycles_solve = nrec, cyc
+
+    words, nrec, cyc = [], 0, 0
+    nlev = s.factor.n_levels
+    sizes = [int(s.factor.lev_meta[lv][1]) for lv in range(nlev)]
+    for lv in range(nlev):
+        tasks = level_tasks(s.factor, lv)
+        nxt = sizes[lv + 1] if lv + 1 < nlev else 10 ** 9
+        fl = 0 if (sizes[lv] <= 32 and nxt <= 32) else F_TEAM
+        # factor pad task: out = the spare slot nnz_lu + 2 (scratch), written as a U entry
+        r, c = _emit_records(words, tasks, fl, nz | (nz << 16), lambda t: t[0] | (t[1] << 16), (nz + 2) | (AUX_U << 16),
+                             allow_group=(fl == 0))
+        # wide levels are spread over the whole team
+        nrec, cyc = nrec + r, cyc + (c if sizes[lv] <= 32 else 45 + (c - 45) * 32 // team + 40)
+    s.factor_stream = np.asarray(words, dtype=np.uint32)
+    s.n_factor_records, s.est_cycles_factor = nrec, cyc
+    return s
+
+
+def _walk(stream):
+    off = 0
+    while off < len(stream):
+        meta = int(stream[off])
+        nt, ml, fl = meta & 0xFFFF, (meta >> 16) & 0xFFF, meta >> 28
+        yield off, nt, ml, fl
+        off += 1 + nt * (1 + ml)
+
+
+def stream_factor(s: SymbolicLU, a_vals):
+    """numpy emulation of the device factorisation driven by the packed stream (validation of the tables)."""
+    lu = np.zeros(s.nnz_lu + 3)
+    lu[s.nnz_lu + 1] = 1.0
+    np.add.at(lu, s.a_slot, a_vals)
+    st = s.factor_stream
+    for off, nt, ml, fl in _walk(st):
+        tw = st[off + 1:off + 1 + nt].astype(np.int64)
+        out, aux = tw & 0xFFFF, tw >> 16
+        acc = lu[out].copy()
+        for p in range(ml):
+            ow = st[off + 1 + nt + p * nt:off + 1 + nt + (p + 1) * nt].astype(np.int64)
+            acc -= lu[ow & 0xFFFF] * lu[ow >> 16]
+        for q in range(nt):
+            if aux[q] == AUX_U:
+                lu[out[q]] = acc[q]
+            elif aux[q] == AUX_DIAG:
+                lu[out[q]] = 1.0 / acc[q]
+            else:
+                lu[out[q]] = acc[q] * lu[aux[q]]
+    return lu
+
+
+def stream_solve(s: SymbolicLU, lu, b):
+    w = np.zeros(s.n + 1)
+    w[:s.n] = b[s.perm_r]
+    st = s.solve_stream
+    for off, nt, ml, fl in _walk(st):
+        tw = st[off + 1:off + 1 + nt].astype(np.int64)
+        row, dg = tw & 0xFFFF, tw >> 16
+        acc = w[row].copy()
+        for p in range(ml):
+            ow = st[off + 1 + nt + p * nt:off + 1 + nt + (p + 1) * nt].astype(np.int64)
+            acc -= lu[ow & 0xFFFF] * w[ow >> 16]
+        if fl & F_BWD:
+            acc *= lu[dg]
+        w[row] = acc
+    x = np.empty(s.n)
+    x[s.perm_c] = w[:s.n]
+    return x

@@ -25,7 +25,7 @@ def build_emu(bundle, force=False):
     if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:
         return out
     cmd = ["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", "-ffp-contract=off",
-           f"-DPBM_HEADER=\"{header}\"", f"-I{build.CSRC}", f"-I{build.ROOT}/include", srcs[0], "-o", out]
+           f"-DPBM_HEADER=\"{header}\"", f"-DPB_GLOBAL_VEC={1 if bundle.n_states > 256 else 0}", f"-I{build.CSRC}", f"-I{build.ROOT}/include", srcs[0], "-o", out]
     subprocess.run(cmd, check=True)
     with open(stamp, "w") as f:
         f.write(dig)

@@ -16,9 +16,9 @@
 #include "pbgpu_ida.cuh"
 
 extern "C" int emu_solve(const pbgpu_launch* L) {
-  double* sm = (double*)calloc(PB_SMEM_DOUBLES, sizeof(double));
+  double* sm = (double*)calloc(PB_SMEM_DOUBLES + PB_SCRATCH_DOUBLES + 1, sizeof(double));
   pb_sys S;
-  pb_sys_init(S, sm, *L);
+  pb_sys_init(S, sm, PB_GLOBAL_VEC ? sm + PB_SMEM_DOUBLES : sm, *L);
   for (int sys = 0; sys < L->n_sys; sys++) pb_solve_system(S, *L, sys);
   free(sm);
   return 0;
@@ -31,10 +31,12 @@ extern "C" void emu_sizes(int* out) {
 
 // which: 0 res, 1 jac (CSC order), 2 events, 3 ic, 4 vars, 5 (J - cj M) x = y2
 extern "C" int emu_eval(int which, const double* y, const double* p, double t, double cj, const double* y2, double* out) {
-  double* sm = (double*)calloc(PB_SMEM_DOUBLES, sizeof(double));
+  double* sm = (double*)calloc(PB_SMEM_DOUBLES + PB_SCRATCH_DOUBLES + 1, sizeof(double));
   pb_sys S;
   S.sm = sm;
+  S.gv = PB_GLOBAL_VEC ? sm + PB_SMEM_DOUBLES : sm;
   S.team.red = sm + PB_OFF_RED;
+  pb_sys_tables(S);
   if (y) memcpy(S_YY(S), y, sizeof(double) * PBM_N);
   memcpy(S_P(S), p, sizeof(double) * PBM_NP_REAL);
   int rc = 0;
@@ -42,7 +44,7 @@ extern "C" int emu_eval(int which, const double* y, const double* p, double t, d
     case 0: pbm_res(S_YY(S), S_P(S), t, cj, out, S_TMP(S)); break;
     case 1:
       memset(S_LU(S), 0, sizeof(double) * PBM_NNZ_LU);
-      pbm_jac(S_YY(S), S_P(S), t, cj, S_LU(S), S_TMP(S));
+      pbm_jac(S_YY(S), S_P(S), t, cj, S_LU(S), S_TMPJ(S));
       for (int k = 0; k < PBM_NNZ; k++) out[k] = S_LU(S)[pbm_ent_slot[k]];
       break;
     case 2:
