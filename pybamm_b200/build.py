@@ -93,11 +93,12 @@ def build_model(bundle: ModelBundle, force=False, team=None, verbose=False, prof
     if team is None:
         team = default_team(bundle)
     gvec = 1 if bundle.n_states > 256 else 0   # streamed vectors in global scratch for large models (pbgpu_ida.cuh)
-    dig = _src_digest(srcs) + f"-t{team}-g{gvec}-p{int(profile)}-" + hashlib.sha256(" ".join(NVCC_FLAGS).encode()).hexdigest()[:8]
+    min_teams = 2 if gvec else 1               # register cap: two large teams per SM (65536 / (2 * team) registers each)
+    dig = _src_digest(srcs) + f"-t{team}-g{gvec}-m{min_teams}-p{int(profile)}-" + hashlib.sha256(" ".join(NVCC_FLAGS).encode()).hexdigest()[:8]
     stamp = out + ".stamp"
     if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:
         return out
-    cmd = [NVCC] + NVCC_FLAGS + [f"-DPBM_HEADER=\"{header}\"", f"-DPB_TEAM_SIZE={team}", f"-DPB_GLOBAL_VEC={gvec}", f"-I{inc}", f"-I{CSRC}",
+    cmd = [NVCC] + NVCC_FLAGS + [f"-DPBM_HEADER=\"{header}\"", f"-DPB_TEAM_SIZE={team}", f"-DPB_GLOBAL_VEC={gvec}", f"-DPB_MIN_TEAMS={min_teams}", f"-I{inc}", f"-I{CSRC}",
                                  kernel_srcs[0], "-o", out] + ([f"-DPB_PROFILE={int(profile)}"] if profile else [])
     r = subprocess.run(cmd, capture_output=True, text=True)
     log = r.stdout + r.stderr
@@ -113,15 +114,8 @@ def build_model(bundle: ModelBundle, force=False, team=None, verbose=False, prof
 
 
 def default_team(bundle: ModelBundle) -> int:
-    """Threads per system: one warp for small models, a CTA of several warps for large ones."""
-    n = bundle.n_states
-    if n <= 128:
-        return 32
-    if n <= 512:
-        return 64
-    if n <= 2048:
-        return 128
-    return 256
+    """Threads per system (codegen.default_team: the SEQ solve stream is laid out for it)."""
+    return codegen.default_team(bundle.n_states)
 
 
 def build_api(force=False):

@@ -249,11 +249,64 @@ def sample_matrices(bundle, p_nominal=None, n_samples=2, seed=0):
     return out
 
 
+def emit_solve_program(sym: slu.SymbolicLU) -> str:
+    """The triangular solves as straight-line code: one specialised call per record of the solve stream (record shapes
+    are compile-time constants, so the device code has no record decoding, no operand loops and every load of a
+    record can be issued up front).  Expanded inside pb_lu_solve (pbgpu_ida.cuh), which defines st, lu, w."""
+    out, open_narrow = [], False
+    for r in sym.solve_program:
+        boff = r["offset"] + slu.SEQ_HDR + r["nblocks"]
+        calls = []
+        for v in range(r["nblocks"]):
+            nt = r["desc"][v] & 0xFFFF
+            if r["kind"] == 1:
+                G, mlg = r["param"] & 0xFF, r["param"] >> 8
+                call = f"pb_par_rec<{nt}, {G}, {mlg}, {r['mode']}>(st + {boff}, lu, w);"
+                boff += (1 + mlg) * nt
+            elif r["kind"] == 2:
+                call = f"pb_chain_rec<{r['mode'] & 1}>(st + {boff}, {nt}, lu, w);"
+                boff += 3 * nt
+            else:
+                call = f"pb_seq_rec<{r['mode'] & 1}>(st + {boff}, {nt}, lu, w);"
+                boff += nt * (r["desc"][v] >> 16)
+            calls.append((r["first_warp"] + v, call))
+        if r.get("narrow"):
+            if not open_narrow:
+                out.append("if (PB_WARP == 0) {")
+                open_narrow = True
+            out.append("  " + calls[0][1])
+            if r["sync"] == 1:
+                out.append("  PB_SYNCWARP();")
+            else:
+                out.append("}")
+                out.append("PB_SYNC();")
+                open_narrow = False
+        else:
+            assert not open_narrow
+            out.append(" else ".join(f"if (PB_WARP == {wv}) {{ {c} }}" for wv, c in calls))
+            if r["sync"] == 2:
+                out.append("PB_SYNC();")
+            elif r["sync"] == 1:
+                out.append("PB_SYNCWARP();")
+    assert not open_narrow
+    return "#define PBM_SOLVE_PROGRAM \\\n  " + " \\\n  ".join(out) + "\n"
+
+
+def default_team(n_states: int) -> int:
+    """Threads per system: one warp for small models, a CTA of several warps for large ones."""
+    if n_states <= 128:
+        return 32
+    if n_states <= 512:
+        return 64
+    return 256      # DFN-sized and larger: 8 warps per team, two teams per SM (128 registers per thread)
+
+
 def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
     """Return (source_text, info dict). The text is a header included by the integrator
     translation unit (CUDA) or the oracle model shim (C)."""
     if dialect == "cuda" and sym is None:
-        sym = slu.analyse(bundle.n_states, bundle.jac_rows, bundle.jac_cols, sample_matrices(bundle))
+        sym = slu.analyse(bundle.n_states, bundle.jac_rows, bundle.jac_cols, sample_matrices(bundle),
+                          team=min(default_team(bundle.n_states), 128))
     progs = model_functions(bundle, sym, dialect)
     n_tmp = max(p.n_tmp for p in progs.values())
     n_var = progs["vars"].n_out
@@ -298,13 +351,16 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
         lines.append(f"#define PBM_FAC_NLEV {sym.factor.n_levels}")
         lines.append(f"#define PBM_FWD_NLEV {sym.fwd.n_levels}")
         lines.append(f"#define PBM_BWD_NLEV {sym.bwd.n_levels}")
-        lines.append(f"#define PBM_SLV_WORDS {len(sym.solve_stream)}")
+        lines.append(f"#define PBM_SLV_WORDS {sym.n_solve_words}")
+        lines.append(f"#define PBM_SLV_ALLOC {len(sym.solve_stream)}")
         lines.append(f"#define PBM_SLV_NREC {sym.n_solve_records}")
+        lines.append(f"#define PBM_LU_TEAM_MIN {sym.seq_info['team_min']}")
         lines.append(f"#define PBM_FAC_WORDS {len(sym.factor_stream)}")
         lines.append(f"#define PBM_FAC_NREC {sym.n_factor_records}")
         lines.append(f"#define PBM_FAC_SMEM {1 if 4 * len(sym.factor_stream) <= FACTOR_STREAM_SMEM_BUDGET else 0}")
         _emit_u32(lines, "pbm_slv_tab", sym.solve_stream)
         _emit_u32(lines, "pbm_fac_tab", sym.factor_stream)
+        lines.append(emit_solve_program(sym))
         out.append("\n".join(lines))
         out.append(f"#define PBM_FLOPS_FACTOR {sym.flops_factor}")
         out.append(f"#define PBM_FLOPS_SOLVE {sym.flops_solve}")
@@ -313,7 +369,9 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
                           solve_stream_words=len(sym.solve_stream), factor_stream_words=len(sym.factor_stream),
                           solve_records=sym.n_solve_records, factor_records=sym.n_factor_records,
                           est_cycles_solve=sym.est_cycles_solve, est_cycles_factor=sym.est_cycles_factor,
-                          flops_factor=sym.flops_factor, flops_solve=sym.flops_solve)
+                          flops_factor=sym.flops_factor, flops_solve=sym.flops_solve,
+                          seq_clusters=sym.seq_info["clusters"], seq_fwd_heights=sym.seq_info["fwd_heights"],
+                          seq_bwd_heights=sym.seq_info["bwd_heights"], seq_team_min=sym.seq_info["team_min"])
     else:
         rows = ", ".join(str(int(r)) for r in bundle.jac_rows)
         cols = ", ".join(str(int(c)) for c in bundle.jac_cols)

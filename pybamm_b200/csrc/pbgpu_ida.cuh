@@ -69,7 +69,7 @@
 #define PB_OFF_RED (PB_OFF_COEF + 32)
 #define PB_OFF_STATS (PB_OFF_RED + 64)
 #define PB_OFF_SLV (PB_OFF_STATS + 8)                          /* packed solve stream (u32 words) */
-#define PB_OFF_FAC (PB_OFF_SLV + (PBM_SLV_WORDS + 1) / 2)      /* packed factor stream when it fits (PBM_FAC_SMEM) */
+#define PB_OFF_FAC (PB_OFF_SLV + (PBM_SLV_ALLOC + 1) / 2)      /* packed factor stream when it fits (PBM_FAC_SMEM) */
 #if PBM_FAC_SMEM
 #define PB_SMEM_DOUBLES (PB_OFF_FAC + (PBM_FAC_WORDS + 1) / 2)
 #else
@@ -145,43 +145,17 @@ struct pb_sys {
 #endif
 
 // ---- static-pattern sparse LU (packed streams from pybamm_b200/symbolic_lu.py: build_streams) -------
-// A stream is a sequence of records [meta][task x nt][operand x nt x ml] walked with one running offset:
-//   meta = nt | ml << 16 | flags << 28;  flags: 1 END of a dependency level, 2 backward record, 4 team-wide level
-//   solve : task = row | diag_slot << 16, operand = lu_slot | w_index << 16
-//   factor: task = out_slot | aux << 16,  operand = lu_slot | lu_slot << 16
+// The factor stream is a sequence of records [meta][task x nt][operand x nt x ml] walked with one running offset:
+//   meta = nt | ml << 16 | flags << 28;  flags: 1 END of a dependency level, 4 team-wide level, 8 GROUP mode
+//   task = out_slot | aux << 16,  operand = lu_slot | lu_slot << 16
 // Padding operands point at lu[PBM_NNZ_LU] = 0 / w[PBM_N] = 0; lu[PBM_NNZ_LU + 1] = 1.
-// The solve stream lives in shared memory: a dependency level costs one shared-memory round trip, not a trip
-// to L2 for its indices.  Triangular solves are narrow (tens of rows per level), so warp 0 runs them alone
-// with __syncwarp between levels; the team meets again at the end.
+// The triangular solves (1000 per simulation against 40 factorisations) use the SEQ stream further down, which
+// lives in shared memory.
 #define PB_F_END 1u
 #define PB_F_BWD 2u
 #define PB_F_TEAM 4u
 #define PB_F_GROUP 8u
 
-// GROUP-mode partial sum of one record: 32/nt lanes share a task; lane l reads the operand words base + l + 32k
-// (k < ml*nt/32) and the partial sums of a task are combined with an xor-shuffle butterfly over lane strides
-// nt, 2nt, ... 16.  x is the vector the second operand index refers to (w for solves, lu for the factorisation).
-// Returns sum(lu[a] * x[b]) of the task lane & (nt - 1); valid in every lane.
-#ifndef PB_EMU
-static PB_DEV double pb_group_dot(const unsigned int* ops, const int nt, const int ml, const double* lu, const double* x) {
-  const int k_n = (ml * nt) >> 5;
-  const unsigned int* op = ops + PB_LANE;
-  double a0 = 0.0, a1 = 0.0;
-  int k = 0;
-  for (; k + 1 < k_n; k += 2) {
-    const unsigned int o0 = op[32 * k], o1 = op[32 * k + 32];
-    a0 += lu[o0 & 0xFFFFu] * x[o0 >> 16];
-    a1 += lu[o1 & 0xFFFFu] * x[o1 >> 16];
-  }
-  if (k < k_n) {
-    const unsigned int o0 = op[32 * k];
-    a0 += lu[o0 & 0xFFFFu] * x[o0 >> 16];
-  }
-  a0 += a1;
-  for (int o = nt; o < 32; o <<= 1) a0 += __shfl_xor_sync(0xffffffffu, a0, o);
-  return a0;
-}
-#endif
 #if PBM_FAC_SMEM
 #define PB_FAC_LD(x) (x)
 #else
@@ -298,9 +272,169 @@ static PB_DEV int pb_lu_factor(pb_sys& S) {
   return pb_team_max(S.team, bad) != 0.0;
 }
 
+// ---- SEQ triangular solves (stream layout: pybamm_b200/symbolic_lu.py, build_seq_solve_stream) ------------------
+// One thread walks one cluster of the elimination tree (a particle chain, a separator) row by row; the only
+// loop-carried dependency is the w[] value it has just stored.  Everything that does not depend on it -- the next
+// task's header, its first operand word and that operand's L/U value -- is fetched one task ahead, so a chain row
+// costs one LDS + one DFMA (+ one DMUL backward) instead of a dependency level of the interpreter.
+#define PB_SEQ_HDR 4
+#define PB_PAR_ADD 2u
+#define PB_PAR_DIAG 4u
+
+template <int BWD>
+static PB_DEV void pb_seq_thread(const unsigned int* PB_RESTRICT p, const int nt, const double* PB_RESTRICT lu,
+                                 double* PB_RESTRICT w) {
+  const int ntask = (int)p[0];
+  p += nt;
+  unsigned int hdr = p[0], o0 = p[nt];
+  double l0 = lu[o0 & 0xFFFFu];
+  double ld = BWD ? lu[hdr & 0xFFFFu] : 1.0;
+  for (int k = 0; k < ntask; k++) {
+    const int row = (int)(hdr & 0xFFFFu), ml = (int)(hdr >> 16);
+    const unsigned int* pn = p + (1 + ml) * nt;
+    const double wv0 = w[o0 >> 16], wr = w[row];       // the chain-critical loads first
+    const unsigned int hdr_n = pn[0], o0n = pn[nt];    // prefetch of the next task (independent of the chain)
+    double acc = wr - l0 * wv0;
+    if (ml > 1) {
+      // operands 1..ml-1 in chunks of four: the words of chunk c+1 are in flight while chunk c multiplies
+      const unsigned int* q = p + 2 * nt;
+      unsigned int a0 = q[0], a1 = q[nt], a2 = q[2 * nt], a3 = q[3 * nt];
+      double acc1 = 0.0;
+      for (int j = 1; j < ml; j += 4) {
+        q += 4 * nt;
+        const double x0 = lu[a0 & 0xFFFFu], y0 = w[a0 >> 16], x1 = lu[a1 & 0xFFFFu], y1 = w[a1 >> 16];
+        const double x2 = lu[a2 & 0xFFFFu], y2 = w[a2 >> 16], x3 = lu[a3 & 0xFFFFu], y3 = w[a3 >> 16];
+        a0 = q[0];
+        a1 = q[nt];
+        a2 = q[2 * nt];
+        a3 = q[3 * nt];
+        acc -= x0 * y0;
+        acc1 -= x1 * y1;
+        acc -= x2 * y2;
+        acc1 -= x3 * y3;
+      }
+      acc += acc1;
+    }
+    const double l0n = lu[o0n & 0xFFFFu];
+    double ldn = 1.0;
+    if (BWD) {
+      ldn = lu[hdr_n & 0xFFFFu];
+      acc *= ld;
+    }
+    w[row] = acc;
+    hdr = hdr_n;
+    o0 = o0n;
+    l0 = l0n;
+    ld = ldn;
+    p = pn;
+  }
+}
+
+// ---- specialised records (device): shapes are template parameters, calls come from PBM_SOLVE_PROGRAM ------------
+#ifndef PB_EMU
+// PAR record: NT lanes, G lanes per row, MLG operands per lane.  Partial dot product, xor-butterfly over the G lanes,
+// w[row] = base +/- sum with base = w[row] or w[row] / u_ii.  Every lane reads before any lane writes (rows of one
+// cluster read each other's old values through the explicit inverse block).
+template <int NT, int G, int MLG, unsigned int MODE>
+static PB_DEV void pb_par_rec(const unsigned int* PB_RESTRICT blk, const double* PB_RESTRICT lu, double* PB_RESTRICT w) {
+  constexpr unsigned int mask = NT == 32 ? 0xffffffffu : ((1u << NT) - 1u);
+  if (PB_LANE < NT) {
+    const unsigned int* p = blk + PB_LANE;
+    const int row = (int)p[0];
+    unsigned int a[MLG > 0 ? MLG : 1];
+#pragma unroll
+    for (int j = 0; j < MLG; j++) a[j] = p[(1 + j) * NT];
+    const double wr = w[row];
+    const double ld = (MODE & PB_PAR_DIAG) ? lu[row] : 1.0;
+    double x[MLG > 0 ? MLG : 1], y[MLG > 0 ? MLG : 1];
+#pragma unroll
+    for (int j = 0; j < MLG; j++) {
+      x[j] = lu[a[j] & 0xFFFFu];
+      y[j] = w[a[j] >> 16];
+    }
+    double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+    for (int j = 0; j < MLG; j += 2) {
+      s0 = fma(x[j], y[j], s0);
+      if (j + 1 < MLG) s1 = fma(x[j + 1], y[j + 1], s1);
+    }
+    double sum = MLG > 1 ? s0 + s1 : s0;
+#pragma unroll
+    for (int o = 1; o < G; o <<= 1) sum += __shfl_xor_sync(mask, sum, o);
+    const double base = (MODE & PB_PAR_DIAG) ? wr * ld : wr;
+    const double acc = (MODE & PB_PAR_ADD) ? base + sum : base - sum;
+    __syncwarp(mask);
+    if (G == 1 || (PB_LANE & (G - 1)) == 0) w[row] = acc;
+  }
+}
+
+// CHAIN record: one lane per bidiagonal chain of K consecutive rows.  All operands are independent of the recurrence
+// and are loaded in batches ahead of it: the chain costs one DFMA per row.
+template <int BWD>
+static PB_DEV void pb_chain_rec(const unsigned int* PB_RESTRICT blk, const int nt, const double* PB_RESTRICT lu,
+                                double* PB_RESTRICT w) {
+  if (PB_LANE >= nt) return;
+  const unsigned int h = blk[PB_LANE], sl = blk[nt + PB_LANE];
+  const int r0 = (int)(h & 0xFFFFu), K = (int)(h >> 16);
+  constexpr int B = 6;
+  if (!BWD) {
+    const double* l = lu + (sl & 0xFFFFu) - 1;   // l[k] = L(r0 + k, r0 + k - 1)
+    double* z = w + r0;
+    double prev = z[0];
+    for (int k = 1; k < K; k += B) {
+      double wv[B], lv[B];
+#pragma unroll
+      for (int j = 0; j < B; j++)
+        if (k + j < K) {
+          wv[j] = z[k + j];
+          lv[j] = l[k + j];
+        }
+#pragma unroll
+      for (int j = 0; j < B; j++)
+        if (k + j < K) {
+          prev = fma(-lv[j], prev, wv[j]);
+          z[k + j] = prev;
+        }
+    }
+  } else {
+    const double* u = lu + (sl >> 16);           // u[k] = U(r0 + k, next row)
+    const double* d = lu + r0;                   // 1 / u_kk
+    double* z = w + r0;
+    double nxt = w[blk[2 * nt + PB_LANE]];
+    for (int k = K - 1; k >= 0; k -= B) {
+      double zd[B], ud[B];
+#pragma unroll
+      for (int j = 0; j < B; j++)
+        if (k - j >= 0) {
+          const double dd = d[k - j];
+          zd[j] = z[k - j] * dd;
+          ud[j] = u[k - j] * dd;
+        }
+#pragma unroll
+      for (int j = 0; j < B; j++)
+        if (k - j >= 0) {
+          nxt = fma(-ud[j], nxt, zd[j]);
+          z[k - j] = nxt;
+        }
+    }
+  }
+}
+
+template <int BWD>
+static PB_DEV void pb_seq_rec(const unsigned int* PB_RESTRICT blk, const int nt, const double* PB_RESTRICT lu,
+                              double* PB_RESTRICT w) {
+  if (PB_LANE < nt) pb_seq_thread<BWD>(blk + PB_LANE, nt, lu, w);
+}
+#endif
+
 // Solve (J - cj M) x = b in place (b: shared vector), w = S_W scratch. Ends with a team barrier.
-static PB_DEV void pb_lu_solve(pb_sys& S, double* b) {
+// TRACE (tools/gpu_cycles.py only): thread 0 stores the clock64() cycles of gather, every record, scatter in trace[].
+template <int TRACE>
+static PB_DEV void pb_lu_solve_t(pb_sys& S, double* b, double* trace) {
   const double* lu = S_LU(S);
+  long long tr0 = 0;
+  int trk = 0;
+  if (TRACE) tr0 = clock64();
   double* w = S_W(S);
 #if defined(PB_PROFILE) && PB_PROFILE == 2
   PB_T0(tga_);
@@ -308,73 +442,91 @@ static PB_DEV void pb_lu_solve(pb_sys& S, double* b) {
   for (int i = PB_TID; i < PBM_N; i += PB_TEAM) w[i] = b[(int)PB_LD(pbm_perm_r[i])];
   PB_SYNC();
 #if defined(PB_PROFILE) && PB_PROFILE == 2
-  PB_T1(S, tga_, 5);   // PB_PROFILE=2: slots 5/6/7 = gather / level loop / scatter of the triangular solves
+  PB_T1(S, tga_, 5);   // PB_PROFILE=2: slots 5/6/7 = gather / records / scatter of the triangular solves
   PB_T0(tlv_);
 #endif
-  if (PB_WARP == 0) {
+  if (TRACE) {
+    const long long t1 = clock64();
+    if (PB_TID == 0) trace[trk] = (double)(t1 - tr0);
+    trk++;
+    tr0 = t1;
+  }
+  {
+#ifndef PB_EMU
+    const unsigned int* PB_RESTRICT st = S.slv;
+    PBM_SOLVE_PROGRAM
+#else
     const unsigned int* st = S.slv;
     int off = 0;
-    unsigned int meta = st[0];
-    for (int rec = 0; rec < PBM_SLV_NREC; rec++) {
-      const int nt = (int)(meta & 0xFFFFu), ml = (int)((meta >> 16) & 0xFFFu);
-      const unsigned int fl = meta >> 28;
-      const int base = off + 1;
-      off = base + nt * (1 + ml);
-      if (rec + 1 < PBM_SLV_NREC) meta = st[off];
-      if (fl & PB_F_GROUP) {
-#ifndef PB_EMU
-        const unsigned int tw = st[base + (PB_LANE & (nt - 1))];
-        const double dot = pb_group_dot(st + base + nt, nt, ml, lu, w);
-        if (PB_LANE < nt) {
-          const int row = (int)(tw & 0xFFFFu);
-          double acc = w[row] - dot;
-          if (fl & PB_F_BWD) acc *= lu[tw >> 16];
-          w[row] = acc;
-        }
-#else
-        for (int q = 0; q < nt; q++) {
-          const unsigned int tw = st[base + q];
-          const int row = (int)(tw & 0xFFFFu);
-          double dot = 0.0;
-          for (int p = 0; p < ml; p++) {
-            const unsigned int o0 = st[base + nt + p * nt + q];
-            dot += lu[o0 & 0xFFFFu] * w[o0 >> 16];
+    while (off < PBM_SLV_WORDS) {   // host emulation: the generic interpreter of the same stream
+      const unsigned int h0 = st[off];
+      const int total = (int)st[off + 1];
+      const unsigned int kind = h0 & 0xFu, mode = (h0 >> 4) & 0xFu;
+      const int nb = (int)((h0 >> 16) & 0xFFu);
+      const unsigned int* body = st + off + PB_SEQ_HDR + nb;
+      if (kind == 0) {
+        for (int v = 0; v < nb; v++) {
+          const unsigned int d = st[off + PB_SEQ_HDR + v];
+          const int nt = (int)(d & 0xFFFFu), len = (int)(d >> 16);
+          for (int q = 0; q < nt; q++) {
+            if (mode & 1u) pb_seq_thread<1>(body + q, nt, lu, w);
+            else pb_seq_thread<0>(body + q, nt, lu, w);
           }
-          double acc = w[row] - dot;
-          if (fl & PB_F_BWD) acc *= lu[tw >> 16];
-          w[row] = acc;
+          body += nt * len;
         }
-#endif
-        if (fl & PB_F_END) PB_SYNCWARP();
-        continue;
+      } else if (kind == 2) {
+        for (int v = 0; v < nb; v++) {
+          const int nt = (int)st[off + PB_SEQ_HDR + v];
+          for (int q = 0; q < nt; q++) {
+            const int r0 = (int)(body[q] & 0xFFFFu), K = (int)(body[q] >> 16);
+            const int L0 = (int)(body[nt + q] & 0xFFFFu), U0 = (int)(body[nt + q] >> 16);
+            if (mode & 1u) {
+              double nxt = w[body[2 * nt + q]];
+              for (int k = K - 1; k >= 0; k--) {
+                nxt = (w[r0 + k] - lu[U0 + k] * nxt) * lu[r0 + k];
+                w[r0 + k] = nxt;
+              }
+            } else {
+              for (int k = 1; k < K; k++) w[r0 + k] -= lu[L0 + k - 1] * w[r0 + k - 1];
+            }
+          }
+          body += 3 * nt;
+        }
+      } else {
+        const unsigned int prm = st[off + 3];
+        const int G = (int)(prm & 0xFFu), mlg = (int)(prm >> 8);
+        for (int v = 0; v < nb; v++) {   // a block = a warp: all its lanes read before any of them writes
+          double accs[32];
+          int rws[32], na = 0;
+          const int nt = (int)st[off + PB_SEQ_HDR + v];
+          for (int g = 0; g < nt / G; g++) {
+            const int row = (int)body[g * G];
+            double sum = 0.0;
+            for (int l = g * G; l < (g + 1) * G; l++)
+              for (int j = 0; j < mlg; j++) {
+                const unsigned int a = body[(1 + j) * nt + l];
+                sum += lu[a & 0xFFFFu] * w[a >> 16];
+              }
+            const double base = (mode & PB_PAR_DIAG) ? w[row] * lu[row] : w[row];
+            rws[na] = row;
+            accs[na++] = (mode & PB_PAR_ADD) ? base + sum : base - sum;
+          }
+          body += (1 + mlg) * nt;
+          for (int k = 0; k < na; k++) w[rws[k]] = accs[k];
+        }
       }
-      for (int q = PB_LANE; q < nt; q += PB_LANES) {
-        const unsigned int tw = st[base + q];
-        const int row = (int)(tw & 0xFFFFu);
-        const unsigned int* op = st + base + nt + q;
-        double acc0 = w[row], acc1 = 0.0;
-        int p = 0;
-        for (; p + 1 < ml; p += 2) {
-          const unsigned int o0 = op[p * nt], o1 = op[(p + 1) * nt];
-          acc0 -= lu[o0 & 0xFFFFu] * w[o0 >> 16];
-          acc1 -= lu[o1 & 0xFFFFu] * w[o1 >> 16];
-        }
-        if (p < ml) {
-          const unsigned int o0 = op[p * nt];
-          acc0 -= lu[o0 & 0xFFFFu] * w[o0 >> 16];
-        }
-        double acc = acc0 + acc1;
-        if (fl & PB_F_BWD) acc *= lu[tw >> 16];
-        w[row] = acc;
-      }
-      if (fl & PB_F_END) PB_SYNCWARP();
+      off += total;
     }
+#endif
+  }
+  if (TRACE) {
+    const long long t1 = clock64();
+    if (PB_TID == 0) trace[trk] = (double)(t1 - tr0);
+    trk++;
+    tr0 = t1;
   }
 #if defined(PB_PROFILE) && PB_PROFILE == 2
   PB_T1(S, tlv_, 6);
-#endif
-  PB_SYNC();
-#if defined(PB_PROFILE) && PB_PROFILE == 2
   PB_T0(tsc_);
 #endif
   for (int i = PB_TID; i < PBM_N; i += PB_TEAM) b[(int)PB_LD(pbm_perm_c[i])] = w[i];
@@ -382,7 +534,9 @@ static PB_DEV void pb_lu_solve(pb_sys& S, double* b) {
 #if defined(PB_PROFILE) && PB_PROFILE == 2
   PB_T1(S, tsc_, 7);
 #endif
+  if (TRACE && PB_TID == 0) trace[trk] = (double)(clock64() - tr0);
 }
+static PB_DEV void pb_lu_solve(pb_sys& S, double* b) { pb_lu_solve_t<0>(S, b, nullptr); }
 
 // Evaluate J - cj*M at (t, y) into the LU value array and factor it.  ic_mode: replace the
 // differential rows by identity rows (the algebraic sub-block system of the IC Newton,
@@ -1440,7 +1594,7 @@ static PB_DEV void pb_sys_tables(pb_sys& S) {
     S_W(S)[PBM_N] = 0.0;
   }
   unsigned int* slv = (unsigned int*)(S.sm + PB_OFF_SLV);
-  for (int i = PB_TID; i < PBM_SLV_WORDS; i += PB_TEAM) slv[i] = PB_LD(pbm_slv_tab[i]);
+  for (int i = PB_TID; i < PBM_SLV_ALLOC; i += PB_TEAM) slv[i] = PB_LD(pbm_slv_tab[i]);
   S.slv = slv;
 #if PBM_FAC_SMEM
   unsigned int* fac = (unsigned int*)(S.sm + PB_OFF_FAC);

@@ -16,7 +16,12 @@
 #include PBM_HEADER
 #include "pbgpu_ida.cuh"
 
-extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE) pbgpu_solve_kernel(const pbgpu_launch L) {
+static_assert(PB_TEAM_SIZE >= PBM_LU_TEAM_MIN, "team smaller than the widest record of the SEQ solve stream");
+
+#ifndef PB_MIN_TEAMS
+#define PB_MIN_TEAMS 1
+#endif
+extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_solve_kernel(const pbgpu_launch L) {
   extern __shared__ double pb_smem[];
   __shared__ unsigned int next_sys;
   pb_sys S;
@@ -36,7 +41,7 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE) pbgpu_solve_kernel(co
 }
 
 // Evaluate generated functions / the LU for parity tests of the code generator (one team per system).
-extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE) pbgpu_eval_kernel(const pbgpu_eval_launch E) {
+extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_eval_kernel(const pbgpu_eval_launch E) {
   extern __shared__ double pb_smem[];
   pb_sys S;
   S.sm = pb_smem;
@@ -94,6 +99,59 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE) pbgpu_eval_kernel(con
         PB_SYNC();
         pb_lu_solve(S, out);
         for (int i = PB_TID; i < PBM_N && i < E.out_len; i += PB_TEAM) gout[i] = bad ? CUDART_NAN : out[i];
+      } break;
+      case 6: {   // clock64() cycles per call of the building blocks, measured in place (tools/gpu_cycles.py)
+        const int reps = 16;
+        long long c[6];
+        pb_lsetup(S, E.t, y, E.cj, 0);
+        long long t0 = clock64();
+        for (int r = 0; r < reps; r++) {
+          pbm_res(y, S_P(S), E.t, 0.0, out, S_TMP(S));
+          PB_SYNC();
+        }
+        c[0] = clock64() - t0;
+        for (int i = PB_TID; i < PBM_N; i += PB_TEAM) out[i] = E.y2[(size_t)sys * PBM_N + i];
+        PB_SYNC();
+        t0 = clock64();
+        for (int r = 0; r < reps; r++) pb_lu_solve(S, out);
+        c[1] = clock64() - t0;
+        t0 = clock64();
+        for (int r = 0; r < reps; r++) {
+          double* lu = S_LU(S);
+          for (int i = PB_TID; i < PBM_NFILL; i += PB_TEAM) lu[(int)PB_LD(pbm_fill[i])] = 0.0;
+          pbm_jac(y, S_P(S), E.t, E.cj, lu, S_TMPJ(S));
+          PB_SYNC();
+        }
+        c[2] = clock64() - t0;
+        t0 = clock64();
+        for (int r = 0; r < reps; r++) pb_lu_factor(S);   // refactoring a factor: same instruction stream, values irrelevant
+        c[3] = clock64() - t0;
+        S.rtol = 1e-8;
+        S.atol = E.y2;   // any readable vector of N doubles
+        t0 = clock64();
+        for (int r = 0; r < reps; r++) pb_ewt_set(S, y);
+        c[4] = clock64() - t0;
+        double acc = 0.0;
+        t0 = clock64();
+        for (int r = 0; r < reps; r++) acc += pb_wrms(S, S_PHI(S, r % 6));
+        c[5] = clock64() - t0;
+        if (PB_TID == 0) {
+          for (int k = 0; k < 6 && k < E.out_len; k++) gout[k] = (double)c[k] / reps;
+          if (E.out_len > 6) gout[6] = acc;
+        }
+        if (E.out_len >= 8 + 3) {
+          pb_lu_solve_t<1>(S, out, gout + 8);   // warm
+          pb_lu_solve_t<1>(S, out, gout + 8);
+        }
+      } break;
+      case 7: {   // profiling target: nothing but triangular solves (E.cj = repetitions), for ncu source-level sampling
+        pb_lsetup(S, E.t, y, 1.0, 0);
+        for (int i = PB_TID; i < PBM_N; i += PB_TEAM) out[i] = E.y2[(size_t)sys * PBM_N + i];
+        PB_SYNC();
+        const long long t0 = clock64();
+        const int reps = (int)E.cj;
+        for (int r = 0; r < reps; r++) pb_lu_solve(S, out);
+        if (PB_TID == 0 && E.out_len > 0) gout[0] = (double)(clock64() - t0) / reps;
       } break;
       default:
         break;

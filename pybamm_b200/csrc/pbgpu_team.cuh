@@ -33,6 +33,7 @@
 struct pb_team_ctx {
   double* red;  // unused
 };
+static inline long long clock64() { return 0; }   // cycle traces are device-only
 PB_FN double pb_team_sum(pb_team_ctx&, double x) { return x; }
 PB_FN double pb_team_max(pb_team_ctx&, double x) { return x; }
 #else

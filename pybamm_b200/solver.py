@@ -385,9 +385,9 @@ class BatchedIDASolver:
     def eval(self, which, y, p, t=0.0, cj=0.0, y2=None):
         self._ensure()
         D = self.desc
-        idx = {"res": 0, "jac": 1, "events": 2, "ic": 3, "vars": 4, "solve": 5}[which]
+        idx = {"res": 0, "jac": 1, "events": 2, "ic": 3, "vars": 4, "solve": 5, "cycles": 6, "solve_loop": 7}[which]
         out_len = {"res": D.n_states, "jac": D.nnz_jac, "events": max(D.n_events, 1), "ic": D.n_states,
-                   "vars": max(D.n_vars, 1), "solve": D.n_states}[which]
+                   "vars": max(D.n_vars, 1), "solve": D.n_states, "cycles": 128, "solve_loop": 8}[which]
         p = np.ascontiguousarray(np.atleast_2d(np.asarray(p, dtype=np.float64)))
         n_sys = p.shape[0]
         if y is not None:

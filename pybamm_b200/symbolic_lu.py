@@ -81,6 +81,15 @@ class SymbolicLU:
     n_factor_records: int = 0
     est_cycles_solve: int = 0
     est_cycles_factor: int = 0
+    Lrows: list = None                 # strict-lower pattern per row of B = P A Q
+    Urows: list = None                 # upper pattern (incl. diagonal) per row
+    seq_info: dict = None              # cluster statistics of the SEQ solve stream (see build_seq_solve_stream)
+    n_solve_words: int = 0             # words of the solve stream without the prefetch padding at its end
+    clusters: list = None              # rows of every elimination-tree cluster (_seq_clusters)
+    cl: np.ndarray = None              # row -> cluster
+    inv_cluster: np.ndarray = None     # cluster has explicit inverse diagonal blocks (slots ("Q", i, j) / ("P", i, j))
+    cluster_kind: list = None          # "chain" | "inv" | "seq" per cluster
+    solve_program: list = None         # the records of the solve stream as dicts (code generator input)
 
     def summary(self):
         return (f"n={self.n} nnz_lu={self.nnz_lu} ordering={self.ordering} streams: solve {len(self.solve_stream)} words/"
@@ -268,11 +277,13 @@ def _jds(levels_tasks, pad_a, pad_b, warp=32):
                np.asarray(task_out, i32), np.asarray(task_aux, i32), n_real)
 
 
+INV_MAX = 8         # clusters of 2..INV_MAX rows get explicit inverse diagonal blocks
+ONE = object()      # placeholder of the constant-one slot (nnz_lu + 1) while slots are still being handed out
 AUX_U = 0xFFFF      # factor task writes an off-diagonal U entry
 AUX_DIAG = 0xFFFE   # factor task writes a diagonal entry (stores the reciprocal)
 
 
-def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01) -> SymbolicLU:
+def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01, team=128) -> SymbolicLU:
     """rows/cols: structural pattern of A (every entry the numeric phase may set).
     samples: list of value arrays (same order as rows/cols) used to pick the pivot order
     and to validate it."""
@@ -311,7 +322,7 @@ def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01) -> 
             print(f"[symbolic_lu] ordering {name} failed: {e}")
     best = None
     for name, perm_r, perm_c in candidates:
-        s = _build(n, rows, cols, perm_r, perm_c, name)
+        s = _build(n, rows, cols, perm_r, perm_c, name, team=team)
         # cost proxy (cycles per factorisation interval): ~30 triangular solves per factorisation (measured on the
         # battery models); the L+U values and the solve stream must stay in shared memory (8 + ~6 bytes per entry)
         score = 30.0 * s.est_cycles_solve + s.est_cycles_factor + 30.0 * s.nnz_lu
@@ -325,7 +336,7 @@ def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01) -> 
     return best[1]
 
 
-def _build(n, rows, cols, perm_r, perm_c, name) -> SymbolicLU:
+def _build(n, rows, cols, perm_r, perm_c, name, team=128) -> SymbolicLU:
     inv_r = np.empty(n, np.int64)
     inv_r[perm_r] = np.arange(n)
     inv_c = np.empty(n, np.int64)
@@ -334,13 +345,47 @@ def _build(n, rows, cols, perm_r, perm_c, name) -> SymbolicLU:
     B = sp.csr_matrix((np.ones(len(rows)), (bi, bj)), shape=(n, n))
     Lrows, Urows = _symbolic_fill(B)
     # slots: row-major over (L row, U row)
-    slot_of = {}
+    # the diagonal of row i sits in slot i (the backward solve reads 1/u_ii as lu[row] without a table look-up)
+    slot_of = {(i, i): i for i in range(n)}
+    clusters, cl, kinds = _seq_clusters(n, Lrows, Urows)
+    for c, rws in enumerate(clusters):     # chains: L entries in consecutive slots, then U entries in consecutive slots
+        if kinds[c] == "chain":
+            for k in range(1, len(rws)):
+                slot_of[(rws[k], rws[k - 1])] = len(slot_of)
+            for i in rws:
+                slot_of[(i, Urows[i][1])] = len(slot_of)
     for i in range(n):
         for j in Lrows[i]:
-            slot_of[(i, j)] = len(slot_of)
+            slot_of.setdefault((i, j), len(slot_of))
         for j in Urows[i]:
-            slot_of[(i, j)] = len(slot_of)
+            slot_of.setdefault((i, j), len(slot_of))
+    # small clusters of the elimination tree (separators, leaves) get the explicit inverse of their diagonal block:
+    # Q = L_CC^-1 (strict lower part) and P = U_CC^-1 (strict upper part) in extra slots, computed by extra factor
+    # tasks, so that the rows of a cluster are solved side by side instead of one after the other (PAR records below)
+    inv_cluster = np.array([kinds[c] == "inv" and len(clusters[c]) >= 2 for c in range(len(clusters))])
+    q_pairs, p_pairs = {}, {}         # (i, j) -> operand pairs of the factor task
+    for c, rws in enumerate(clusters):
+        if not inv_cluster[c]:
+            continue
+        for jj, j in enumerate(rws):                  # Q[i][j] = -(L[i][j] + sum_{j<k<i} L[i][k] Q[k][j])
+            for i in rws[jj + 1:]:
+                pr = [(slot_of[(i, j)], ONE)] if (i, j) in slot_of else []
+                pr += [(slot_of[(i, k)], slot_of[("Q", k, j)]) for k in rws[jj + 1:] if k < i and (i, k) in slot_of
+                       and ("Q", k, j) in slot_of]
+                if pr:
+                    slot_of[("Q", i, j)] = len(slot_of)
+                    q_pairs[(i, j)] = pr
+        for jj, j in enumerate(rws):                  # P[i][j] = -1/u_ii * sum_{i<k<=j} U[i][k] P[k][j],  P[j][j] = 1/u_jj
+            for i in reversed(rws[:jj]):
+                pr = [(slot_of[(i, k)], slot_of[(j, j)] if k == j else slot_of[("P", k, j)]) for k in rws if i < k <= j
+                      and (i, k) in slot_of and (k == j or ("P", k, j) in slot_of)]
+                if pr:
+                    slot_of[("P", i, j)] = len(slot_of)
+                    p_pairs[(i, j)] = pr
     nnz_lu = len(slot_of)
+    for d in (q_pairs, p_pairs):
+        for key, pr in d.items():
+            d[key] = [(a, nnz_lu + 1 if b is ONE else b) for a, b in pr]
     diag_slot = np.array([slot_of[(i, i)] for i in range(n)], np.int64)
     a_slot = np.array([slot_of[(int(i), int(j))] for i, j in zip(bi, bj)], np.int64)
 
@@ -377,6 +422,17 @@ def _build(n, rows, cols, perm_r, perm_c, name) -> SymbolicLU:
             level[(i, j)] = lv
             tasks_by_level.setdefault(lv, []).append((slot_of[(i, j)], aux, pairs))
             flops += 2 * len(pairs) + 1
+    slot_level = {slot_of[k]: v for k, v in level.items()}
+    for (i, j), pr in q_pairs.items():
+        lv = 1 + max(slot_level.get(x, -1) for ab in pr for x in ab)
+        slot_level[slot_of[("Q", i, j)]] = lv
+        tasks_by_level.setdefault(lv, []).append((slot_of[("Q", i, j)], AUX_U, pr))
+        flops += 2 * len(pr)
+    for (i, j), pr in p_pairs.items():
+        lv = 1 + max(max(slot_level.get(x, -1) for ab in pr for x in ab), slot_level[slot_of[(i, i)]])
+        slot_level[slot_of[("P", i, j)]] = lv
+        tasks_by_level.setdefault(lv, []).append((slot_of[("P", i, j)], slot_of[(i, i)], pr))
+        flops += 2 * len(pr) + 1
     nlev = max(tasks_by_level) + 1
     factor = _jds([tasks_by_level.get(l, []) for l in range(nlev)], nnz_lu, nnz_lu)
 
@@ -410,55 +466,13 @@ def _build(n, rows, cols, perm_r, perm_c, name) -> SymbolicLU:
         sflops += 2 * len(ops) + 1
     bwd = _jds([blv.get(l, []) for l in range(max(blv) + 1)], nnz_lu, n)
     return build_streams(SymbolicLU(n, nnz_lu, np.asarray(perm_r), np.asarray(perm_c), slot_of, a_slot, diag_slot,
-                                    factor, fwd, bwd, flops, sflops, name))
+                                    factor, fwd, bwd, flops, sflops, name, Lrows=Lrows, Urows=Urows,
+                                    clusters=clusters, cl=cl, inv_cluster=inv_cluster, cluster_kind=kinds), team=team)
 
 
 # ---------------------------------------------------------------------------
 # numpy emulation of the numeric phase (validation of tables; tests)
 # ---------------------------------------------------------------------------
-def numeric_factor(s: SymbolicLU, a_vals):
-    """lu has nnz_lu + 1 entries: the last one is the constant-zero padding slot."""
-    lu = np.zeros(s.nnz_lu + 1)
-    np.add.at(lu, s.a_slot, a_vals)
-    f = s.factor
-    for lv in range(f.n_levels):
-        t0, nt, ob, ml = (int(x) for x in f.lev_meta[lv])
-        ml &= 0xFFFF
-        out = f.task_out[t0:t0 + nt]
-        aux = f.task_aux[t0:t0 + nt]
-        acc = lu[out].copy()
-        for p in range(ml):
-            sl = slice(ob + p * nt, ob + (p + 1) * nt)
-            acc -= lu[f.op_a[sl]] * lu[f.op_b[sl]]
-        for q in range(nt):
-            if aux[q] == AUX_U:
-                lu[out[q]] = acc[q]
-            elif aux[q] == AUX_DIAG:
-                lu[out[q]] = 1.0 / acc[q]
-            else:
-                lu[out[q]] = acc[q] * lu[aux[q]]
-    return lu
-
-
-def numeric_solve(s: SymbolicLU, lu, b):
-    w = np.zeros(s.n + 1)
-    for jds, back in ((s.fwd, False), (s.bwd, True)):
-        for lv in range(jds.n_levels):
-            t0, nt, ob, ml = (int(x) for x in jds.lev_meta[lv])
-            ml &= 0xFFFF
-            rows_ = jds.task_out[t0:t0 + nt]
-            acc = w[rows_].copy() if back else b[jds.task_aux[t0:t0 + nt]].copy()
-            for p in range(ml):
-                sl = slice(ob + p * nt, ob + (p + 1) * nt)
-                acc -= lu[jds.op_a[sl]] * w[jds.op_b[sl]]
-            if back:
-                acc *= lu[s.diag_slot[rows_]]
-            w[rows_] = acc
-    x = np.empty(s.n)
-    x[s.bwd.task_aux] = w[s.bwd.task_out]
-    return x
-
-
 def _validate(s: SymbolicLU, rows, cols, vals):
     A = sp.csc_matrix((vals, (rows, cols)), shape=(s.n, s.n))
     rng = np.random.default_rng(1)
@@ -580,20 +594,7 @@ def build_streams(s: SymbolicLU, team=128):
             out.append((int(j.task_out[t0 + q]), int(j.task_aux[t0 + q]), ops))
         return out
 
-    words, nrec, cyc = [], 0, 0
-    for lv in range(s.fwd.n_levels):
-        tasks = [t for t in level_tasks(s.fwd, lv) if t[2]]   # rows without L entries: w = gathered b already
-        if not tasks:
-            continue
-        r, c = _emit_records(words, tasks, 0, nz | (n << 16), lambda t: t[0] | (one_slot << 16), n | (nz << 16))
-        nrec, cyc = nrec + r, cyc + c
-    for lv in range(s.bwd.n_levels):
-        tasks = level_tasks(s.bwd, lv)
-        r, c = _emit_records(words, tasks, F_BWD, nz | (n << 16), lambda t: t[0] | (int(s.diag_slot[t[0]]) << 16),
-                             n | (nz << 16))
-        nrec, cyc = nrec + r, cyc + c
-    s.solve_stream = np.asarray(words, dtype=np.uint32)
-    s.n_solve_records, s.est_cycles_solve = nrec, cyc
+    build_seq_solve_stream(s, team)
 
     words, nrec, cyc = [], 0, 0
     nlev = s.factor.n_levels
@@ -609,6 +610,361 @@ def build_streams(s: SymbolicLU, team=128):
         nrec, cyc = nrec + r, cyc + (c if sizes[lv] <= 32 else 45 + (c - 45) * 32 // team + 40)
     s.factor_stream = np.asarray(words, dtype=np.uint32)
     s.n_factor_records, s.est_cycles_factor = nrec, cyc
+    return s
+
+
+# ---------------------------------------------------------------------------
+# SEQ solve stream: thread-sequential clusters of the elimination tree
+# ---------------------------------------------------------------------------
+# Level scheduling pays one dependent round trip through shared memory *and* the interpreter per dependency level.
+# The battery models' factors are made of long thin chains (particle radial meshes) hanging off a nested-dissection
+# tree of small dense separators: their depth is close to their size, so a level holds a handful of rows.  Here the
+# rows are instead grouped in *clusters* (maximal single-child paths of the elimination tree: a chain, a separator);
+# one thread walks one cluster row by row with no synchronisation, its only loop-carried dependency being the
+# w[] value it has just stored.  Clusters of equal height run side by side, one record per height:
+#   record  = [nw | flags << 16] [words in the record] [skip] [nt_v | len_v << 16] * nw  + nw blocks, one per warp:
+#             block v holds len_v * nt_v words, word j of its thread q (= lane) at block + j * nt_v + q
+#   thread  = [ntask] task ... task [dummy task]      (dummy: target of the software prefetch of the last task)
+#   task    = [row | ml << 16] [op] * ml              op = lu_slot | w_index << 16,  ml = 1 + 4k (zero-operand padded);
+#             backward tasks finish with  w[row] *= lu[row]  (slot i holds 1/u_ii)
+# flags: 1 backward, 2 WIDE (warp v of the team runs block v), 4 team barrier after the record.
+# Narrow records are run by warp 0 alone; the other warps jump to `skip` (the end of the narrow run) and wait there.
+SEQ_HDR = 4
+SEQ_NARROW = 1 << 31
+PAR_ADD, PAR_DIAG = 2, 4
+PAR_BASE_CYC, PAR_OP_CYC, PAR_SHFL_CYC = 150, 25, 40
+CHAIN_BASE_CYC, CHAIN_ROW_CYC = 200, 12
+# cycle model of one task (measured B200 latencies: LDS 29, DFMA/DADD 8): chain-critical LDS + 2 DFMA levels + store,
+# + 4 cycles per operand beyond the two prefetched ones (two accumulators) + one dependent LDS pair when ml > 2
+SEQ_TASK_CYC, SEQ_CHUNK_CYC, SEQ_LONG_CYC, SEQ_REC_CYC = 90, 45, 30, 150
+
+
+def _seq_clusters(n, Lrows, Urows):
+    """Clusters = maximal paths i1 -> i2 -> ... of the elimination tree in which every node has exactly one child."""
+    first_below = [None] * n          # first row i > k with L[i, k] != 0
+    for i in range(n):
+        for k in Lrows[i]:
+            if first_below[k] is None:
+                first_below[k] = i
+    parent = np.full(n, -1, np.int64)
+    for i in range(n):
+        cand = [j for j in Urows[i] if j > i][:1]
+        if first_below[i] is not None:
+            cand.append(first_below[i])
+        if cand:
+            parent[i] = min(cand)
+    nchild = np.zeros(n, np.int64)
+    only_child = np.full(n, -1, np.int64)
+    for i in range(n):
+        if parent[i] >= 0:
+            nchild[parent[i]] += 1
+            only_child[parent[i]] = i
+    cl = np.full(n, -1, np.int64)
+    clusters = []
+    for i in range(n):
+        c = only_child[i] if nchild[i] == 1 else -1
+        if c >= 0 and clusters[cl[c]][-1] == c:
+            cl[i] = cl[c]
+            clusters[cl[i]].append(i)
+        else:
+            cl[i] = len(clusters)
+            clusters.append([i])
+    # split the pure bidiagonal start of a long cluster off as a CHAIN (consecutive rows i0 .. i0+K-1 with
+    # L row = {previous row} and U row = {diagonal, next row}): its recurrence needs no tables at all
+    out, kinds = [], []
+    for rws in clusters:
+        K = 0
+        if len(rws) > INV_MAX:
+            while K < len(rws) - 1:
+                i = rws[K]
+                if i != rws[0] + K or Lrows[i] != ([rws[K - 1]] if K else []) or Urows[i] != [i, rws[K + 1]]:
+                    break
+                K += 1
+        if K >= 4:
+            out.append(rws[:K])
+            kinds.append("chain")
+            rws = rws[K:]
+        if rws:
+            out.append(rws)
+            kinds.append("inv" if len(rws) <= INV_MAX else "seq")
+    order = sorted(range(len(out)), key=lambda c: out[c][0])     # ascending first row = topological
+    clusters = [out[c] for c in order]
+    kinds = [kinds[c] for c in order]
+    for c, rws in enumerate(clusters):
+        cl[rws] = c
+    return clusters, cl, kinds
+
+
+def build_seq_solve_stream(s: SymbolicLU, team=128):
+    """Solve stream = SEQ records (long chains: one thread per cluster, rows one after the other) and PAR records
+    (clusters with explicit inverse diagonal blocks: one group of G lanes per row, every lane one partial dot product).
+
+    record header (4 words): [kind | mode << 4 | sync << 8 | first_warp << 12 | nblocks << 16] [words in the record]
+                             [skip] [G | mlg << 8]                 followed by one descriptor word per block
+    kind 0 SEQ: descriptor nt | len << 16, block = len * nt words (layout in the comment block above)
+    kind 1 PAR: descriptor nt,             block = (1 + mlg) * nt words: [row] then mlg operand words per lane
+    mode: 1 backward SEQ; PAR: 2 ADD (base + sum, else base - sum), 4 DIAG (base = w[row] / u_ii, else w[row])
+    sync: 0 none, 1 warp, 2 team.   Warp v runs block v - first_warp.  Warps other than 0 jump to `skip` from a
+    narrow run (records of warp 0 alone) and meet warp 0 at the team barrier that ends it."""
+    n, nz = s.n, s.nnz_lu
+    Lrows, Urows, clusters, cl, inv = s.Lrows, s.Urows, s.clusters, s.cl, s.inv_cluster
+    nc = len(clusters)
+    kinds = s.cluster_kind
+    par = np.array([kinds[c] == "inv" for c in range(nc)])
+    # heights from the actual dependencies (not from the tree): always a valid schedule
+    hf = np.zeros(nc, np.int64)
+    for c, rws in enumerate(clusters):
+        for i in rws:
+            for k in Lrows[i]:
+                if cl[k] != c:
+                    hf[c] = max(hf[c], hf[cl[k]] + 1)
+    # backward sweep: as late as possible, so that the long leaf chains all land in the last record instead of
+    # stretching every record on the way down (a record lasts as long as its longest thread)
+    deps_b = [set() for _ in range(nc)]
+    for c, rws in enumerate(clusters):
+        for i in rws:
+            for j in Urows[i]:
+                if j != i and cl[j] != c:
+                    assert cl[j] > c, "upper dependency on an earlier cluster"
+                    deps_b[c].add(int(cl[j]))
+    tail = np.zeros(nc, np.int64)
+    for c in range(nc):               # dependents of d are clusters c < d: ascending order sees them first
+        for d in deps_b[c]:
+            tail[d] = max(tail[d], tail[c] + 1)
+    hb = int(tail.max()) - tail
+    pad_op = nz | (n << 16)
+    n_warps = max(min(team, 128) // 32, 1)
+
+    def seq_task(i, back):
+        ops = [(s.slot_of[(i, j)], j) for j in Urows[i] if j != i] if back else [(s.slot_of[(i, k)], k) for k in Lrows[i]]
+        if not back and not ops:
+            return None, 0            # w[i] is already the gathered right-hand side
+        ml = 1 + 4 * ((max(len(ops), 1) + 2) // 4)      # one prefetched operand + chunks of four
+        wd = [i | (ml << 16)] + [a | (b << 16) for a, b in ops] + [pad_op] * (ml - len(ops))
+        cyc = SEQ_TASK_CYC + (8 if back else 0) + (SEQ_LONG_CYC + SEQ_CHUNK_CYC * ((ml - 1) // 4) if ml > 1 else 0)
+        return wd, cyc
+
+    dummy = [n | (1 << 16), pad_op]
+
+    def fold(progs, nbins):
+        """longest-processing-time folding of cluster programs [cyc, ntask, words] into at most nbins threads"""
+        progs = sorted(progs, key=lambda t: -t[0])
+        if len(progs) <= nbins:
+            return progs
+        bins = [list(t) for t in progs[:nbins]]
+        for t in progs[nbins:]:
+            bmin = min(bins, key=lambda x: x[0])
+            bmin[0] += t[0]
+            bmin[1] += t[1]
+            bmin[2] = bmin[2] + t[2]
+        return sorted(bins, key=lambda t: -t[0])
+
+    def seq_record(progs, back, nw):
+        progs = fold(progs, 32 * nw)
+        nb = min(nw, (len(progs) + 31) // 32)
+        blocks = [progs[v::nb] for v in range(nb)]
+        desc, body = [], []
+        for blk in blocks:
+            streams = [[t[1]] + t[2] + dummy for t in blk]
+            ln = max(len(x) for x in streams)
+            m = np.zeros((ln, len(blk)), np.int64)
+            for q, x in enumerate(streams):
+                m[:len(x), q] = x
+            desc.append(len(blk) | (ln << 16))
+            body += m.reshape(-1).tolist()
+        return dict(kind=0, mode=1 if back else 0, nblocks=nb, param=0, desc=desc, body=body, cyc=progs[0][0],
+                    threads=[d & 0xFFFF for d in desc])
+
+    def chain_record(cs, back, nw):
+        """kind 2: one lane per chain, three words per lane: [first row | K << 16] [L slot of row 1 | U slot of row 0 << 16]
+        [parent row of the last chain row]"""
+        cs = sorted(cs, key=lambda c: -len(clusters[c]))
+        nb = min(nw, (len(cs) + 31) // 32)
+        assert len(cs) <= 32 * nb, "more chains than lanes"
+        desc, body = [], []
+        for v in range(nb):
+            blk = cs[v::nb]
+            m = np.zeros((3, len(blk)), np.int64)
+            for q, c in enumerate(blk):
+                rws = clusters[c]
+                m[0, q] = rws[0] | (len(rws) << 16)
+                m[1, q] = s.slot_of[(rws[1], rws[0])] | (s.slot_of[(rws[0], rws[1])] << 16)
+                m[2, q] = Urows[rws[-1]][1]
+            desc.append(len(blk))
+            body += m.reshape(-1).tolist()
+        K = len(clusters[cs[0]])
+        return dict(kind=2, mode=1 if back else 0, nblocks=nb, param=K, desc=desc, body=body,
+                    cyc=CHAIN_BASE_CYC + CHAIN_ROW_CYC * K, threads=desc)
+
+    def par_records(rows_ops, mode, nw):
+        """rows_ops: list of (row, [(slot, w index), ...]).  The rows of one cluster stay in one block (= one warp): they
+        read each other's old values, and "every lane reads before any lane writes" only holds inside a warp."""
+        units = {}
+        for row, ops in rows_ops:
+            units.setdefault(int(cl[row]), []).append((row, ops))
+        units = sorted(units.values(), key=lambda u: -len(u))
+        records, cur = [], []
+        for u in units:                      # first fit into the blocks of the current record
+            for blk in cur:
+                if len(blk) + len(u) <= 32:
+                    blk += u
+                    break
+            else:
+                if len(cur) == nw:
+                    records.append(cur)
+                    cur = []
+                cur.append(list(u))
+        if cur:
+            records.append(cur)
+        out = []
+        for blocks in records:
+            nb = len(blocks)
+            maxml = max(len(t[1]) for blk in blocks for t in blk)
+            G = 1
+            if nb == 1:
+                while 2 * G * len(blocks[0]) <= 32 and G < maxml:
+                    G *= 2
+            mlg = (maxml + G - 1) // G
+            desc, body = [], []
+            for blk in blocks:
+                nt = len(blk) * G
+                m = np.full((1 + mlg, nt), pad_op, np.int64)
+                for g, (row, ops) in enumerate(blk):
+                    m[0, g * G:(g + 1) * G] = row
+                    for k, (a, b) in enumerate(ops):
+                        m[1 + k // G, g * G + k % G] = a | (b << 16)
+                desc.append(nt)
+                body += m.reshape(-1).tolist()
+            lg = G.bit_length() - 1
+            out.append(dict(kind=1, mode=mode, nblocks=nb, param=G | (mlg << 8), desc=desc, body=body,
+                            cyc=PAR_BASE_CYC + PAR_OP_CYC * mlg + PAR_SHFL_CYC * lg, threads=desc))
+        return out
+
+    recs = []                         # records in execution order, grouped by height: [(height key, [records])]
+    for back, heights in ((False, hf), (True, hb)):
+        for h in range(int(heights.max()) + 1):
+            cs = [c for c in range(nc) if heights[c] == h]
+            progs, rows_a, rows_b, chains = [], [], [], []
+            for c in cs:
+                rws = clusters[c][::-1] if back else clusters[c]
+                if kinds[c] == "chain":
+                    chains.append(c)
+                    continue
+                if not par[c]:
+                    wd, cyc, nt_ = [], 0, 0
+                    for i in rws:
+                        tw, tc = seq_task(i, back)
+                        if tw is not None:
+                            wd += tw
+                            cyc += tc
+                            nt_ += 1
+                    if nt_:
+                        progs.append([cyc, nt_, wd])
+                    continue
+                inside = set(rws)
+                for i in rws:
+                    if back:
+                        ext = [(s.slot_of[(i, j)], j) for j in Urows[i] if j != i and j not in inside]
+                        inn = [(s.slot_of[("P", i, j)], j) for j in clusters[c] if j > i and ("P", i, j) in s.slot_of]
+                        if ext:
+                            rows_a.append((i, ext))
+                        rows_b.append((i, inn))           # always: the division by u_ii
+                    else:
+                        ext = [(s.slot_of[(i, k)], k) for k in Lrows[i] if k not in inside]
+                        inn = [(s.slot_of[("Q", i, j)], j) for j in clusters[c] if j < i and ("Q", i, j) in s.slot_of]
+                        if ext:
+                            rows_a.append((i, ext))
+                        if inn:
+                            rows_b.append((i, inn))
+            group = []
+            # chains on the first warps, the first PAR phase of the other clusters beside them on the remaining warps
+            first_par = rows_a if rows_a else rows_b
+            seq_w = n_warps
+            side_by_side = False
+            if (progs or chains) and first_par and n_warps > 1 and len(progs) + len(chains) > 8:
+                need = (len(first_par) + 23) // 24      # blocks hold whole clusters: allow for packing slack
+                if need < n_warps:
+                    seq_w, side_by_side = n_warps - need, True
+            if chains and progs:
+                side_by_side = False          # not worth a third concurrent stream: one record after the other
+                seq_w = n_warps
+            if chains:
+                r = chain_record(chains, back, seq_w if len(chains) > 32 or side_by_side else 1)
+                r["first_warp"] = 0
+                group.append(r)
+            if progs:
+                r = seq_record(progs, back, seq_w if len(progs) > 32 or side_by_side else 1)
+                r["first_warp"] = 0
+                group.append(r)
+            for phase, (rows_x, mode) in enumerate(((rows_a, 0), (rows_b, PAR_ADD | (PAR_DIAG if back else 0)))):
+                if not rows_x:
+                    continue
+                beside = side_by_side and rows_x is first_par
+                nw = (n_warps - seq_w) if beside else (n_warps if len(rows_x) > 32 else 1)
+                for r in par_records(rows_x, mode, nw):
+                    r["first_warp"] = seq_w if beside else 0
+                    r["beside"] = beside
+                    group.append(r)
+            for r in group:
+                r["back"], r["height"] = back, h
+            recs += group
+    # sync codes: nothing between the chain record and the PAR record running beside it; otherwise a warp barrier
+    # when this record and the next one involve warp 0 alone, a team barrier in every other case
+    def narrow(r):
+        return r["first_warp"] == 0 and r["nblocks"] == 1
+
+    for k, r in enumerate(recs):
+        nxt = recs[k + 1] if k + 1 < len(recs) else None
+        if nxt is not None and nxt.get("beside"):
+            r["sync"] = 0
+        elif nxt is not None and narrow(r) and narrow(nxt) and not r.get("beside"):
+            r["sync"] = 1
+        else:
+            r["sync"] = 2
+    words, offs = [], []
+    for r in recs:
+        offs.append(len(words))
+        w0 = r["kind"] | (r["mode"] << 4) | (r["sync"] << 8) | (r["first_warp"] << 12) | (r["nblocks"] << 16)
+        total = SEQ_HDR + len(r["desc"]) + len(r["body"])
+        words += [w0, total, 0, r["param"]] + r["desc"] + r["body"]
+    end = len(words)
+    # narrow runs: maximal sequences of narrow records joined by warp barriers; other warps skip to the end of the run
+    k = 0
+    while k < len(recs):
+        if narrow(recs[k]) and recs[k]["sync"] != 0 and not recs[k].get("beside") and (k == 0 or recs[k - 1]["sync"] == 2):
+            e = k
+            while recs[e]["sync"] == 1:
+                e += 1
+            stop = offs[e + 1] if e + 1 < len(recs) else end
+            for q in range(k, e + 1):
+                words[offs[q]] |= SEQ_NARROW
+                words[offs[q] + 2] = stop
+                recs[q]["narrow"] = True
+            k = e + 1
+        else:
+            k += 1
+    s.n_solve_words = end
+    words += [0] * (4 * 32)           # the operand prefetch of the very last SEQ task reads up to 4 * nt words ahead
+    s.solve_stream = np.asarray(words, dtype=np.uint32)
+    # critical path estimate: records run one after the other except a PAR record beside its chain record
+    est, k = 0, 0
+    while k < len(recs):
+        c = recs[k]["cyc"]
+        if recs[k]["sync"] == 0 and k + 1 < len(recs):
+            c = max(c, recs[k + 1]["cyc"])
+            k += 1
+        est += c + SEQ_REC_CYC
+        k += 1
+    s.n_solve_records, s.est_cycles_solve = len(recs), int(est)
+    for r, o in zip(recs, offs):
+        r["offset"] = o
+    s.solve_program = recs
+    s.seq_info = dict(clusters=nc, fwd_heights=int(hf.max()) + 1, bwd_heights=int(hb.max()) + 1,
+                      records=[dict(back=r["back"], height=r["height"], kind=("SEQ", "PAR", "CHAIN")[r["kind"]], mode=r["mode"],
+                                    sync=r["sync"], first_warp=r["first_warp"], threads=r["threads"],
+                                    G=r["param"] & 0xFF, mlg=r["param"] >> 8, words=len(r["body"]), cyc=r["cyc"])
+                               for r in recs],
+                      team_min=32 * max(r["first_warp"] + r["nblocks"] for r in recs))
     return s
 
 
@@ -645,19 +1001,67 @@ def stream_factor(s: SymbolicLU, a_vals):
 
 
 def stream_solve(s: SymbolicLU, lu, b):
+    """numpy emulation of the device triangular solves driven by the solve stream (validation of the tables)."""
     w = np.zeros(s.n + 1)
     w[:s.n] = b[s.perm_r]
     st = s.solve_stream
-    for off, nt, ml, fl in _walk(st):
-        tw = st[off + 1:off + 1 + nt].astype(np.int64)
-        row, dg = tw & 0xFFFF, tw >> 16
-        acc = w[row].copy()
-        for p in range(ml):
-            ow = st[off + 1 + nt + p * nt:off + 1 + nt + (p + 1) * nt].astype(np.int64)
-            acc -= lu[ow & 0xFFFF] * w[ow >> 16]
-        if fl & F_BWD:
-            acc *= lu[dg]
-        w[row] = acc
+    off = 0
+    while off < s.n_solve_words:
+        w0, total, param = int(st[off]), int(st[off + 1]), int(st[off + 3])
+        kind, mode, nb = w0 & 0xF, (w0 >> 4) & 0xF, (w0 >> 16) & 0xFF
+        base = off + SEQ_HDR + nb
+        if kind == 0:
+            for v in range(nb):
+                nt, ln = int(st[off + SEQ_HDR + v]) & 0xFFFF, int(st[off + SEQ_HDR + v]) >> 16
+                for q in range(nt):
+                    p = base + q
+                    ntask = int(st[p])
+                    p += nt
+                    for _ in range(ntask):
+                        hdr = int(st[p])
+                        row, ml = hdr & 0xFFFF, hdr >> 16
+                        acc = w[row]
+                        for j in range(ml):
+                            o = int(st[p + (1 + j) * nt])
+                            acc -= lu[o & 0xFFFF] * w[o >> 16]
+                        if mode & 1:
+                            acc *= lu[row]
+                        w[row] = acc
+                        p += (1 + ml) * nt
+                base += nt * ln
+        elif kind == 2:
+            for v in range(nb):
+                nt = int(st[off + SEQ_HDR + v])
+                for q in range(nt):
+                    r0, K = int(st[base + q]) & 0xFFFF, int(st[base + q]) >> 16
+                    L0, U0 = int(st[base + nt + q]) & 0xFFFF, int(st[base + nt + q]) >> 16
+                    if mode & 1:
+                        nxt = w[int(st[base + 2 * nt + q])]
+                        for k in range(K - 1, -1, -1):
+                            nxt = (w[r0 + k] - lu[U0 + k] * nxt) * lu[r0 + k]
+                            w[r0 + k] = nxt
+                    else:
+                        for k in range(1, K):
+                            w[r0 + k] -= lu[L0 + k - 1] * w[r0 + k - 1]
+                base += 3 * nt
+        else:
+            G, mlg = param & 0xFF, param >> 8
+            for v in range(nb):
+                new = {}
+                nt = int(st[off + SEQ_HDR + v])
+                for g in range(nt // G):
+                    row = int(st[base + g * G])
+                    acc = 0.0
+                    for l in range(g * G, (g + 1) * G):
+                        for j in range(mlg):
+                            o = int(st[base + (1 + j) * nt + l])
+                            acc += lu[o & 0xFFFF] * w[o >> 16]
+                    bse = w[row] * lu[row] if mode & PAR_DIAG else w[row]
+                    new[row] = bse + acc if mode & PAR_ADD else bse - acc
+                base += (1 + mlg) * nt
+                for row, val in new.items():      # every lane of the warp reads before any lane writes
+                    w[row] = val
+        off += total
     x = np.empty(s.n)
     x[s.perm_c] = w[:s.n]
     return x
