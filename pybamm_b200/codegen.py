@@ -41,15 +41,15 @@ def _dlit(v):
 
 
 _UN = {
-    ir.NEG: "(-{a})", ir.ABS: "fabs({a})", ir.EXP: "exp({a})", ir.LOG: "log({a})", ir.SQRT: "sqrt({a})",
-    ir.TANH: "tanh({a})", ir.SINH: "sinh({a})", ir.COSH: "cosh({a})", ir.SIN: "sin({a})", ir.COS: "cos({a})",
-    ir.ASINH: "asinh({a})", ir.ATAN: "atan({a})", ir.ERF: "erf({a})", ir.ERFC: "erfc({a})",
+    ir.NEG: "(-{a})", ir.ABS: "fabs({a})", ir.EXP: "PB_EXP({a})", ir.LOG: "PB_LOG({a})", ir.SQRT: "sqrt({a})",
+    ir.TANH: "PB_TANH({a})", ir.SINH: "PB_SINH({a})", ir.COSH: "PB_COSH({a})", ir.SIN: "sin({a})", ir.COS: "cos({a})",
+    ir.ASINH: "PB_ASINH({a})", ir.ATAN: "atan({a})", ir.ERF: "erf({a})", ir.ERFC: "erfc({a})",
     ir.FLOOR: "floor({a})", ir.CEIL: "ceil({a})", ir.RECIP: "(1.0 / {a})", ir.SQR: "({a} * {a})",
     ir.LOG10: "log10({a})", ir.SIGN: "(({a} > 0.0) - ({a} < 0.0))",
 }
 _BIN = {
     ir.ADD: "({a} + {b})", ir.SUB: "({a} - {b})", ir.MUL: "({a} * {b})", ir.DIV: "({a} / {b})",
-    ir.POW: "pow({a}, {b})", ir.MIN: "fmin({a}, {b})", ir.MAX: "fmax({a}, {b})",
+    ir.POW: "PB_POW({a}, {b})", ir.MIN: "fmin({a}, {b})", ir.MAX: "fmax({a}, {b})",
     ir.LT: "(({a} < {b}) ? 1.0 : 0.0)", ir.LE: "(({a} <= {b}) ? 1.0 : 0.0)",
     ir.MOD: "({a} - floor({a} / {b}) * {b})", ir.HYPOT: "hypot({a}, {b})",
 }
@@ -63,7 +63,7 @@ class _Emitter:
         self.table_bytes = 0
         self._ntab = 0
 
-    def table(self, ctype, values, hint="t"):
+    def table(self, ctype, values, hint="t", qual="PB_TABLE"):
         name = f"{self.prefix}_{hint}{self._ntab}"
         self._ntab += 1
         vals = list(values)
@@ -73,7 +73,7 @@ class _Emitter:
         else:
             body = ", ".join(str(int(v)) for v in vals)
             self.table_bytes += (2 if "short" in ctype else 4) * len(vals)
-        self.tables.append(f"static PB_TABLE const {ctype} {name}[{max(len(vals), 1)}] = {{{body if vals else '0'}}};")
+        self.tables.append(f"static {qual} const {ctype} {name}[{max(len(vals), 1)}] = {{{body if vals else '0'}}};")
         return name
 
 
@@ -174,11 +174,12 @@ def emit_program(prog: Program, fname: str, prefix: str):
             _emit_template(em, t, dest, L, "    ")
             L.append("  }")
             continue
-        ttp = em.table("unsigned char" if len(tpls) < 256 else "unsigned short", tiles_tp, "tt")
-        tbs = em.table(_itype(max(tiles_base) if tiles_base else 0), tiles_base, "tb")
+        # tile dispatch tables: warp-uniform look-ups on the critical path of every tile -> constant memory
+        ttp = em.table("unsigned char" if len(tpls) < 256 else "unsigned short", tiles_tp, "tt", qual="PB_CTABLE")
+        tbs = em.table(_itype(max(tiles_base) if tiles_base else 0), tiles_base, "tb", qual="PB_CTABLE")
         L.append(f"  for (int tile = PB_WARP; tile < {nt}; tile += PB_NWARPS) {{")
-        L.append(f"    const int tb = (int)PB_LDU({tbs}[tile]);")
-        L.append(f"    switch ((int)PB_LDU({ttp}[tile])) {{")
+        L.append(f"    const int tb = (int){tbs}[tile];")
+        L.append(f"    switch ((int){ttp}[tile]) {{")
         for k, (t, dest) in enumerate(tpls):
             L.append(f"    case {k}: {{")
             L.append(f"      const int qe = (tb + 32 < {t.n_inst}) ? tb + 32 : {t.n_inst};")
@@ -261,7 +262,7 @@ def emit_solve_program(sym: slu.SymbolicLU) -> str:
             nt = r["desc"][v] & 0xFFFF
             if r["kind"] == 1:
                 G, mlg = r["param"] & 0xFF, r["param"] >> 8
-                call = f"pb_par_rec<{nt}, {G}, {mlg}, {r['mode']}>(st + {boff}, lu, w);"
+                call = f"pb_par_rec<{G}, {mlg}, {r['mode']}>(st + {boff}, {nt}, lu, w);"
                 boff += (1 + mlg) * nt
             elif r["kind"] == 2:
                 call = f"pb_chain_rec<{r['mode'] & 1}>(st + {boff}, {nt}, lu, w);"
@@ -312,6 +313,16 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
     n_var = progs["vars"].n_out
     out = []
     out.append(f"/* generated by pybamm_b200.codegen ({dialect}) -- do not edit */")
+    # the long libm sequences go through PB_* so that the device build can route them to shared out-of-line copies
+    # (instruction-cache footprint of the generated functions); everywhere else they are the plain libm calls
+    out.append("#ifndef PB_CTABLE")
+    out.append("#define PB_CTABLE")
+    out.append("#endif")
+    out.append("#ifndef PB_EXP")
+    for fn in ("EXP", "LOG", "TANH", "SINH", "COSH", "ASINH"):
+        out.append(f"#define PB_{fn}(x) {fn.lower()}(x)")
+    out.append("#define PB_POW(x, y) pow(x, y)")
+    out.append("#endif")
     out.append(f'#define PBM_NAME "{bundle.name}"')
     out.append(f"#define PBM_N {bundle.n_states}")
     out.append(f"#define PBM_NDIFF {bundle.n_diff}")

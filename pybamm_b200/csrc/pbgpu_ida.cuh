@@ -33,6 +33,7 @@
 
 #define PB_AUX_U 0xFFFF
 #define PB_AUX_DIAG 0xFFFE
+#define PB_AUX_NEG 0xFFFD   /* out = -sum(pairs): the old value of the slot is not part of the result */
 
 #define PB_NEV_PAD ((PBM_NEV > 0) ? PBM_NEV : 1)
 
@@ -71,11 +72,25 @@
 #define PB_OFF_SLV (PB_OFF_STATS + 8)                          /* packed solve stream (u32 words) */
 #define PB_OFF_FAC (PB_OFF_SLV + (PBM_SLV_ALLOC + 1) / 2)      /* packed factor stream when it fits (PBM_FAC_SMEM) */
 #if PBM_FAC_SMEM
-#define PB_SMEM_DOUBLES (PB_OFF_FAC + (PBM_FAC_WORDS + 1) / 2)
+#define PB_OFF_END0 (PB_OFF_FAC + (PBM_FAC_WORDS + 1) / 2)
 #else
-#define PB_SMEM_DOUBLES PB_OFF_FAC
+#define PB_OFF_END0 PB_OFF_FAC
+#endif
+// Large models: the correction ee, read and written by every Newton iteration, stays in shared memory as well; the
+// history, the predictors, the error weights and the Jacobian temporaries are the ones streamed from L2.
+#if PB_GLOBAL_VEC
+#define PB_OFF_EE PB_OFF_END0
+#define PB_SMEM_DOUBLES (PB_OFF_EE + PBM_N)
+#else
+#define PB_SMEM_DOUBLES PB_OFF_END0
 #endif
 #define PB_SMEM_BYTES (PB_SMEM_DOUBLES * 8)
+
+// Strided vector loops, written so that every load of a pass is in flight before the first use: the trip count is a
+// compile-time constant (elements per thread), the body is fully unrolled and guarded.  The streamed vectors of the
+// large models live in L2 (PB_GLOBAL_VEC): a pass then costs about one L2 round trip instead of one per element.
+#define PB_VPT ((PBM_N + PB_TEAM - 1) / PB_TEAM)
+#define PB_VEC_FOR(k, i) _Pragma("unroll") for (int k = 0, i = PB_TID; k < PB_VPT; k++, i += PB_TEAM)
 
 enum { PB_ST_NST, PB_ST_NRE, PB_ST_NSETUPS, PB_ST_NETF, PB_ST_NNI, PB_ST_NCFN, PB_ST_NJE, PB_ST_NGE };
 
@@ -100,7 +115,11 @@ struct pb_sys {
 
 #define S_PHI(S, j) ((S).gv + PB_GOFF_PHI + (j) * PBM_N)
 #define S_EWT(S) ((S).gv + PB_GOFF_EWT)
+#if PB_GLOBAL_VEC
+#define S_EE(S) ((S).sm + PB_OFF_EE)
+#else
 #define S_EE(S) ((S).gv + PB_GOFF_EE)
+#endif
 #define S_YYPRED(S) ((S).gv + PB_GOFF_YYPRED)
 #define S_YPPRED(S) ((S).gv + PB_GOFF_YPPRED)
 #define S_TMPJ(S) ((S).gv + PB_GOFF_TMPJ)
@@ -198,8 +217,8 @@ static PB_DEV int pb_lu_factor(pb_sys& S) {
         for (int o = nt; o < 32; o <<= 1) a0 += __shfl_xor_sync(0xffffffffu, a0, o);
         if (PB_LANE < nt) {
           const int out = (int)(tw & 0xFFFFu), aux = (int)(tw >> 16);
-          const double acc = lu[out] - a0;
-          if (aux == PB_AUX_U) {
+          const double acc = (aux == PB_AUX_NEG ? 0.0 : lu[out]) - a0;
+          if (aux == PB_AUX_U || aux == PB_AUX_NEG) {
             lu[out] = acc;
           } else if (aux == PB_AUX_DIAG) {
             const double inv = 1.0 / acc;
@@ -218,8 +237,8 @@ static PB_DEV int pb_lu_factor(pb_sys& S) {
             const unsigned int o0 = st[base + nt + p * nt + q];
             dot += lu[o0 & 0xFFFFu] * lu[o0 >> 16];
           }
-          const double acc = lu[out] - dot;
-          if (aux == PB_AUX_U) {
+          const double acc = (aux == PB_AUX_NEG ? 0.0 : lu[out]) - dot;
+          if (aux == PB_AUX_U || aux == PB_AUX_NEG) {
             lu[out] = acc;
           } else if (aux == PB_AUX_DIAG) {
             const double inv = 1.0 / acc;
@@ -240,7 +259,7 @@ static PB_DEV int pb_lu_factor(pb_sys& S) {
         const unsigned int tw = PB_FAC_LD(st[base + q]);
         const int out = (int)(tw & 0xFFFFu), aux = (int)(tw >> 16);
         const unsigned int* op = st + base + nt + q;
-        double acc0 = lu[out], acc1 = 0.0;
+        double acc0 = (aux == PB_AUX_NEG) ? 0.0 : lu[out], acc1 = 0.0;
         int p = 0;
         for (; p + 1 < ml; p += 2) {
           const unsigned int o0 = PB_FAC_LD(op[p * nt]), o1 = PB_FAC_LD(op[(p + 1) * nt]);
@@ -252,7 +271,7 @@ static PB_DEV int pb_lu_factor(pb_sys& S) {
           acc0 -= lu[o0 & 0xFFFFu] * lu[o0 >> 16];
         }
         const double acc = acc0 + acc1;
-        if (aux == PB_AUX_U) {
+        if (aux == PB_AUX_U || aux == PB_AUX_NEG) {
           lu[out] = acc;
         } else if (aux == PB_AUX_DIAG) {
           const double inv = 1.0 / acc;
@@ -335,15 +354,17 @@ static PB_DEV void pb_seq_thread(const unsigned int* PB_RESTRICT p, const int nt
 // PAR record: NT lanes, G lanes per row, MLG operands per lane.  Partial dot product, xor-butterfly over the G lanes,
 // w[row] = base +/- sum with base = w[row] or w[row] / u_ii.  Every lane reads before any lane writes (rows of one
 // cluster read each other's old values through the explicit inverse block).
-template <int NT, int G, int MLG, unsigned int MODE>
-static PB_DEV void pb_par_rec(const unsigned int* PB_RESTRICT blk, const double* PB_RESTRICT lu, double* PB_RESTRICT w) {
-  constexpr unsigned int mask = NT == 32 ? 0xffffffffu : ((1u << NT) - 1u);
-  if (PB_LANE < NT) {
+// Out of line and shared by every record of the same shape (G, MLG, MODE): the solve is one call per record.
+template <int G, int MLG, unsigned int MODE>
+static __device__ __noinline__ void pb_par_rec(const unsigned int* PB_RESTRICT blk, const int nt, const double* PB_RESTRICT lu,
+                                               double* PB_RESTRICT w) {
+  const unsigned int mask = nt == 32 ? 0xffffffffu : ((1u << nt) - 1u);
+  if (PB_LANE < nt) {
     const unsigned int* p = blk + PB_LANE;
     const int row = (int)p[0];
     unsigned int a[MLG > 0 ? MLG : 1];
 #pragma unroll
-    for (int j = 0; j < MLG; j++) a[j] = p[(1 + j) * NT];
+    for (int j = 0; j < MLG; j++) a[j] = p[(1 + j) * nt];
     const double wr = w[row];
     const double ld = (MODE & PB_PAR_DIAG) ? lu[row] : 1.0;
     double x[MLG > 0 ? MLG : 1], y[MLG > 0 ? MLG : 1];
@@ -371,8 +392,8 @@ static PB_DEV void pb_par_rec(const unsigned int* PB_RESTRICT blk, const double*
 // CHAIN record: one lane per bidiagonal chain of K consecutive rows.  All operands are independent of the recurrence
 // and are loaded in batches ahead of it: the chain costs one DFMA per row.
 template <int BWD>
-static PB_DEV void pb_chain_rec(const unsigned int* PB_RESTRICT blk, const int nt, const double* PB_RESTRICT lu,
-                                double* PB_RESTRICT w) {
+static __device__ __noinline__ void pb_chain_rec(const unsigned int* PB_RESTRICT blk, const int nt, const double* PB_RESTRICT lu,
+                                                 double* PB_RESTRICT w) {
   if (PB_LANE >= nt) return;
   const unsigned int h = blk[PB_LANE], sl = blk[nt + PB_LANE];
   const int r0 = (int)(h & 0xFFFFu), K = (int)(h >> 16);
@@ -421,9 +442,17 @@ static PB_DEV void pb_chain_rec(const unsigned int* PB_RESTRICT blk, const int n
 }
 
 template <int BWD>
-static PB_DEV void pb_seq_rec(const unsigned int* PB_RESTRICT blk, const int nt, const double* PB_RESTRICT lu,
-                              double* PB_RESTRICT w) {
+static __device__ __noinline__ void pb_seq_rec(const unsigned int* PB_RESTRICT blk, const int nt, const double* PB_RESTRICT lu,
+                                               double* PB_RESTRICT w) {
   if (PB_LANE < nt) pb_seq_thread<BWD>(blk + PB_LANE, nt, lu, w);
+}
+#endif
+
+#ifndef PB_EMU
+// one copy of the call sequence for every call site of pb_lu_solve
+static __device__ __noinline__ void pb_solve_program(const unsigned int* PB_RESTRICT st, const double* PB_RESTRICT lu,
+                                                     double* PB_RESTRICT w) {
+  PBM_SOLVE_PROGRAM
 }
 #endif
 
@@ -453,8 +482,7 @@ static PB_DEV void pb_lu_solve_t(pb_sys& S, double* b, double* trace) {
   }
   {
 #ifndef PB_EMU
-    const unsigned int* PB_RESTRICT st = S.slv;
-    PBM_SOLVE_PROGRAM
+    pb_solve_program(S.slv, lu, w);
 #else
     const unsigned int* st = S.slv;
     int off = 0;
@@ -563,11 +591,16 @@ static PB_DEV int pb_lsetup(pb_sys& S, double t, const double* y, double cj, int
   return ier;
 }
 
-static PB_DEV double pb_wrms(pb_sys& S, const double* x) {
-  const double* ewt = S_EWT(S);
+static PB_DEV double pb_wrms(pb_sys& S, const double* PB_RESTRICT x) {
+  const double* PB_RESTRICT ewt = S_EWT(S);
+  double xv[PB_VPT], ev[PB_VPT];
+  PB_VEC_FOR(k, i) {
+    xv[k] = (i < PBM_N) ? x[i] : 0.0;
+    ev[k] = (i < PBM_N) ? ewt[i] : 0.0;
+  }
   double acc = 0.0;
-  for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
-    const double v = x[i] * ewt[i];
+  PB_VEC_FOR(k, i) {
+    const double v = xv[k] * ev[k];
     acc += v * v;
   }
   return sqrt(pb_team_sum(S.team, acc) / PBM_N);
@@ -575,12 +608,17 @@ static PB_DEV double pb_wrms(pb_sys& S, const double* x) {
 
 // ewt_i = 1 / (rtol |y_i| + atol_i); returns non-zero if a weight is not positive. Ends with a barrier.
 static PB_DEV int pb_ewt_set(pb_sys& S, const double* y) {
-  double* ewt = S_EWT(S);
+  double* PB_RESTRICT ewt = S_EWT(S);
   double bad = 0.0;
-  for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
-    const double w = S.rtol * fabs(y[i]) + PB_LD(S.atol[i]);
+  double yv[PB_VPT], av[PB_VPT];
+  PB_VEC_FOR(k, i) {
+    yv[k] = (i < PBM_N) ? y[i] : 1.0;
+    av[k] = (i < PBM_N) ? PB_LD(S.atol[i]) : 1.0;
+  }
+  PB_VEC_FOR(k, i) {
+    const double w = S.rtol * fabs(yv[k]) + av[k];
     if (!(w > 0.0)) bad = 1.0;
-    ewt[i] = 1.0 / w;
+    if (i < PBM_N) ewt[i] = 1.0 / w;
   }
   PB_SYNC();
   return pb_team_max(S.team, bad) != 0.0;
@@ -618,13 +656,20 @@ static PB_DEV void pb_interp_coeffs(const pb_sys& S, double t, pb_interp& I) {
 static PB_DEV void pb_get_solution(const pb_sys& S, double t, double* dst) {
   pb_interp I;
   pb_interp_coeffs(S, t, I);
-  const double* phi = S_PHI(S, 0);
-  for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
-    double s = 0.0;
+  const double* PB_RESTRICT phi = S_PHI(S, 0);
+  double pv[PB_VPT][PB_MXORDP1];
+  PB_VEC_FOR(k, i) {
 #pragma unroll
-    for (int j = PB_MXORDP1 - 1; j >= 0; j--)
-      if (j <= I.kord) s += I.c[j] * phi[j * PBM_N + i];
-    dst[i] = s;
+    for (int j = 0; j < PB_MXORDP1; j++) pv[k][j] = (j <= I.kord && i < PBM_N) ? phi[j * PBM_N + i] : 0.0;
+  }
+  PB_VEC_FOR(k, i) {
+    if (i < PBM_N) {
+      double s = 0.0;
+#pragma unroll
+      for (int j = PB_MXORDP1 - 1; j >= 0; j--)
+        if (j <= I.kord) s += I.c[j] * pv[k][j];
+      dst[i] = s;
+    }
   }
 }
 // y(t) -> ydst and y'(t) -> ypdst. No barrier.
@@ -758,24 +803,32 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
       bj[j] = (j <= kk) ? beta[j] : 0.0;
       gj[j] = (j <= kk) ? gamma[j] : 0.0;
     }
-    for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
-      double a = 0.0, b = 0.0;
+    // orders above kk contribute nothing: their coefficients are zero and the loads are skipped (team-uniform branch)
+    double pv[PB_VPT][PB_MXORDP1];
+    PB_VEC_FOR(k, i) {
 #pragma unroll
-      for (int j = PB_MXORDP1 - 1; j >= 0; j--) {
-        if (j <= kk) {
-          double v = phi[j * PBM_N + i];
-          if (j >= ns) {
-            v *= bj[j];
-            phi[j * PBM_N + i] = v;
+      for (int j = 0; j < PB_MXORDP1; j++) pv[k][j] = (j <= kk && i < PBM_N) ? phi[j * PBM_N + i] : 0.0;
+    }
+    PB_VEC_FOR(k, i) {
+      if (i < PBM_N) {
+        double a = 0.0, b = 0.0;
+#pragma unroll
+        for (int j = PB_MXORDP1 - 1; j >= 0; j--) {
+          if (j <= kk) {
+            double v = pv[k][j];
+            if (j >= ns) {
+              v *= bj[j];
+              phi[j * PBM_N + i] = v;
+            }
+            a += v;
+            if (j >= 1) b += gj[j] * v;
           }
-          a += v;
-          if (j >= 1) b += gj[j] * v;
         }
+        yypred[i] = a;
+        yppred[i] = b;
+        ee[i] = 0.0;
+        yy[i] = a;
       }
-      yypred[i] = a;
-      yppred[i] = b;
-      ee[i] = 0.0;
-      yy[i] = a;
     }
     PB_SYNC();
   }
@@ -806,10 +859,19 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
       for (;;) {
         PB_STAT(S, PB_ST_NNI);
         // rhs = -F = -(f - M y'),  y' = yppred + cj * ee on the differential rows
-        for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
-          double r = delta[i];
-          if (i < PBM_NDIFF) r -= yppred[i] + S.cj * ee[i];
-          delta[i] = -r;
+        {
+          double yp[PB_VPT], ev[PB_VPT];
+          PB_VEC_FOR(k, i) {
+            yp[k] = (i < PBM_NDIFF) ? yppred[i] : 0.0;
+            ev[k] = (i < PBM_NDIFF) ? ee[i] : 0.0;
+          }
+          PB_VEC_FOR(k, i) {
+            if (i < PBM_N) {
+              double r = delta[i];
+              if (i < PBM_NDIFF) r -= yp[k] + S.cj * ev[k];
+              delta[i] = -r;
+            }
+          }
         }
         PB_SYNC();
         {
@@ -819,13 +881,23 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
         }
         const double scale = (S.scalesol && S.cjratio != 1.0) ? 2.0 / (1.0 + S.cjratio) : 1.0;
         double acc = 0.0;
-        for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
-          const double d = delta[i] * scale;
-          const double e = ee[i] + d;
-          ee[i] = e;
-          yy[i] = yypred[i] + e;
-          const double v = d * ewt[i];
-          acc += v * v;
+        {
+          double ev[PB_VPT], pv[PB_VPT], wv[PB_VPT];
+          PB_VEC_FOR(k, i) {
+            ev[k] = (i < PBM_N) ? ee[i] : 0.0;
+            pv[k] = (i < PBM_N) ? yypred[i] : 0.0;
+            wv[k] = (i < PBM_N) ? ewt[i] : 0.0;
+          }
+          PB_VEC_FOR(k, i) {
+            if (i < PBM_N) {
+              const double d = delta[i] * scale;
+              const double e = ev[k] + d;
+              ee[i] = e;
+              yy[i] = pv[k] + e;
+              const double v = d * wv[k];
+              acc += v * v;
+            }
+          }
         }
         PB_SYNC();
         const double delnrm = sqrt(pb_team_sum(S.team, acc) / PBM_N);
@@ -890,16 +962,26 @@ static PB_DEV int pb_test_error(pb_sys& S, double ck, double* err_k, double* err
   const double* phik = S_PHI(S, kk);
   const double* phikm1 = S_PHI(S, kk > 0 ? kk - 1 : 0);
   double a0 = 0.0, a1 = 0.0, a2 = 0.0;
-  for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
-    const double w = ewt[i];
-    double v = ee[i];
-    a0 += (v * w) * (v * w);
-    if (kk > 1) {
-      v += phik[i];
-      a1 += (v * w) * (v * w);
-      if (kk > 2) {
-        v += phikm1[i];
-        a2 += (v * w) * (v * w);
+  {
+    double wv[PB_VPT], ev[PB_VPT], p1[PB_VPT], p2[PB_VPT];
+    PB_VEC_FOR(k, i) {
+      const bool in = i < PBM_N;
+      wv[k] = in ? ewt[i] : 0.0;
+      ev[k] = in ? ee[i] : 0.0;
+      p1[k] = (in && kk > 1) ? phik[i] : 0.0;
+      p2[k] = (in && kk > 2) ? phikm1[i] : 0.0;
+    }
+    PB_VEC_FOR(k, i) {
+      const double w = wv[k];
+      double v = ev[k];
+      a0 += (v * w) * (v * w);
+      if (kk > 1) {
+        v += p1[k];
+        a1 += (v * w) * (v * w);
+        if (kk > 2) {
+          v += p2[k];
+          a2 += (v * w) * (v * w);
+        }
       }
     }
   }
@@ -981,9 +1063,18 @@ static PB_DEV void pb_complete_step(pb_sys& S, double err_k, double err_km1) {
       const double* phikp1 = S_PHI(S, S.kk + 1);
       const double* ewt = S_EWT(S);
       double acc = 0.0;
-      for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
-        const double v = (ee[i] - phikp1[i]) * ewt[i];
-        acc += v * v;
+      {
+        double ev[PB_VPT], pv[PB_VPT], wv[PB_VPT];
+        PB_VEC_FOR(k, i) {
+          const bool in = i < PBM_N;
+          ev[k] = in ? ee[i] : 0.0;
+          pv[k] = in ? phikp1[i] : 0.0;
+          wv[k] = in ? ewt[i] : 0.0;
+        }
+        PB_VEC_FOR(k, i) {
+          const double v = (ev[k] - pv[k]) * wv[k];
+          acc += v * v;
+        }
       }
       const double enorm = sqrt(pb_team_sum(S.team, acc) / PBM_N);
       err_kp1 = enorm / (S.kk + 2);
@@ -1022,14 +1113,24 @@ static PB_DEV void pb_complete_step(pb_sys& S, double err_k, double err_km1) {
   {
     double* phi = S_PHI(S, 0);
     const int ku = S.kused, save = (ku < S.maxord);
-    for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
-      const double e = ee[i];
-      if (save) phi[(ku + 1) * PBM_N + i] = e;
-      double run = phi[ku * PBM_N + i] + e;
-      phi[ku * PBM_N + i] = run;
-      for (int j = ku - 1; j >= 0; j--) {
-        run += phi[j * PBM_N + i];
-        phi[j * PBM_N + i] = run;
+    double pv[PB_VPT][PB_MXORDP1], ev[PB_VPT];
+    PB_VEC_FOR(k, i) {
+      ev[k] = (i < PBM_N) ? ee[i] : 0.0;
+#pragma unroll
+      for (int j = 0; j < PB_MXORDP1; j++) pv[k][j] = (j <= ku && i < PBM_N) ? phi[j * PBM_N + i] : 0.0;
+    }
+    PB_VEC_FOR(k, i) {
+      if (i < PBM_N) {
+        const double e = ev[k];
+        if (save) phi[(ku + 1) * PBM_N + i] = e;
+        double run = e;
+#pragma unroll
+        for (int j = PB_MXORDP1 - 1; j >= 0; j--) {
+          if (j <= ku) {
+            run += pv[k][j];
+            phi[j * PBM_N + i] = run;
+          }
+        }
       }
     }
   }
@@ -1188,9 +1289,9 @@ static PB_DEV int pb_rcheck3(pb_sys& S) {
   double* glo = S_GLO(S);
   double* grout = S_GROUT(S);
   S.thi = S.tn;
-  pb_get_solution(S, S.thi, S_YY(S));
-  PB_SYNC();
-  pb_gfun(S, S.thi, S_YY(S), S_GHI(S));
+  // y(tn) is phi[0] itself: the interpolant at delt = 0 has c[0] = 1 and c[j >= 1] = 0 (IDAGetSolution), so the
+  // event functions read the history array directly instead of a six-array interpolation pass
+  pb_gfun(S, S.thi, S_PHI(S, 0), S_GHI(S));
   S.ttol = (fabs(S.tn) + fabs(S.hh)) * PB_UROUND * 100.0;
   const int ier = pb_rootfind(S);
   for (int i = 0; i < PBM_NEV; i++)

@@ -45,6 +45,7 @@ PB_FN double pb_team_max(pb_team_ctx&, double x) { return x; }
 #define PB_DEV __device__ __forceinline__
 #define PB_ALIGN16 __align__(16)
 #define PB_TABLE __device__
+#define PB_CTABLE __constant__
 #define PB_FN static __device__ __noinline__
 #define PB_RESTRICT __restrict__
 #define PB_TEAM PB_TEAM_SIZE
@@ -63,6 +64,25 @@ PB_FN double pb_team_max(pb_team_ctx&, double x) { return x; }
 #define PB_LDU(x) __ldg(&(x))
 #define PB_NAN CUDART_NAN
 #define PB_INF CUDART_INF
+
+// Out-of-line copies of the long libm sequences: the generated model functions call them from dozens of sites, and
+// the integration is bound by instruction fetch (1 MB of straight-line code against a 128 KB instruction cache).
+#define PB_NOINLINE_FN(name, expr) \
+  static __device__ __noinline__ double name(double x) { return expr; }
+PB_NOINLINE_FN(pb_f_exp, exp(x))
+PB_NOINLINE_FN(pb_f_log, log(x))
+PB_NOINLINE_FN(pb_f_tanh, tanh(x))
+PB_NOINLINE_FN(pb_f_sinh, sinh(x))
+PB_NOINLINE_FN(pb_f_cosh, cosh(x))
+PB_NOINLINE_FN(pb_f_asinh, asinh(x))
+static __device__ __noinline__ double pb_f_pow(double x, double y) { return pow(x, y); }
+#define PB_EXP(x) pb_f_exp(x)
+#define PB_LOG(x) pb_f_log(x)
+#define PB_TANH(x) pb_f_tanh(x)
+#define PB_SINH(x) pb_f_sinh(x)
+#define PB_COSH(x) pb_f_cosh(x)
+#define PB_ASINH(x) pb_f_asinh(x)
+#define PB_POW(x, y) pb_f_pow(x, y)
 
 struct pb_team_ctx {
   double* red;   // 2 * 32 doubles of shared memory for cross-warp reductions (double buffered)

@@ -90,6 +90,8 @@ class SymbolicLU:
     inv_cluster: np.ndarray = None     # cluster has explicit inverse diagonal blocks (slots ("Q", i, j) / ("P", i, j))
     cluster_kind: list = None          # "chain" | "inv" | "seq" per cluster
     solve_program: list = None         # the records of the solve stream as dicts (code generator input)
+    s_ops: dict = None                 # row -> [(slot, w index)]: solve-form forward coupling  S = -Q L_C,desc
+    t_ops: dict = None                 # row -> [(slot, w index)]: solve-form backward coupling T = -P U_C,anc
 
     def summary(self):
         return (f"n={self.n} nnz_lu={self.nnz_lu} ordering={self.ordering} streams: solve {len(self.solve_stream)} words/"
@@ -281,6 +283,7 @@ INV_MAX = 8         # clusters of 2..INV_MAX rows get explicit inverse diagonal 
 ONE = object()      # placeholder of the constant-one slot (nnz_lu + 1) while slots are still being handed out
 AUX_U = 0xFFFF      # factor task writes an off-diagonal U entry
 AUX_DIAG = 0xFFFE   # factor task writes a diagonal entry (stores the reciprocal)
+AUX_NEG = 0xFFFD    # factor task writes -sum(pairs), ignoring the old value of the slot (solve-form entries)
 
 
 def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01, team=128) -> SymbolicLU:
@@ -382,10 +385,44 @@ def _build(n, rows, cols, perm_r, perm_c, name, team=128) -> SymbolicLU:
                 if pr:
                     slot_of[("P", i, j)] = len(slot_of)
                     p_pairs[(i, j)] = pr
+    # solve form of the coupling blocks: with S = -Q_CC L_C,desc and T = -P_CC U_C,anc (P including 1/u_ii) a cluster
+    # is solved in ONE step per sweep,  x_C = w_C + Q w_C + S z_desc   /   x_C = w_C / u + P w_C + T x_anc .
+    # S and T overwrite L_C,desc and U_C,anc after the factorisation proper (extra slots only for their fill); the
+    # tasks run in levels after all others, rows of a cluster ordered so that an original entry is read by the rows
+    # that need it before its own row replaces it (forward: last row first; backward: first row first).
+    s_tasks, t_tasks = [], []         # (out slot, pairs, rank within the cluster)
+    s_ops, t_ops = {}, {}             # row -> [(slot, w index)] of the solve-form coupling operands
+    for c, rws in enumerate(clusters):
+        if kinds[c] != "inv":
+            continue
+        inside = set(rws)
+        for rank, i in enumerate(reversed(rws)):
+            contrib = [(i, ONE)] + [(j, slot_of[("Q", i, j)]) for j in rws if j < i and ("Q", i, j) in slot_of]
+            cols = {}
+            for j, coef in contrib:
+                for k in Lrows[j]:
+                    if k not in inside:
+                        cols.setdefault(k, []).append((coef, slot_of[(j, k)]))
+            for k in sorted(cols):
+                out = slot_of.setdefault((i, k), len(slot_of)) if (i, k) in slot_of else slot_of.setdefault(("S", i, k), len(slot_of))
+                s_tasks.append((out, cols[k], rank))
+                s_ops.setdefault(i, []).append((out, k))
+        for rank, i in enumerate(rws):
+            contrib = [(i, slot_of[(i, i)])] + [(j, slot_of[("P", i, j)]) for j in rws if j > i and ("P", i, j) in slot_of]
+            cols = {}
+            for j, coef in contrib:
+                for k in Urows[j]:
+                    if k != j and k not in inside:
+                        cols.setdefault(k, []).append((coef, slot_of[(j, k)]))
+            for k in sorted(cols):
+                out = slot_of[(i, k)] if (i, k) in slot_of else slot_of.setdefault(("T", i, k), len(slot_of))
+                t_tasks.append((out, cols[k], rank))
+                t_ops.setdefault(i, []).append((out, k))
     nnz_lu = len(slot_of)
     for d in (q_pairs, p_pairs):
         for key, pr in d.items():
             d[key] = [(a, nnz_lu + 1 if b is ONE else b) for a, b in pr]
+    s_tasks = [(out, [(nnz_lu + 1 if a is ONE else a, b) for a, b in pr], rank) for out, pr, rank in s_tasks]
     diag_slot = np.array([slot_of[(i, i)] for i in range(n)], np.int64)
     a_slot = np.array([slot_of[(int(i), int(j))] for i, j in zip(bi, bj)], np.int64)
 
@@ -433,6 +470,10 @@ def _build(n, rows, cols, perm_r, perm_c, name, team=128) -> SymbolicLU:
         slot_level[slot_of[("P", i, j)]] = lv
         tasks_by_level.setdefault(lv, []).append((slot_of[("P", i, j)], slot_of[(i, i)], pr))
         flops += 2 * len(pr) + 1
+    base = max(tasks_by_level) + 1
+    for out, pr, rank in s_tasks + t_tasks:
+        tasks_by_level.setdefault(base + rank, []).append((out, AUX_NEG, pr))
+        flops += 2 * len(pr)
     nlev = max(tasks_by_level) + 1
     factor = _jds([tasks_by_level.get(l, []) for l in range(nlev)], nnz_lu, nnz_lu)
 
@@ -467,7 +508,8 @@ def _build(n, rows, cols, perm_r, perm_c, name, team=128) -> SymbolicLU:
     bwd = _jds([blv.get(l, []) for l in range(max(blv) + 1)], nnz_lu, n)
     return build_streams(SymbolicLU(n, nnz_lu, np.asarray(perm_r), np.asarray(perm_c), slot_of, a_slot, diag_slot,
                                     factor, fwd, bwd, flops, sflops, name, Lrows=Lrows, Urows=Urows,
-                                    clusters=clusters, cl=cl, inv_cluster=inv_cluster, cluster_kind=kinds), team=team)
+                                    clusters=clusters, cl=cl, inv_cluster=inv_cluster, cluster_kind=kinds,
+                                    s_ops=s_ops, t_ops=t_ops), team=team)
 
 
 # ---------------------------------------------------------------------------
@@ -578,7 +620,7 @@ def _emit_records(words, level_tasks, flags, pad_word, task_word, pad_task, allo
 def build_streams(s: SymbolicLU, team=128):
     """Fill s.solve_stream / s.factor_stream (and the cycle estimates used to rank orderings)."""
     n, nz = s.n, s.nnz_lu
-    assert nz + 3 < 0xFFFE and n + 1 < 0xFFFF, "16-bit packed indices: pattern too large"
+    assert nz + 3 < 0xFFFD and n + 1 < 0xFFFF, "16-bit packed indices: pattern too large"
     one_slot = nz + 1                     # lu[nnz_lu] = 0.0, lu[nnz_lu + 1] = 1.0 (set once by the kernel)
 
     def level_tasks(j: JDS, lv):
@@ -634,6 +676,7 @@ SEQ_NARROW = 1 << 31
 PAR_ADD, PAR_DIAG = 2, 4
 PAR_BASE_CYC, PAR_OP_CYC, PAR_SHFL_CYC = 150, 25, 40
 CHAIN_BASE_CYC, CHAIN_ROW_CYC = 200, 12
+PAR_MLG_SHAPES = (0, 1, 2, 3, 4, 6, 8, 10, 12, 16, 20, 24, 32)   # operand counts per lane the device code is compiled for
 # cycle model of one task (measured B200 latencies: LDS 29, DFMA/DADD 8): chain-critical LDS + 2 DFMA levels + store,
 # + 4 cycles per operand beyond the two prefetched ones (two accumulators) + one dependent LDS pair when ml > 2
 SEQ_TASK_CYC, SEQ_CHUNK_CYC, SEQ_LONG_CYC, SEQ_REC_CYC = 90, 45, 30, 150
@@ -825,6 +868,7 @@ def build_seq_solve_stream(s: SymbolicLU, team=128):
                 while 2 * G * len(blocks[0]) <= 32 and G < maxml:
                     G *= 2
             mlg = (maxml + G - 1) // G
+            mlg = next(v for v in PAR_MLG_SHAPES if v >= mlg) if mlg <= PAR_MLG_SHAPES[-1] else mlg
             desc, body = [], []
             for blk in blocks:
                 nt = len(blk) * G
@@ -861,21 +905,15 @@ def build_seq_solve_stream(s: SymbolicLU, team=128):
                     if nt_:
                         progs.append([cyc, nt_, wd])
                     continue
-                inside = set(rws)
                 for i in rws:
-                    if back:
-                        ext = [(s.slot_of[(i, j)], j) for j in Urows[i] if j != i and j not in inside]
-                        inn = [(s.slot_of[("P", i, j)], j) for j in clusters[c] if j > i and ("P", i, j) in s.slot_of]
-                        if ext:
-                            rows_a.append((i, ext))
-                        rows_b.append((i, inn))           # always: the division by u_ii
-                    else:
-                        ext = [(s.slot_of[(i, k)], k) for k in Lrows[i] if k not in inside]
-                        inn = [(s.slot_of[("Q", i, j)], j) for j in clusters[c] if j < i and ("Q", i, j) in s.slot_of]
-                        if ext:
-                            rows_a.append((i, ext))
-                        if inn:
-                            rows_b.append((i, inn))
+                    if back:     # x_i = w_i / u_ii + sum_j P[i][j] w_j + sum_k T[i][k] x_k
+                        ops = [(s.slot_of[("P", i, j)], j) for j in clusters[c] if j > i and ("P", i, j) in s.slot_of]
+                        rows_b.append((i, ops + s.t_ops.get(i, [])))
+                    else:        # x_i = w_i + sum_j Q[i][j] w_j + sum_k S[i][k] z_k
+                        ops = [(s.slot_of[("Q", i, j)], j) for j in clusters[c] if j < i and ("Q", i, j) in s.slot_of]
+                        ops = ops + s.s_ops.get(i, [])
+                        if ops:
+                            rows_b.append((i, ops))
             group = []
             # chains on the first warps, the first PAR phase of the other clusters beside them on the remaining warps
             first_par = rows_a if rows_a else rows_b
@@ -986,12 +1024,12 @@ def stream_factor(s: SymbolicLU, a_vals):
     for off, nt, ml, fl in _walk(st):
         tw = st[off + 1:off + 1 + nt].astype(np.int64)
         out, aux = tw & 0xFFFF, tw >> 16
-        acc = lu[out].copy()
+        acc = np.where(aux == AUX_NEG, 0.0, lu[out])
         for p in range(ml):
             ow = st[off + 1 + nt + p * nt:off + 1 + nt + (p + 1) * nt].astype(np.int64)
             acc -= lu[ow & 0xFFFF] * lu[ow >> 16]
         for q in range(nt):
-            if aux[q] == AUX_U:
+            if aux[q] == AUX_U or aux[q] == AUX_NEG:
                 lu[out[q]] = acc[q]
             elif aux[q] == AUX_DIAG:
                 lu[out[q]] = 1.0 / acc[q]
