@@ -307,7 +307,7 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
     translation unit (CUDA) or the oracle model shim (C)."""
     if dialect == "cuda" and sym is None:
         sym = slu.analyse(bundle.n_states, bundle.jac_rows, bundle.jac_cols, sample_matrices(bundle),
-                          team=min(default_team(bundle.n_states), 128))
+                          team=default_team(bundle.n_states))
     progs = model_functions(bundle, sym, dialect)
     n_tmp = max(p.n_tmp for p in progs.values())
     n_var = progs["vars"].n_out

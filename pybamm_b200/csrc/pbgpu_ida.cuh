@@ -31,6 +31,7 @@
 #define PB_IDA_LSETUP_FAIL (-6)
 #define PB_IDA_ILL_INPUT (-22)
 
+#define PB_FAC_PAD ((unsigned int)PBM_NNZ_LU | ((unsigned int)PBM_NNZ_LU << 16))   /* zero slot times zero slot */
 #define PB_AUX_U 0xFFFF
 #define PB_AUX_DIAG 0xFFFE
 #define PB_AUX_NEG 0xFFFD   /* out = -sum(pairs): the old value of the slot is not part of the result */
@@ -203,15 +204,15 @@ static PB_DEV int pb_lu_factor(pb_sys& S) {
         const unsigned int* op = st + base + nt + PB_LANE;
         const int k_n = (ml * nt) >> 5;
         double a0 = 0.0, a1 = 0.0;
-        int k = 0;
-        for (; k + 1 < k_n; k += 2) {
-          const unsigned int o0 = PB_FAC_LD(op[32 * k]), o1 = PB_FAC_LD(op[32 * k + 32]);
-          a0 += lu[o0 & 0xFFFFu] * lu[o0 >> 16];
-          a1 += lu[o1 & 0xFFFFu] * lu[o1 >> 16];
-        }
-        if (k < k_n) {
-          const unsigned int o0 = PB_FAC_LD(op[32 * k]);
-          a0 += lu[o0 & 0xFFFFu] * lu[o0 >> 16];
+        for (int k = 0; k < k_n; k += 8) {   // operand words in batches of eight: one L2 round trip per batch
+          unsigned int o[8];
+#pragma unroll
+          for (int j = 0; j < 8; j++) o[j] = (k + j < k_n) ? PB_FAC_LD(op[32 * (k + j)]) : PB_FAC_PAD;
+#pragma unroll
+          for (int j = 0; j < 8; j += 2) {
+            a0 += lu[o[j] & 0xFFFFu] * lu[o[j] >> 16];
+            a1 += lu[o[j + 1] & 0xFFFFu] * lu[o[j + 1] >> 16];
+          }
         }
         a0 += a1;
         for (int o = nt; o < 32; o <<= 1) a0 += __shfl_xor_sync(0xffffffffu, a0, o);
@@ -260,16 +261,24 @@ static PB_DEV int pb_lu_factor(pb_sys& S) {
         const int out = (int)(tw & 0xFFFFu), aux = (int)(tw >> 16);
         const unsigned int* op = st + base + nt + q;
         double acc0 = (aux == PB_AUX_NEG) ? 0.0 : lu[out], acc1 = 0.0;
-        int p = 0;
-        for (; p + 1 < ml; p += 2) {
-          const unsigned int o0 = PB_FAC_LD(op[p * nt]), o1 = PB_FAC_LD(op[(p + 1) * nt]);
-          acc0 -= lu[o0 & 0xFFFFu] * lu[o0 >> 16];
-          acc1 -= lu[o1 & 0xFFFFu] * lu[o1 >> 16];
+#ifndef PB_EMU
+        for (int p = 0; p < ml; p += 8) {   // operand words in batches of eight: one L2 round trip per batch
+          unsigned int o[8];
+#pragma unroll
+          for (int j = 0; j < 8; j++) o[j] = (p + j < ml) ? PB_FAC_LD(op[(p + j) * nt]) : PB_FAC_PAD;
+#pragma unroll
+          for (int j = 0; j < 8; j += 2) {
+            acc0 -= lu[o[j] & 0xFFFFu] * lu[o[j] >> 16];
+            acc1 -= lu[o[j + 1] & 0xFFFFu] * lu[o[j + 1] >> 16];
+          }
         }
-        if (p < ml) {
-          const unsigned int o0 = PB_FAC_LD(op[p * nt]);
-          acc0 -= lu[o0 & 0xFFFFu] * lu[o0 >> 16];
+#else
+        for (int p = 0; p < ml; p++) {
+          const unsigned int o0 = op[p * nt];
+          if (p & 1) acc1 -= lu[o0 & 0xFFFFu] * lu[o0 >> 16];
+          else acc0 -= lu[o0 & 0xFFFFu] * lu[o0 >> 16];
         }
+#endif
         const double acc = acc0 + acc1;
         if (aux == PB_AUX_U || aux == PB_AUX_NEG) {
           lu[out] = acc;

@@ -676,6 +676,7 @@ SEQ_NARROW = 1 << 31
 PAR_ADD, PAR_DIAG = 2, 4
 PAR_BASE_CYC, PAR_OP_CYC, PAR_SHFL_CYC = 150, 25, 40
 CHAIN_BASE_CYC, CHAIN_ROW_CYC = 200, 12
+PAR_WIDE_GROUPS = False   # several lanes per row in multi-warp records: measured no faster, costs stream padding
 PAR_MLG_SHAPES = (0, 1, 2, 3, 4, 6, 8, 10, 12, 16, 20, 24, 32)   # operand counts per lane the device code is compiled for
 # cycle model of one task (measured B200 latencies: LDS 29, DFMA/DADD 8): chain-critical LDS + 2 DFMA levels + store,
 # + 4 cycles per operand beyond the two prefetched ones (two accumulators) + one dependent LDS pair when ml > 2
@@ -776,7 +777,7 @@ def build_seq_solve_stream(s: SymbolicLU, team=128):
             tail[d] = max(tail[d], tail[c] + 1)
     hb = int(tail.max()) - tail
     pad_op = nz | (n << 16)
-    n_warps = max(min(team, 128) // 32, 1)
+    n_warps = max(team // 32, 1)
 
     def seq_task(i, back):
         ops = [(s.slot_of[(i, j)], j) for j in Urows[i] if j != i] if back else [(s.slot_of[(i, k)], k) for k in Lrows[i]]
@@ -846,10 +847,16 @@ def build_seq_solve_stream(s: SymbolicLU, team=128):
         for row, ops in rows_ops:
             units.setdefault(int(cl[row]), []).append((row, ops))
         units = sorted(units.values(), key=lambda u: -len(u))
+        # lanes per row: as many as the warps can hold (with slack for packing whole clusters into warps)
+        maxml_all = max(len(t[1]) for t in rows_ops)
+        Gw = 1
+        while (PAR_WIDE_GROUPS and 2 * Gw * len(rows_ops) <= 24 * nw and 2 * Gw * len(units[0]) <= 32 and Gw < maxml_all
+               and nw > 1):
+            Gw *= 2
         records, cur = [], []
         for u in units:                      # first fit into the blocks of the current record
             for blk in cur:
-                if len(blk) + len(u) <= 32:
+                if (len(blk) + len(u)) * Gw <= 32:
                     blk += u
                     break
             else:
@@ -863,7 +870,7 @@ def build_seq_solve_stream(s: SymbolicLU, team=128):
         for blocks in records:
             nb = len(blocks)
             maxml = max(len(t[1]) for blk in blocks for t in blk)
-            G = 1
+            G = Gw
             if nb == 1:
                 while 2 * G * len(blocks[0]) <= 32 and G < maxml:
                     G *= 2
