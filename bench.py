@@ -71,6 +71,7 @@ def workload_config(args, world):
         "output": "Voltage [V]",
         "sharding": f"batch rows over {world} rank(s), no collective",
         "l2": "flushed between timed steps (256 MiB write)",
+        "launch_order": "rows handed to the teams by descending cost proxy (|current|), results in row order",
     }
 
 
@@ -253,6 +254,12 @@ def run_b200_arm(args):
     stream = torch.cuda.Stream(device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     vp = C.c_void_p
+    # launch order of the persistent kernel: expensive rows first (shard.launch_order; results stay in row order)
+    from pybamm_b200.shard import launch_order
+
+    order = np.ascontiguousarray(launch_order(p, bundle.input_names), dtype=np.int32)
+    if lib.pbgpu_solver_set_launch_order(solver._solver, order.ctypes.data_as(vp), n):
+        raise RuntimeError(lib.pbgpu_last_error().decode())
 
     def launch():
         rc = lib.pbgpu_solve_device(solver._solver, n, vp(d_te.data_ptr()), len(te), vp(d_ti.data_ptr()), len(ti), None,

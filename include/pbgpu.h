@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define PBGPU_ABI_VERSION 2
+#define PBGPU_ABI_VERSION 3
 
 typedef struct pbgpu_model_s* pbgpu_model_t;
 typedef struct pbgpu_solver_s* pbgpu_solver_t;
@@ -108,6 +108,12 @@ int pbgpu_solver_create(pbgpu_model_t model, const double* atol, const pbgpu_opt
                         pbgpu_solver_t* solver);
 int pbgpu_solver_destroy(pbgpu_solver_t solver);
 
+/* Launch order of the next solves with n systems (host array of n distinct row indices, or NULL / n = 0 to clear):
+ * teams pull systems from a queue, and a batch ends when its slowest system does, so the expensive rows should be
+ * handed out first.  Results stay in row order.  The reference has no equivalent: it splits the batch in static
+ * contiguous chunks (IDAKLUSolverGroup.cpp:99-126). */
+int pbgpu_solver_set_launch_order(pbgpu_solver_t solver, const int* order, int n);
+
 /* Number of time points a result block must hold per system for these grids. */
 int pbgpu_result_capacity(int n_teval, int n_tinterp);
 
@@ -130,7 +136,9 @@ int pbgpu_solve_device(pbgpu_solver_t solver, int n_sys, const double* t_eval, i
 
 /* Evaluate generated model functions / the sparse LU on the device for n_sys (y, p) pairs (parity tests
  * of the code generator).  which: 0 res, 1 jac (bundle CSC order), 2 events, 3 ic, 4 vars,
- * 5 solve (J - cj*M) x = rhs with rhs = y2.  Host pointers. */
+ * 5 solve (J - cj*M) x = rhs with rhs = y2; 8 events at per-system times t_sys = y2[sys][0] (which event ended each
+ * system of a batch: idaklu_solver.py:826-834); 6 / 7 cycle probes of the building blocks (tools/gpu_cycles.py,
+ * tools/gpu_solve_loop.py).  Host pointers. */
 int pbgpu_model_eval(pbgpu_solver_t solver, int which, int n_sys, const double* y, const double* p, double t,
                      double cj, const double* y2, double* out, int out_len);
 
@@ -152,6 +160,7 @@ typedef struct {
   long long* stats;
   unsigned int* queue;
   double* scratch;      /* [teams][scratch_doubles_per_team] device memory owned by the solver handle, may be NULL if 0 */
+  const int* order;     /* [n_sys] or NULL: the k-th system handed out by the queue is order[k] */
   pbgpu_options opt;
 } pbgpu_launch;
 

@@ -72,8 +72,9 @@ struct pbgpu_solver_s {
   pbgpu_options opt;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-  DevBuf atol, t_eval, t_interp, inputs, y0, t_out, y_out, n_out, flag, y_term, stats, queue, scratch_a, scratch_b, team_scratch;
+  DevBuf atol, t_eval, t_interp, inputs, y0, t_out, y_out, n_out, flag, y_term, stats, queue, scratch_a, scratch_b, team_scratch, order;
   int last_grid = 0;
+  int order_n = 0;
 };
 
 extern "C" {
@@ -191,7 +192,7 @@ int pbgpu_solver_destroy(pbgpu_solver_t s) {
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
   DevBuf* bufs[] = {&s->atol, &s->t_eval, &s->t_interp, &s->inputs, &s->y0, &s->t_out, &s->y_out, &s->n_out,
-                    &s->flag, &s->y_term, &s->stats, &s->queue, &s->scratch_a, &s->scratch_b, &s->team_scratch};
+                    &s->flag, &s->y_term, &s->stats, &s->queue, &s->scratch_a, &s->scratch_b, &s->team_scratch, &s->order};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 4; i++)
     if (s->ev[i]) cudaEventDestroy(s->ev[i]);
@@ -255,6 +256,7 @@ static int launch_common(pbgpu_solver_s* s, int n_sys, const double* d_t_eval, i
   L.queue = (unsigned int*)s->queue.p;
   if (ensure_team_scratch(s, n_sys)) return 1;
   L.scratch = (double*)s->team_scratch.p;
+  L.order = (s->order_n == n_sys && n_sys > 0) ? (const int*)s->order.p : nullptr;
   L.opt = s->opt;
   CK(cudaMemsetAsync(s->queue.p, 0, sizeof(unsigned int), stream));
   char err[512];
@@ -339,6 +341,25 @@ int pbgpu_solve(pbgpu_solver_t s, int n_sys, const double* t_eval, int n_teval, 
   if (e != cudaSuccess) return cuda_fail("integration kernel", e);
   CK(cudaEventElapsedTime(&out->kernel_ms, s->ev[1], s->ev[2]));
   CK(cudaEventElapsedTime(&out->total_ms, s->ev[0], s->ev[3]));
+  return 0;
+}
+
+int pbgpu_solver_set_launch_order(pbgpu_solver_t s, const int* order, int n) {
+  if (!s) return fail("pbgpu_solver_set_launch_order: bad argument");
+  if (!order || n <= 0) {
+    s->order_n = 0;
+    return 0;
+  }
+  std::vector<char> seen((size_t)n, 0);
+  for (int i = 0; i < n; i++) {
+    if (order[i] < 0 || order[i] >= n || seen[(size_t)order[i]]) return fail("pbgpu_solver_set_launch_order: not a permutation of 0..n-1");
+    seen[(size_t)order[i]] = 1;
+  }
+  CK(cudaSetDevice(s->device));
+  if (s->order.ensure(sizeof(int) * (size_t)n)) return 1;
+  CK(cudaMemcpyAsync(s->order.p, order, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  s->order_n = n;
   return 0;
 }
 

@@ -33,10 +33,10 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_s
   for (;;) {
     if (threadIdx.x == 0) next_sys = atomicAdd(L.queue, 1u);
     __syncthreads();
-    const unsigned int sys = next_sys;
+    const unsigned int slot = next_sys;
     __syncthreads();
-    if (sys >= (unsigned int)L.n_sys) break;
-    pb_solve_system(S, L, (int)sys);
+    if (slot >= (unsigned int)L.n_sys) break;
+    pb_solve_system(S, L, L.order ? L.order[slot] : (int)slot);
   }
 }
 
@@ -100,6 +100,13 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_e
         pb_lu_solve(S, out);
         for (int i = PB_TID; i < PBM_N && i < E.out_len; i += PB_TEAM) gout[i] = bad ? CUDART_NAN : out[i];
       } break;
+      case 8:   // events at per-system times: t of system sys is y2[sys][0] (event identification of a whole batch)
+#if PBM_NEV > 0
+        pbm_events(y, S_P(S), E.y2[(size_t)sys * PBM_N], E.cj, S_GHI(S), S_TMP(S));
+        PB_SYNC();
+        for (int i = PB_TID; i < PBM_NEV && i < E.out_len; i += PB_TEAM) gout[i] = S_GHI(S)[i];
+#endif
+        break;
       case 6: {   // clock64() cycles per call of the building blocks, measured in place (tools/gpu_cycles.py)
         const int reps = 16;
         long long c[6];

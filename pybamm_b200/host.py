@@ -54,7 +54,7 @@ class LaunchArgs(C.Structure):
         ("n_ret", C.c_int), ("t_eval", C.c_void_p), ("t_interp", C.c_void_p), ("inputs", C.c_void_p),
         ("y0", C.c_void_p), ("atol", C.c_void_p), ("t_out", C.c_void_p), ("y_out", C.c_void_p),
         ("n_out", C.c_void_p), ("flag", C.c_void_p), ("y_term", C.c_void_p), ("stats", C.c_void_p),
-        ("queue", C.c_void_p), ("scratch", C.c_void_p), ("opt", Options),
+        ("queue", C.c_void_p), ("scratch", C.c_void_p), ("order", C.c_void_p), ("opt", Options),
     ]
 
 

@@ -13,16 +13,22 @@ import numpy as np
 
 
 def cost_proxy(inputs: np.ndarray, input_names=None) -> np.ndarray:
-    """Expected work per system.  Lower |current| -> longer discharge -> more steps; falls back to
-    uniform cost when the model has no current input."""
+    """Expected work per system.  Measured on the DFN bench (10 000 sets, 2.5-7.5 A): the step count GROWS with the
+    current (correlation +0.55; 371 to 4 030 steps around a mean of 731) -- a fast discharge ends on the steep knee of the
+    voltage curve, where the step size collapses, while a slow one just runs to the final time.  Falls back to uniform
+    cost when the model has no current input."""
     inputs = np.asarray(inputs, dtype=np.float64)
     n = inputs.shape[0]
     if input_names is not None and "Current function [A]" in input_names and inputs.shape[1]:
         cur = np.abs(inputs[:, list(input_names).index("Current function [A]")])
-        with np.errstate(divide="ignore"):
-            c = 1.0 / np.maximum(cur, 1e-300)
-        return np.where(np.isfinite(c), c, 0.0)
+        return np.where(np.isfinite(cur), cur, 0.0)
     return np.ones(n)
+
+
+def launch_order(inputs: np.ndarray, input_names=None) -> np.ndarray:
+    """Row order for one device: most expensive systems first, so that the persistent kernel's teams do not end the
+    batch waiting for one long straggler (the queue hands out rows in index order)."""
+    return np.argsort(-cost_proxy(inputs, input_names), kind="stable")
 
 
 def partition(n_sys: int, n_shards: int, cost=None):

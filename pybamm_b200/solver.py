@@ -334,6 +334,12 @@ class BatchedIDASolver:
         res.n_max, res.n_ret = n_max, n_ret
         res.t, res.y, res.n_t, res.flag = _ptr(t_out), _ptr(y_out), _ptr(n_t), _ptr(flag)
         res.y_term, res.stats = _ptr(y_term), _ptr(stats)
+        # expensive systems first: the batch ends when its slowest system does (results stay in row order)
+        from .shard import launch_order
+
+        order = np.ascontiguousarray(launch_order(inputs, self.bundle.input_names), dtype=np.int32)
+        if lib.pbgpu_solver_set_launch_order(self._solvers[k], _ptr(order), n_sys):
+            raise SolverError(_err(lib))
         rc = lib.pbgpu_solve(self._solvers[k], n_sys, _ptr(t_eval), len(t_eval), _ptr(t_interp) if len(t_interp) else None,
                              len(t_interp), _ptr(y0), _ptr(inputs), output_mode, C.byref(res))
         if rc:
@@ -396,6 +402,13 @@ class BatchedIDASolver:
             y2 = np.ascontiguousarray(np.atleast_2d(np.asarray(y2, dtype=np.float64)))
         t_arr = np.broadcast_to(np.asarray(t, dtype=np.float64), (n_sys,))
         out = np.zeros((n_sys, out_len))
+        if which == "events" and not np.all(t_arr == t_arr[0]):
+            # one launch for the whole batch: per-system times travel in column 0 of the y2 block (which = 8)
+            tcol = np.zeros((n_sys, D.n_states))
+            tcol[:, 0] = t_arr
+            if self._lib.pbgpu_model_eval(self._solver, 8, n_sys, _ptr(y), _ptr(p), 0.0, float(cj), _ptr(tcol), _ptr(out), out_len):
+                raise SolverError(_err(self._lib))
+            return out
         if np.all(t_arr == t_arr[0]):
             if self._lib.pbgpu_model_eval(self._solver, idx, n_sys, _ptr(y), _ptr(p), float(t_arr[0]), float(cj),
                                           _ptr(y2), _ptr(out), out_len):

@@ -254,6 +254,26 @@ def test_device_pointer_entry_point():
         np.testing.assert_array_equal(y_out[i, :k, 0].cpu().numpy(), ref["y"][i, :k, 0])
 
 
+def test_batched_event_identification_matches_per_system_evaluation():
+    """solve(inputs=[{...}] * n) names the event that ended every system from ONE device launch (which = 8, per-system
+    times); it must agree with the per-system evaluation of the event functions (idaklu_solver.py:826-834)."""
+    b = util.bundle("spme")
+    s = gpu("spme")
+    n = 24
+    p = util.sample_inputs(b, n, np.random.default_rng(11))
+    dicts = [dict(zip(b.input_names, row.tolist())) for row in p]
+    sols = s.solve(util.T_EVAL, inputs=dicts, t_interp=util.T_INTERP)
+    r = s.solve_arrays(util.T_EVAL, p, t_interp=util.T_INTERP)
+    t_end = np.array([r["t"][i, r["n_t"][i] - 1] for i in range(n)])
+    batched = s.eval("events", r["y_term"], p, t_end)
+    single = np.vstack([s.eval("events", r["y_term"][i:i + 1], p[i:i + 1], float(t_end[i])) for i in range(n)])
+    np.testing.assert_array_equal(batched, single)
+    assert np.any(r["flag"] == 2)
+    for i, sol in enumerate(sols):
+        want = f"event: {b.event_names[int(np.argmin(np.abs(single[i])))]}" if r["flag"][i] == 2 else "final time"
+        assert sol.termination == want, (i, sol.termination, want)
+
+
 # ---- BASELINE.json sizes: size-independent properties ---------------------------------------------------------
 def test_config1_spm_1000_sets_properties():
     b = util.bundle("spm")

@@ -23,7 +23,7 @@ def _declared_functions():
 
 def test_c_abi_library_exports_every_declared_symbol():
     names = _declared_functions()
-    assert {"pbgpu_model_load", "pbgpu_solver_create", "pbgpu_solve", "pbgpu_solve_device", "pbgpu_model_eval",
+    assert {"pbgpu_model_load", "pbgpu_solver_create", "pbgpu_solve", "pbgpu_solve_device", "pbgpu_model_eval", "pbgpu_solver_set_launch_order",
             "pbgpu_last_error", "pbgpu_result_capacity", "pbgpu_default_options"} <= set(names)
     lib = ctypes.CDLL(build.build_api())
     for n in names:
