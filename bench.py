@@ -75,6 +75,27 @@ def workload_config(args, world):
     }
 
 
+def ncu_dram_traffic(n_sys):
+    """dram__bytes_read.sum + dram__bytes_write.sum of pbgpu_solve_kernel from the committed `ncu --set full` capture
+    (one launch of 148 DFN systems, profiles/r01_dfn_full_ncu_raw.csv), scaled to this launch's system count.
+    Returns (bytes per launch or None, provenance)."""
+    path = os.path.join(ROOT, "profiles", "r01_dfn_full_ncu_raw.csv")
+    try:
+        import csv
+
+        vals = {}
+        for row in csv.reader(open(path)):
+            if len(row) == 3 and row[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                vals[row[0]] = float(row[2]) * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[row[1]]
+        if len(vals) == 2:
+            per_sim = (vals["dram__bytes_read.sum"] + vals["dram__bytes_write.sum"]) / 148.0
+            return per_sim * n_sys, ("profiles/r01_dfn_full_ncu_raw.csv: ncu --set full, one launch of 148 systems "
+                                     f"({per_sim / 1e3:.1f} KB per simulation), scaled to {n_sys} systems")
+    except Exception:
+        pass
+    return None, "no ncu capture found"
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
 
@@ -351,9 +372,11 @@ def run_b200_arm(args):
         except Exception:
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        traffic, traffic_src = ncu_dram_traffic(n)
         line["roofline"] = {
             "bound": "fp64", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
-            "traffic": None, "kernel": "pbgpu_solve_kernel", "flop_per_simulation": w, "work_terms": terms,
+            "traffic": traffic, "traffic_source": traffic_src, "kernel": "pbgpu_solve_kernel", "flop_per_simulation": w,
+            "work_terms": terms,
             "peak_source": "DFMA microbenchmark measured in this run (pbgpu_peak.cu); MEASURED_PEAKS.json has no FP64 entry",
             "hbm": {"achieved": alg_bytes * n / kernel_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
                     "frac": alg_bytes * n / kernel_s / 1e9 / hbm_peak,

@@ -819,26 +819,29 @@ def build_seq_solve_stream(s: SymbolicLU, team=128):
         return dict(kind=0, mode=1 if back else 0, nblocks=nb, param=0, desc=desc, body=body, cyc=progs[0][0],
                     threads=[d & 0xFFFF for d in desc])
 
-    def chain_record(cs, back, nw):
+    def chain_records(cs, back, nw):
         """kind 2: one lane per chain, three words per lane: [first row | K << 16] [L slot of row 1 | U slot of row 0 << 16]
-        [parent row of the last chain row]"""
+        [parent row of the last chain row].  One record per 32 * nw chains."""
         cs = sorted(cs, key=lambda c: -len(clusters[c]))
-        nb = min(nw, (len(cs) + 31) // 32)
-        assert len(cs) <= 32 * nb, "more chains than lanes"
-        desc, body = [], []
-        for v in range(nb):
-            blk = cs[v::nb]
-            m = np.zeros((3, len(blk)), np.int64)
-            for q, c in enumerate(blk):
-                rws = clusters[c]
-                m[0, q] = rws[0] | (len(rws) << 16)
-                m[1, q] = s.slot_of[(rws[1], rws[0])] | (s.slot_of[(rws[0], rws[1])] << 16)
-                m[2, q] = Urows[rws[-1]][1]
-            desc.append(len(blk))
-            body += m.reshape(-1).tolist()
-        K = len(clusters[cs[0]])
-        return dict(kind=2, mode=1 if back else 0, nblocks=nb, param=K, desc=desc, body=body,
-                    cyc=CHAIN_BASE_CYC + CHAIN_ROW_CYC * K, threads=desc)
+        out = []
+        for at in range(0, len(cs), 32 * nw):
+            part = cs[at:at + 32 * nw]
+            nb = min(nw, (len(part) + 31) // 32)
+            desc, body = [], []
+            for v in range(nb):
+                blk = part[v::nb]
+                m = np.zeros((3, len(blk)), np.int64)
+                for q, c in enumerate(blk):
+                    rws = clusters[c]
+                    m[0, q] = rws[0] | (len(rws) << 16)
+                    m[1, q] = s.slot_of[(rws[1], rws[0])] | (s.slot_of[(rws[0], rws[1])] << 16)
+                    m[2, q] = Urows[rws[-1]][1]
+                desc.append(len(blk))
+                body += m.reshape(-1).tolist()
+            K = len(clusters[part[0]])
+            out.append(dict(kind=2, mode=1 if back else 0, nblocks=nb, param=K, desc=desc, body=body,
+                            cyc=CHAIN_BASE_CYC + CHAIN_ROW_CYC * K, threads=desc))
+        return out
 
     def par_records(rows_ops, mode, nw):
         """rows_ops: list of (row, [(slot, w index), ...]).  The rows of one cluster stay in one block (= one warp): they
@@ -934,9 +937,11 @@ def build_seq_solve_stream(s: SymbolicLU, team=128):
                 side_by_side = False          # not worth a third concurrent stream: one record after the other
                 seq_w = n_warps
             if chains:
-                r = chain_record(chains, back, seq_w if len(chains) > 32 or side_by_side else 1)
-                r["first_warp"] = 0
-                group.append(r)
+                if len(chains) > 32 * seq_w:
+                    side_by_side = False      # several chain records: no PAR record beside them
+                for r in chain_records(chains, back, seq_w if len(chains) > 32 or side_by_side else 1):
+                    r["first_warp"] = 0
+                    group.append(r)
             if progs:
                 r = seq_record(progs, back, seq_w if len(progs) > 32 or side_by_side else 1)
                 r["first_warp"] = 0
