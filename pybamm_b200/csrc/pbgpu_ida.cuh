@@ -308,6 +308,7 @@ static PB_DEV int pb_lu_factor(pb_sys& S) {
 #define PB_SEQ_HDR 4
 #define PB_PAR_ADD 2u
 #define PB_PAR_DIAG 4u
+#define PB_PAR_PAD ((unsigned int)PBM_NNZ_LU | ((unsigned int)PBM_N << 16))   /* zero L/U slot times w[N] = 0 */
 
 template <int BWD>
 static PB_DEV void pb_seq_thread(const unsigned int* PB_RESTRICT p, const int nt, const double* PB_RESTRICT lu,
@@ -395,6 +396,41 @@ static __device__ __noinline__ void pb_par_rec(const unsigned int* PB_RESTRICT b
     const double acc = (MODE & PB_PAR_ADD) ? base + sum : base - sum;
     __syncwarp(mask);
     if (G == 1 || (PB_LANE & (G - 1)) == 0) w[row] = acc;
+  }
+}
+
+// The same record with run-time shape: ONE copy of the code for every PAR record (about 1.5 KB of instructions
+// instead of one function per shape).  Operands in chunks of four, each chunk's loads issued together.
+static __device__ __noinline__ void pb_par_generic(const unsigned int* PB_RESTRICT blk, const int nt, const int G, const int mlg,
+                                                   const unsigned int mode, const double* PB_RESTRICT lu,
+                                                   double* PB_RESTRICT w) {
+  const unsigned int mask = nt == 32 ? 0xffffffffu : ((1u << nt) - 1u);
+  if (PB_LANE < nt) {
+    const unsigned int* p = blk + PB_LANE;
+    const int row = (int)p[0];
+    const double wr = w[row];
+    const double ld = (mode & PB_PAR_DIAG) ? lu[row] : 1.0;
+    double s0 = 0.0, s1 = 0.0;
+    p += nt;
+    for (int j = 0; j < mlg; j += 4) {
+      const unsigned int a0 = p[0];
+      const unsigned int a1 = (j + 1 < mlg) ? p[nt] : PB_PAR_PAD;
+      const unsigned int a2 = (j + 2 < mlg) ? p[2 * nt] : PB_PAR_PAD;
+      const unsigned int a3 = (j + 3 < mlg) ? p[3 * nt] : PB_PAR_PAD;
+      p += 4 * nt;
+      const double x0 = lu[a0 & 0xFFFFu], y0 = w[a0 >> 16], x1 = lu[a1 & 0xFFFFu], y1 = w[a1 >> 16];
+      const double x2 = lu[a2 & 0xFFFFu], y2 = w[a2 >> 16], x3 = lu[a3 & 0xFFFFu], y3 = w[a3 >> 16];
+      s0 = fma(x0, y0, s0);
+      s1 = fma(x1, y1, s1);
+      s0 = fma(x2, y2, s0);
+      s1 = fma(x3, y3, s1);
+    }
+    double sum = s0 + s1;
+    for (int o = 1; o < G; o <<= 1) sum += __shfl_xor_sync(mask, sum, o);
+    const double base = wr * ld;
+    const double acc = (mode & PB_PAR_ADD) ? base + sum : base - sum;
+    __syncwarp(mask);
+    if ((PB_LANE & (G - 1)) == 0) w[row] = acc;
   }
 }
 
