@@ -77,20 +77,23 @@ def workload_config(args, world):
 
 def ncu_dram_traffic(n_sys):
     """dram__bytes_read.sum + dram__bytes_write.sum of pbgpu_solve_kernel from the committed `ncu --set full` capture
-    (one launch of 148 DFN systems, profiles/r01_dfn_full_ncu_raw.csv), scaled to this launch's system count.
+    (profiles/r01_dfn_full_ncu_raw.csv: `ncu --page raw --csv` of one launch with one DFN system per team, so the
+    grid size is the number of systems), scaled to this launch's system count.
     Returns (bytes per launch or None, provenance)."""
     path = os.path.join(ROOT, "profiles", "r01_dfn_full_ncu_raw.csv")
     try:
         import csv
 
-        vals = {}
-        for row in csv.reader(open(path)):
-            if len(row) == 3 and row[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-                vals[row[0]] = float(row[2]) * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[row[1]]
-        if len(vals) == 2:
-            per_sim = (vals["dram__bytes_read.sum"] + vals["dram__bytes_write.sum"]) / 148.0
-            return per_sim * n_sys, ("profiles/r01_dfn_full_ncu_raw.csv: ncu --set full, one launch of 148 systems "
-                                     f"({per_sim / 1e3:.1f} KB per simulation), scaled to {n_sys} systems")
+        rows = [r for r in csv.reader(open(path)) if r]
+        hdr, units, vals = rows[0], rows[1], rows[2]
+        col = {h: k for k, h in enumerate(hdr)}
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        total = sum(float(vals[col[m]].replace(",", "")) * scale[units[col[m]]]
+                    for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+        n_cap = int(float(vals[col["launch__grid_size"]].replace(",", "")))
+        per_sim = total / n_cap
+        return per_sim * n_sys, (f"profiles/r01_dfn_full_ncu_raw.csv: ncu --set full, one launch of {n_cap} systems "
+                                 f"({per_sim / 1e3:.1f} KB per simulation), scaled to {n_sys} systems")
     except Exception:
         pass
     return None, "no ncu capture found"

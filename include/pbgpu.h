@@ -36,6 +36,7 @@
 extern "C" {
 #endif
 
+#define PBGPU_QUEUE_WORDS (32 + 8 * 256)
 #define PBGPU_ABI_VERSION 3
 
 typedef struct pbgpu_model_s* pbgpu_model_t;
@@ -158,7 +159,9 @@ typedef struct {
   int* flag;
   double* y_term;
   long long* stats;
-  unsigned int* queue;
+  unsigned int* queue;   /* [PBGPU_QUEUE_WORDS], zeroed before every launch: word 0 = next system to hand out; from word
+                            32 on, 8 words per SM: the mailbox through which the two teams resident on one SM keep their
+                            Newton iterations in phase (pbgpu_ida.cuh, pb_align) */
   double* scratch;      /* [teams][scratch_doubles_per_team] device memory owned by the solver handle, may be NULL if 0 */
   const int* order;     /* [n_sys] or NULL: the k-th system handed out by the queue is order[k] */
   pbgpu_options opt;

@@ -82,7 +82,7 @@ def build_oracle(bundle: ModelBundle, force=False):
     return out
 
 
-def build_model(bundle: ModelBundle, force=False, team=None, verbose=False, profile=False, tag=""):
+def build_model(bundle: ModelBundle, force=False, team=None, verbose=False, profile=False, tag="", defines=(), extra_flags=()):
     """Generate + nvcc-compile the sm_100a solver image of a bundle. Returns the .so path."""
     os.makedirs(BUILD, exist_ok=True)
     header, info = generate(bundle, "cuda", BUILD)
@@ -94,12 +94,12 @@ def build_model(bundle: ModelBundle, force=False, team=None, verbose=False, prof
         team = default_team(bundle)
     gvec = 1 if bundle.n_states > 256 else 0   # streamed vectors in global scratch for large models (pbgpu_ida.cuh)
     min_teams = 2 if gvec else 1               # register cap: two large teams per SM (65536 / (2 * team) registers each)
-    dig = _src_digest(srcs) + f"-t{team}-g{gvec}-m{min_teams}-p{int(profile)}-" + hashlib.sha256(" ".join(NVCC_FLAGS).encode()).hexdigest()[:8]
+    dig = _src_digest(srcs) + f"-t{team}-g{gvec}-m{min_teams}-p{int(profile)}-{'-'.join(defines)}-{'-'.join(extra_flags)}-" + hashlib.sha256(" ".join(NVCC_FLAGS).encode()).hexdigest()[:8]
     stamp = out + ".stamp"
     if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:
         return out
     cmd = [NVCC] + NVCC_FLAGS + [f"-DPBM_HEADER=\"{header}\"", f"-DPB_TEAM_SIZE={team}", f"-DPB_GLOBAL_VEC={gvec}", f"-DPB_MIN_TEAMS={min_teams}", f"-I{inc}", f"-I{CSRC}",
-                                 kernel_srcs[0], "-o", out] + ([f"-DPB_PROFILE={int(profile)}"] if profile else [])
+                                 kernel_srcs[0], "-o", out] + ([f"-DPB_PROFILE={int(profile)}"] if profile else []) + [f"-D{d}" for d in defines] + list(extra_flags)
     r = subprocess.run(cmd, capture_output=True, text=True)
     log = r.stdout + r.stderr
     with open(out[:-3] + ".ptxas.log", "w") as f:

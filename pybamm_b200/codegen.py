@@ -256,48 +256,89 @@ def sample_matrices(bundle, p_nominal=None, n_samples=2, seed=0):
 PAR_GENERIC = bool(int(__import__("os").environ.get("PBGPU_PAR_GENERIC", "1")))
 
 
+# Single-warp PAR records in a row that go through the software-pipelined loop pb_par_run instead of one call each.
+# Measured on the DFN: no faster alone (745 against 750 cycles per record: the record is bound by instruction issue,
+# not by the loads the pipeline hides) and 3 % slower inside the integration (larger instruction footprint): off.
+PAR_RUN_MIN = int(__import__("os").environ.get("PBGPU_PAR_RUN_MIN", "99"))
+
+
 def emit_solve_program(sym: slu.SymbolicLU) -> str:
-    """The triangular solves as straight-line code: one specialised call per record of the solve stream (record shapes
-    are compile-time constants, so the device code has no record decoding, no operand loops and every load of a
-    record can be issued up front).  Expanded inside pb_lu_solve (pbgpu_ida.cuh), which defines st, lu, w."""
-    out, open_narrow = [], False
-    for r in sym.solve_program:
+    """The triangular solves as a call sequence: one call per record of the solve stream, expanded inside
+    pb_solve_program (pbgpu_ida.cuh), which defines st, lu, w.  Runs of single-warp PAR records (the top of the
+    elimination tree) become ONE call of the software-pipelined loop pb_par_run, with their shapes in the constant
+    table pbm_par_run."""
+    out, run_desc = [], []
+    recs = sym.solve_program
+
+    def call_of(r, v, boff):
+        nt = r["desc"][v] & 0xFFFF
+        if r["kind"] == 1:
+            G, mlg = r["param"] & 0xFF, r["param"] >> 8
+            call = (f"pb_par_generic(st + {boff}, {nt}, {G}, {mlg}, {r['mode']}u, lu, w);" if PAR_GENERIC else
+                    f"pb_par_rec<{G}, {mlg}, {r['mode']}>(st + {boff}, {nt}, lu, w);")
+            return call, boff + (1 + mlg) * nt
+        if r["kind"] == 2:
+            return f"pb_chain_rec<{r['mode'] & 1}>(st + {boff}, {nt}, lu, w);", boff + 3 * nt
+        return f"pb_seq_rec<{r['mode'] & 1}>(st + {boff}, {nt}, lu, w);", boff + nt * (r["desc"][v] >> 16)
+
+    i = 0
+    while i < len(recs):
+        r = recs[i]
+        if r.get("narrow"):
+            j = i
+            while recs[j]["sync"] == 1:     # the run ends with the record that carries the team barrier
+                j += 1
+            run = recs[i:j + 1]
+            assert all(q.get("narrow") and q["nblocks"] == 1 and q["first_warp"] == 0 for q in run)
+            out.append("if (PB_WARP == 0) {")
+            k = 0
+            while k < len(run):
+                m = k
+                while m < len(run) and run[m]["kind"] == 1:
+                    m += 1
+                if PAR_GENERIC and m - k >= PAR_RUN_MIN:
+                    out.append(f"  pb_par_run(st, {len(run_desc)}, {m - k}, lu, w);")
+                    for q in run[k:m]:
+                        nt, G, mlg = q["desc"][0] & 0xFFFF, q["param"] & 0xFF, q["param"] >> 8
+                        boff = q["offset"] + slu.SEQ_HDR + 1
+                        assert boff < 65536 and nt <= 32 and mlg < 256
+                        run_desc.append((boff | nt << 16, G | mlg << 8 | q["mode"] << 16))
+                    out.append("  PB_REC_MARK")
+                    k = m
+                else:
+                    q = run[k]
+                    out.append("  " + call_of(q, 0, q["offset"] + slu.SEQ_HDR + 1)[0])
+                    out.append("  PB_SYNCWARP();")
+                    out.append("  PB_REC_MARK")
+                    k += 1
+            out.append("}")
+            out.append("PB_SYNC();")
+            out.append("PB_REC_MARK")
+            i = j + 1
+            continue
         boff = r["offset"] + slu.SEQ_HDR + r["nblocks"]
+        if r["kind"] == 3:              # dense top block: all threads, barriers inside
+            out += [f"PB_DENSE_REC({boff})", "PB_REC_MARK"]
+            i += 1
+            continue
         calls = []
         for v in range(r["nblocks"]):
-            nt = r["desc"][v] & 0xFFFF
-            if r["kind"] == 1:
-                G, mlg = r["param"] & 0xFF, r["param"] >> 8
-                call = (f"pb_par_generic(st + {boff}, {nt}, {G}, {mlg}, {r['mode']}u, lu, w);" if PAR_GENERIC else
-                        f"pb_par_rec<{G}, {mlg}, {r['mode']}>(st + {boff}, {nt}, lu, w);")
-                boff += (1 + mlg) * nt
-            elif r["kind"] == 2:
-                call = f"pb_chain_rec<{r['mode'] & 1}>(st + {boff}, {nt}, lu, w);"
-                boff += 3 * nt
-            else:
-                call = f"pb_seq_rec<{r['mode'] & 1}>(st + {boff}, {nt}, lu, w);"
-                boff += nt * (r["desc"][v] >> 16)
+            call, boff = call_of(r, v, boff)
             calls.append((r["first_warp"] + v, call))
-        if r.get("narrow"):
-            if not open_narrow:
-                out.append("if (PB_WARP == 0) {")
-                open_narrow = True
-            out.append("  " + calls[0][1])
-            if r["sync"] == 1:
-                out.append("  PB_SYNCWARP();")
-            else:
-                out.append("}")
-                out.append("PB_SYNC();")
-                open_narrow = False
-        else:
-            assert not open_narrow
-            out.append(" else ".join(f"if (PB_WARP == {wv}) {{ {c} }}" for wv, c in calls))
-            if r["sync"] == 2:
-                out.append("PB_SYNC();")
-            elif r["sync"] == 1:
-                out.append("PB_SYNCWARP();")
-    assert not open_narrow
-    return "#define PBM_SOLVE_PROGRAM \\\n  " + " \\\n  ".join(out) + "\n"
+        out.append(" else ".join(f"if (PB_WARP == {wv}) {{ {c} }}" for wv, c in calls))
+        if r["sync"] == 2:
+            out.append("PB_SYNC();")
+        elif r["sync"] == 1:
+            out.append("PB_SYNCWARP();")
+        out.append("PB_REC_MARK")
+        i += 1
+    text = ""
+    if run_desc:
+        flat = [x for d in run_desc for x in d]
+        text += f"#define PBM_PAR_RUN_N {len(run_desc)}\n"
+        text += (f"static PB_CTABLE const unsigned int pbm_par_run[{len(flat)}] = {{" +
+                 ", ".join(f"{x}u" for x in flat) + "};\n")
+    return text + "#define PBM_SOLVE_PROGRAM \\\n  " + " \\\n  ".join(out) + "\n"
 
 
 def default_team(n_states: int) -> int:
@@ -369,6 +410,13 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
         lines.append(f"#define PBM_FAC_NLEV {sym.factor.n_levels}")
         lines.append(f"#define PBM_FWD_NLEV {sym.fwd.n_levels}")
         lines.append(f"#define PBM_BWD_NLEV {sym.bwd.n_levels}")
+        if sym.dense_rows is not None:
+            nT = len(sym.dense_rows)
+            G = next(r["param"] & 0xFF for r in sym.solve_program if r["kind"] == 3)
+            lines.append(f"#define PBM_DENSE_N {nT}")
+            lines.append(f"#define PBM_DENSE_G {G}")
+            lines.append(f"static PB_TABLE const {_itype(sym.nnz_lu + 1)} pbm_dense_slot[{nT * nT}] = {{" +
+                         ", ".join(str(int(x)) for x in sym.dense_slots.reshape(-1)) + "};")
         lines.append(f"#define PBM_SLV_WORDS {sym.n_solve_words}")
         lines.append(f"#define PBM_SLV_ALLOC {len(sym.solve_stream)}")
         lines.append(f"#define PBM_SLV_NREC {sym.n_solve_records}")

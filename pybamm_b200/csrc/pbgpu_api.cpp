@@ -179,7 +179,7 @@ int pbgpu_solver_create(pbgpu_model_t model, const double* atol, const pbgpu_opt
     delete s;
     return cuda_fail("cudaMemcpy(atol)", e);
   }
-  if (s->queue.ensure(sizeof(unsigned int))) {
+  if (s->queue.ensure(sizeof(unsigned int) * PBGPU_QUEUE_WORDS)) {
     delete s;
     return 1;
   }
@@ -258,7 +258,7 @@ static int launch_common(pbgpu_solver_s* s, int n_sys, const double* d_t_eval, i
   L.scratch = (double*)s->team_scratch.p;
   L.order = (s->order_n == n_sys && n_sys > 0) ? (const int*)s->order.p : nullptr;
   L.opt = s->opt;
-  CK(cudaMemsetAsync(s->queue.p, 0, sizeof(unsigned int), stream));
+  CK(cudaMemsetAsync(s->queue.p, 0, sizeof(unsigned int) * PBGPU_QUEUE_WORDS, stream));
   char err[512];
   err[0] = 0;
   if (s->model->launch(&L, (void*)stream, &s->last_grid, err, sizeof(err))) return fail(err);

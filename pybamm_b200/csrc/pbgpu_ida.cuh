@@ -53,7 +53,11 @@
 #define PB_GOFF_YYPRED (PB_GOFF_EE + PBM_N)
 #define PB_GOFF_YPPRED (PB_GOFF_YYPRED + PBM_N)
 #define PB_GOFF_TMPJ (PB_GOFF_YPPRED + PBM_N)
-#define PB_GVEC_DOUBLES (PB_GOFF_TMPJ + PBM_NTMP_JAC)
+#ifndef PBM_DENSE_N
+#define PBM_DENSE_N 0   /* rows of the dense top block of the elimination tree (symbolic_lu._dense_top) */
+#endif
+#define PB_GOFF_WD (PB_GOFF_TMPJ + PBM_NTMP_JAC)   /* W = (L_TT U_TT)^-1, row-major */
+#define PB_GVEC_DOUBLES (PB_GOFF_WD + PBM_DENSE_N * PBM_DENSE_N)
 #if PB_GLOBAL_VEC
 #define PB_OFF_DELTA 0
 #define PB_SCRATCH_DOUBLES PB_GVEC_DOUBLES
@@ -101,6 +105,9 @@ struct pb_sys {
   const unsigned int* slv;  // solve stream (shared memory)
   const unsigned int* fac;  // factor stream (shared memory when PBM_FAC_SMEM, else the global table)
   pb_team_ctx team;
+  volatile unsigned int* al_me;     // phase-alignment mailbox of this team / of the other team on the SM (pb_align), or null
+  volatile unsigned int* al_other;
+  unsigned int al_count, al_seen;   // meaningful in thread 0 only
   const double* atol;  // global
   // options (copied from pbgpu_options)
   double rtol, epcon, epsNewtIC, step_tol_ic, dt_init, hmax_inv;
@@ -124,6 +131,7 @@ struct pb_sys {
 #define S_YYPRED(S) ((S).gv + PB_GOFF_YYPRED)
 #define S_YPPRED(S) ((S).gv + PB_GOFF_YPPRED)
 #define S_TMPJ(S) ((S).gv + PB_GOFF_TMPJ)
+#define S_WD(S) ((S).gv + PB_GOFF_WD)
 #define S_DELTA(S) ((S).sm + PB_OFF_DELTA)
 #define S_YY(S) ((S).sm + PB_OFF_YY)
 #define S_W(S) ((S).sm + PB_OFF_W)
@@ -297,6 +305,42 @@ static PB_DEV int pb_lu_factor(pb_sys& S) {
     }
   }
   PB_SYNC();
+#if PBM_DENSE_N > 0
+  {
+    // Dense top block: thread j forms column j of W = U_TT^-1 L_TT^-1 in the solve's w scratch (column-major, odd
+    // leading dimension: conflict-free), reading L_TT / U_TT through the slot table (zero slot where the pattern has
+    // no entry), and writes it row-major to the team's global scratch.
+    constexpr int NT = PBM_DENSE_N, LD = NT | 1;
+    static_assert(NT * LD <= PBM_N + 1, "dense block scratch");
+    double* cw = S_W(S);
+    double* wd = S_WD(S);
+    for (int j = PB_TID; j < NT; j += PB_TEAM) {
+      double* c = cw + j * LD;
+      for (int i = 0; i < NT; i++) {
+        double sa = (i == j) ? 1.0 : 0.0, sb = 0.0;
+        int k = 0;
+        for (; k + 1 < i; k += 2) {
+          sa = fma(-lu[(int)PB_LD(pbm_dense_slot[i * NT + k])], c[k], sa);
+          sb = fma(-lu[(int)PB_LD(pbm_dense_slot[i * NT + k + 1])], c[k + 1], sb);
+        }
+        if (k < i) sa = fma(-lu[(int)PB_LD(pbm_dense_slot[i * NT + k])], c[k], sa);
+        c[i] = sa + sb;
+      }
+      for (int i = NT - 1; i >= 0; i--) {
+        double sa = c[i], sb = 0.0;
+        int k = i + 1;
+        for (; k + 1 < NT; k += 2) {
+          sa = fma(-lu[(int)PB_LD(pbm_dense_slot[i * NT + k])], c[k], sa);
+          sb = fma(-lu[(int)PB_LD(pbm_dense_slot[i * NT + k + 1])], c[k + 1], sb);
+        }
+        if (k < NT) sa = fma(-lu[(int)PB_LD(pbm_dense_slot[i * NT + k])], c[k], sa);
+        c[i] = (sa + sb) * lu[(int)PB_LD(pbm_dense_slot[i * NT + i])];
+      }
+      for (int i = 0; i < NT; i++) PB_STCG(wd + i * NT + j, c[i]);
+    }
+    PB_SYNC();
+  }
+#endif
   return pb_team_max(S.team, bad) != 0.0;
 }
 
@@ -308,6 +352,9 @@ static PB_DEV int pb_lu_factor(pb_sys& S) {
 #define PB_SEQ_HDR 4
 #define PB_PAR_ADD 2u
 #define PB_PAR_DIAG 4u
+#ifndef PB_PAR_CH
+#define PB_PAR_CH 6   /* operands fetched together per lane */
+#endif
 #define PB_PAR_PAD ((unsigned int)PBM_NNZ_LU | ((unsigned int)PBM_N << 16))   /* zero L/U slot times w[N] = 0 */
 
 template <int BWD>
@@ -368,9 +415,8 @@ static PB_DEV void pb_seq_thread(const unsigned int* PB_RESTRICT p, const int nt
 template <int G, int MLG, unsigned int MODE>
 static __device__ __noinline__ void pb_par_rec(const unsigned int* PB_RESTRICT blk, const int nt, const double* PB_RESTRICT lu,
                                                double* PB_RESTRICT w) {
-  const unsigned int mask = nt == 32 ? 0xffffffffu : ((1u << nt) - 1u);
-  if (PB_LANE < nt) {
-    const unsigned int* p = blk + PB_LANE;
+  {   // whole warp, constant mask: see pb_par_generic
+    const unsigned int* p = blk + (PB_LANE < nt ? PB_LANE : nt - 1);
     const int row = (int)p[0];
     unsigned int a[MLG > 0 ? MLG : 1];
 #pragma unroll
@@ -391,11 +437,11 @@ static __device__ __noinline__ void pb_par_rec(const unsigned int* PB_RESTRICT b
     }
     double sum = MLG > 1 ? s0 + s1 : s0;
 #pragma unroll
-    for (int o = 1; o < G; o <<= 1) sum += __shfl_xor_sync(mask, sum, o);
+    for (int o = 1; o < G; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
     const double base = (MODE & PB_PAR_DIAG) ? wr * ld : wr;
     const double acc = (MODE & PB_PAR_ADD) ? base + sum : base - sum;
-    __syncwarp(mask);
-    if (G == 1 || (PB_LANE & (G - 1)) == 0) w[row] = acc;
+    __syncwarp();
+    if ((G == 1 || (PB_LANE & (G - 1)) == 0) && PB_LANE < nt) w[row] = acc;
   }
 }
 
@@ -404,35 +450,131 @@ static __device__ __noinline__ void pb_par_rec(const unsigned int* PB_RESTRICT b
 static __device__ __noinline__ void pb_par_generic(const unsigned int* PB_RESTRICT blk, const int nt, const int G, const int mlg,
                                                    const unsigned int mode, const double* PB_RESTRICT lu,
                                                    double* PB_RESTRICT w) {
-  const unsigned int mask = nt == 32 ? 0xffffffffu : ((1u << nt) - 1u);
-  if (PB_LANE < nt) {
-    const unsigned int* p = blk + PB_LANE;
+  // The whole warp runs the record with the full constant mask (a run-time mask costs a MATCH/REDUX sequence per
+  // shuffle): lanes past nt shadow lane nt - 1 -- whole groups, since nt is a multiple of G -- and never write.
+  {
+    const unsigned int* p = blk + (PB_LANE < nt ? PB_LANE : nt - 1);
     const int row = (int)p[0];
     const double wr = w[row];
     const double ld = (mode & PB_PAR_DIAG) ? lu[row] : 1.0;
     double s0 = 0.0, s1 = 0.0;
     p += nt;
-    for (int j = 0; j < mlg; j += 4) {
-      const unsigned int a0 = p[0];
-      const unsigned int a1 = (j + 1 < mlg) ? p[nt] : PB_PAR_PAD;
-      const unsigned int a2 = (j + 2 < mlg) ? p[2 * nt] : PB_PAR_PAD;
-      const unsigned int a3 = (j + 3 < mlg) ? p[3 * nt] : PB_PAR_PAD;
-      p += 4 * nt;
-      const double x0 = lu[a0 & 0xFFFFu], y0 = w[a0 >> 16], x1 = lu[a1 & 0xFFFFu], y1 = w[a1 >> 16];
-      const double x2 = lu[a2 & 0xFFFFu], y2 = w[a2 >> 16], x3 = lu[a3 & 0xFFFFu], y3 = w[a3 >> 16];
-      s0 = fma(x0, y0, s0);
-      s1 = fma(x1, y1, s1);
-      s0 = fma(x2, y2, s0);
-      s1 = fma(x3, y3, s1);
+    // operand words of the next chunk are fetched while the current chunk's values are in flight
+    unsigned int a[PB_PAR_CH];
+#pragma unroll
+    for (int k = 0; k < PB_PAR_CH; k++) a[k] = (k < mlg) ? p[k * nt] : PB_PAR_PAD;
+    for (int j = 0; j < mlg; j += PB_PAR_CH) {
+      double x[PB_PAR_CH], y[PB_PAR_CH];
+#pragma unroll
+      for (int k = 0; k < PB_PAR_CH; k++) {
+        x[k] = lu[a[k] & 0xFFFFu];
+        y[k] = w[a[k] >> 16];
+      }
+      p += PB_PAR_CH * nt;
+      if (j + PB_PAR_CH < mlg) {
+#pragma unroll
+        for (int k = 0; k < PB_PAR_CH; k++) a[k] = (j + PB_PAR_CH + k < mlg) ? p[k * nt] : PB_PAR_PAD;
+      }
+#pragma unroll
+      for (int k = 0; k < PB_PAR_CH; k += 2) {
+        s0 = fma(x[k], y[k], s0);
+        if (k + 1 < PB_PAR_CH) s1 = fma(x[k + 1], y[k + 1], s1);
+      }
     }
     double sum = s0 + s1;
-    for (int o = 1; o < G; o <<= 1) sum += __shfl_xor_sync(mask, sum, o);
+    for (int o = 1; o < G; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
     const double base = wr * ld;
     const double acc = (mode & PB_PAR_ADD) ? base + sum : base - sum;
-    __syncwarp(mask);
-    if ((PB_LANE & (G - 1)) == 0) w[row] = acc;
+    __syncwarp();
+    if ((PB_LANE & (G - 1)) == 0 && PB_LANE < nt) w[row] = acc;
   }
 }
+
+#if defined(PBM_PAR_RUN_N) && !defined(PB_EMU)
+// A run of consecutive single-warp PAR records in one loop, software-pipelined over the records: everything that
+// does not depend on w (descriptor, rows, operand words, L/U values) is fetched two / one records ahead, so the
+// critical path of a record is w loads -> DFMAs -> butterfly -> store.  Descriptors: pbm_par_run[2 r] =
+// body offset | nt << 16, pbm_par_run[2 r + 1] = G | mlg << 8 | mode << 16 (constant memory, emitted by codegen).
+#define PB_RUN_ROWS(D0, D1, P, ROW, A)                                              \
+  {                                                                                 \
+    const int nt_ = (int)((D0) >> 16), mlg_ = (int)(((D1) >> 8) & 0xFFu);           \
+    P = st + ((D0) & 0xFFFFu) + (PB_LANE < nt_ ? PB_LANE : nt_ - 1);                \
+    ROW = (int)P[0];                                                                \
+    _Pragma("unroll") for (int k = 0; k < CH; k++) A[k] = (k < mlg_) ? P[(1 + k) * nt_] : PB_PAR_PAD; \
+  }
+static __device__ __noinline__ void pb_par_run(const unsigned int* PB_RESTRICT st, const int r0, const int nrec,
+                                               const double* PB_RESTRICT lu, double* PB_RESTRICT w) {
+  constexpr int CH = PB_PAR_CH;
+  const int rlast = r0 + nrec - 1;
+  unsigned int c0 = pbm_par_run[2 * r0], c1 = pbm_par_run[2 * r0 + 1];
+  int q = r0 + 1 < rlast ? r0 + 1 : rlast;
+  unsigned int n0 = pbm_par_run[2 * q], n1 = pbm_par_run[2 * q + 1];
+  q = r0 + 2 < rlast ? r0 + 2 : rlast;
+  unsigned int m0 = pbm_par_run[2 * q], m1 = pbm_par_run[2 * q + 1];
+  const unsigned int *pc, *pn;
+  int rowc, rown;
+  unsigned int ac[CH], an[CH];
+  double xc[CH], ldc;
+  PB_RUN_ROWS(c0, c1, pc, rowc, ac)
+  PB_RUN_ROWS(n0, n1, pn, rown, an)
+  ldc = lu[rowc];
+#pragma unroll
+  for (int k = 0; k < CH; k++) xc[k] = lu[ac[k] & 0xFFFFu];
+  for (int r = 0; r < nrec; r++) {
+    // --- fetched ahead, consumed in later iterations
+    double xn[CH];
+    const double ldn = lu[rown];
+#pragma unroll
+    for (int k = 0; k < CH; k++) xn[k] = lu[an[k] & 0xFFFFu];
+    const unsigned int* pm;
+    int rowm;
+    unsigned int am[CH];
+    PB_RUN_ROWS(m0, m1, pm, rowm, am)
+    q = r0 + r + 3 < rlast ? r0 + r + 3 : rlast;
+    const unsigned int l0 = pbm_par_run[2 * q], l1 = pbm_par_run[2 * q + 1];
+    // --- this record
+    const int nt = (int)(c0 >> 16), G = (int)(c1 & 0xFFu), mlg = (int)((c1 >> 8) & 0xFFu);
+    const unsigned int mode = c1 >> 16;
+    const double wr = w[rowc];
+    double y[CH];
+#pragma unroll
+    for (int k = 0; k < CH; k++) y[k] = w[ac[k] >> 16];
+    double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+    for (int k = 0; k < CH; k += 2) {
+      s0 = fma(xc[k], y[k], s0);
+      if (k + 1 < CH) s1 = fma(xc[k + 1], y[k + 1], s1);
+    }
+    for (int j = CH; j < mlg; j += CH) {   // the few long records: remaining operands, not pipelined
+      unsigned int b[CH];
+#pragma unroll
+      for (int k = 0; k < CH; k++) b[k] = (j + k < mlg) ? pc[(1 + j + k) * nt] : PB_PAR_PAD;
+#pragma unroll
+      for (int k = 0; k < CH; k += 2) {
+        s0 = fma(lu[b[k] & 0xFFFFu], w[b[k] >> 16], s0);
+        if (k + 1 < CH) s1 = fma(lu[b[k + 1] & 0xFFFFu], w[b[k + 1] >> 16], s1);
+      }
+    }
+    double sum = s0 + s1;
+    for (int o = 1; o < G; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const double base = (mode & PB_PAR_DIAG) ? wr * ldc : wr;
+    const double acc = (mode & PB_PAR_ADD) ? base + sum : base - sum;
+    __syncwarp();
+    if ((PB_LANE & (G - 1)) == 0 && PB_LANE < nt) w[rowc] = acc;
+    __syncwarp();
+    // --- rotate the pipeline
+    c0 = n0; c1 = n1; pc = pn; rowc = rown; ldc = ldn;
+    n0 = m0; n1 = m1; pn = pm; rown = rowm;
+    m0 = l0; m1 = l1;
+#pragma unroll
+    for (int k = 0; k < CH; k++) {
+      ac[k] = an[k];
+      xc[k] = xn[k];
+      an[k] = am[k];
+    }
+  }
+}
+#endif
 
 // CHAIN record: one lane per bidiagonal chain of K consecutive rows.  All operands are independent of the recurrence
 // and are loaded in batches ahead of it: the chain costs one DFMA per row.
@@ -494,10 +636,41 @@ static __device__ __noinline__ void pb_seq_rec(const unsigned int* PB_RESTRICT b
 #endif
 
 #ifndef PB_EMU
+#if PBM_DENSE_N > 0
+// Dense top block x_T = W r_T: PBM_DENSE_G lanes per row, every lane a few columns.  The thread's share of W comes
+// from L2 and does not depend on the right-hand side: it is fetched before the forward sweep starts.
+#define PB_DENSE_CPL ((PBM_DENSE_N + PBM_DENSE_G - 1) / PBM_DENSE_G)
+#define PB_DENSE_PROLOGUE(wd)                                                                            \
+  double wdv[PB_DENSE_CPL];                                                                              \
+  const int drow = PB_TID / PBM_DENSE_G, dpart = PB_TID % PBM_DENSE_G;                                   \
+  _Pragma("unroll") for (int k = 0; k < PB_DENSE_CPL; k++) {                                             \
+    const int col = dpart + k * PBM_DENSE_G;                                                             \
+    wdv[k] = (drow < PBM_DENSE_N && col < PBM_DENSE_N) ? __ldcg((wd) + drow * PBM_DENSE_N + col) : 0.0;     \
+  }
+#define PB_DENSE_REC(off)                                                                                \
+  {                                                                                                      \
+    const unsigned int* rows = st + (off);                                                               \
+    double sum = 0.0;                                                                                    \
+    _Pragma("unroll") for (int k = 0; k < PB_DENSE_CPL; k++) {                                           \
+      const int col = dpart + k * PBM_DENSE_G;                                                           \
+      sum = fma(wdv[k], w[rows[col < PBM_DENSE_N ? col : 0]], sum);                                      \
+    }                                                                                                    \
+    _Pragma("unroll") for (int o = 1; o < PBM_DENSE_G; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o); \
+    PB_SYNC();                                                                                           \
+    if (dpart == 0 && drow < PBM_DENSE_N) w[rows[drow]] = sum;                                           \
+    PB_SYNC();                                                                                           \
+  }
+static_assert(PBM_DENSE_N * PBM_DENSE_G <= PB_TEAM, "dense block wider than the team");
+#else
+#define PB_DENSE_PROLOGUE(wd)
+#endif
 // one copy of the call sequence for every call site of pb_lu_solve
 static __device__ __noinline__ void pb_solve_program(const unsigned int* PB_RESTRICT st, const double* PB_RESTRICT lu,
-                                                     double* PB_RESTRICT w) {
+                                                     double* PB_RESTRICT w, const double* PB_RESTRICT wd) {
+  PB_DENSE_PROLOGUE(wd)
+#define PB_REC_MARK
   PBM_SOLVE_PROGRAM
+#undef PB_REC_MARK
 }
 #endif
 
@@ -527,7 +700,21 @@ static PB_DEV void pb_lu_solve_t(pb_sys& S, double* b, double* trace) {
   }
   {
 #ifndef PB_EMU
-    pb_solve_program(S.slv, lu, w);
+    if (TRACE) {   // an inline copy with a clock sample after every record (eval kernel only)
+      const unsigned int* st = S.slv;
+      PB_DENSE_PROLOGUE(S_WD(S))
+#define PB_REC_MARK                                              \
+  {                                                              \
+    const long long t1 = clock64();                              \
+    if (PB_TID == 0 && trk < 60) trace[trk] = (double)(t1 - tr0); \
+    trk++;                                                       \
+    tr0 = t1;                                                    \
+  }
+      PBM_SOLVE_PROGRAM
+#undef PB_REC_MARK
+    } else {
+      pb_solve_program(S.slv, lu, w, S_WD(S));
+    }
 #else
     const unsigned int* st = S.slv;
     int off = 0;
@@ -546,6 +733,16 @@ static PB_DEV void pb_lu_solve_t(pb_sys& S, double* b, double* trace) {
             else pb_seq_thread<0>(body + q, nt, lu, w);
           }
           body += nt * len;
+        }
+      } else if (kind == 3) {   // dense top block: x_T = W r_T
+        const int nT = (int)(st[off + 3] >> 8);
+        const double* wd = S_WD(S);
+        double rt[64];
+        for (int q = 0; q < nT; q++) rt[q] = w[body[q]];
+        for (int i = 0; i < nT; i++) {
+          double sum = 0.0;
+          for (int q = 0; q < nT; q++) sum += wd[i * nT + q] * rt[q];
+          w[body[i]] = sum;
         }
       } else if (kind == 2) {
         for (int v = 0; v < nb; v++) {
@@ -591,12 +788,6 @@ static PB_DEV void pb_lu_solve_t(pb_sys& S, double* b, double* trace) {
       off += total;
     }
 #endif
-  }
-  if (TRACE) {
-    const long long t1 = clock64();
-    if (PB_TID == 0) trace[trk] = (double)(t1 - tr0);
-    trk++;
-    tr0 = t1;
   }
 #if defined(PB_PROFILE) && PB_PROFILE == 2
   PB_T1(S, tlv_, 6);
@@ -818,6 +1009,39 @@ static PB_DEV void pb_restore(pb_sys& S, double saved_t, int phi_scaled) {
 #define PB_PREDICT_AGAIN 20
 
 // IDANls + Newton iteration + idaNlsConvTest (modified Newton, J held between lsetups).
+// ---- keeping the two teams of an SM in phase -----------------------------------------------------------------
+// Two teams share an SM and its instruction cache.  Measured on the DFN: 296 copies of one system (teams in phase by
+// construction) run 11 % slower than one team alone, 296 different systems of the same length 62 % slower -- a team
+// that executes other code than its neighbour evicts the neighbour's instructions (icc hit rate 67 %).  So the teams
+// meet before every Newton residual: each publishes an arrival count in a per-SM mailbox (global memory, L2) and
+// waits, for a bounded time, until the neighbour has arrived at its own next meeting point.  The wait is skipped while
+// the neighbour is absent, between systems, or inside a Jacobian set-up (state != 1).
+#ifndef PB_ALIGN_TEAMS
+#define PB_ALIGN_TEAMS 0
+#endif
+#ifndef PB_ALIGN_LIMIT
+#define PB_ALIGN_LIMIT 8000   /* cycles */
+#endif
+#if PB_ALIGN_TEAMS && !defined(PB_EMU)
+static PB_DEV void pb_align_state(pb_sys& S, unsigned int st) {
+  if (S.al_me != nullptr && PB_TID == 0) S.al_me[1] = st;
+}
+static PB_DEV void pb_align(pb_sys& S) {
+  if (S.al_me == nullptr) return;
+  if (PB_TID == 0) {
+    S.al_me[0] = ++S.al_count;
+    const long long t0 = clock64();
+    while (S.al_other[1] == 1u && S.al_other[0] == S.al_seen && clock64() - t0 < PB_ALIGN_LIMIT) {
+    }
+    S.al_seen = S.al_other[0];
+  }
+  PB_SYNC();
+}
+#else
+#define pb_align_state(S, st) ((void)0)
+#define pb_align(S) ((void)0)
+#endif
+
 static PB_DEV int pb_nls_impl(pb_sys& S) {
   int callLSetup = 0;
   if (S.nst == 0) {
@@ -881,6 +1105,7 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
   double oldnrm = 0.0;
   for (;;) {
     {
+      pb_align(S);
       PB_T0(tr_);
       pbm_res(yy, S_P(S), S.tn, 0.0, delta, S_TMP(S));
       PB_STAT(S, PB_ST_NRE);
@@ -889,7 +1114,9 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
     }
     int fail = 0;
     if (callLSetup) {
+      pb_align_state(S, 2u);
       const int ier = pb_lsetup(S, S.tn, yy, S.cj, 0);
+      pb_align_state(S, 1u);
       S.cjold = S.cj;
       S.cjratio = 1.0;
       S.ss = 20.0;
@@ -970,6 +1197,7 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
           break;
         }
         {
+          pb_align(S);
           PB_T0(tr_);
           pbm_res(yy, S_P(S), S.tn, 0.0, delta, S_TMP(S));
           PB_STAT(S, PB_ST_NRE);
@@ -1756,6 +1984,10 @@ static PB_DEV void pb_sys_init(pb_sys& S, double* sm, double* gv, const pbgpu_la
   S.sm = sm;
   S.gv = gv;
   S.team.red = sm + PB_OFF_RED;
+  S.al_me = nullptr;
+  S.al_other = nullptr;
+  S.al_count = 0u;
+  S.al_seen = 0u;
   pb_sys_tables(S);
 #ifndef PB_EMU
   S.team.red_phase = 0;

@@ -30,13 +30,30 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_s
 #else
   pb_sys_init(S, pb_smem, pb_smem, L);
 #endif
+#if PB_ALIGN_TEAMS
+  {   // the first two teams to arrive on an SM share its mailbox (persistent kernel: a team never leaves its SM)
+    unsigned int smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    unsigned int* box = L.queue + 32 + 8 * (smid & 255u);
+    if (threadIdx.x == 0) next_sys = atomicAdd(box, 1u);
+    __syncthreads();
+    const unsigned int me = next_sys;
+    __syncthreads();
+    if (me < 2u) {
+      S.al_me = box + 2 + 2 * me;
+      S.al_other = box + 2 + 2 * (1u - me);
+    }
+  }
+#endif
   for (;;) {
     if (threadIdx.x == 0) next_sys = atomicAdd(L.queue, 1u);
     __syncthreads();
     const unsigned int slot = next_sys;
     __syncthreads();
     if (slot >= (unsigned int)L.n_sys) break;
+    pb_align_state(S, 1u);
     pb_solve_system(S, L, L.order ? L.order[slot] : (int)slot);
+    pb_align_state(S, 2u);
   }
 }
 

@@ -26,6 +26,7 @@
 #define PB_LANES 1
 #define PB_SYNC() ((void)0)
 #define PB_SYNCWARP() ((void)0)
+#define PB_STCG(p, v) (*(p) = (v))
 #define PB_LD(x) (x)
 #define PB_LDU(x) (x)
 #define PB_NAN NAN
@@ -60,6 +61,7 @@ PB_FN double pb_team_max(pb_team_ctx&, double x) { return x; }
 #define PB_SYNC() __syncthreads()
 #endif
 #define PB_SYNCWARP() __syncwarp()
+#define PB_STCG(p, v) __stcg(p, v)   /* L2 only: keep the small L1 for the tables */
 #define PB_LD(x) __ldg(&(x))
 #define PB_LDU(x) __ldg(&(x))
 #define PB_NAN CUDART_NAN

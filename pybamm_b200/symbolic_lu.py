@@ -27,6 +27,8 @@ from __future__ import annotations
 
 from dataclasses import dataclass
 
+import os
+
 import numpy as np
 import scipy.sparse as sp
 import scipy.sparse.linalg as spla
@@ -92,6 +94,8 @@ class SymbolicLU:
     solve_program: list = None         # the records of the solve stream as dicts (code generator input)
     s_ops: dict = None                 # row -> [(slot, w index)]: solve-form forward coupling  S = -Q L_C,desc
     t_ops: dict = None                 # row -> [(slot, w index)]: solve-form backward coupling T = -P U_C,anc
+    dense_rows: list = None            # rows of the dense top block T (ascending), or None
+    dense_slots: np.ndarray = None     # (nT, nT) slot of L/U entry (row, col) of the block, nnz_lu where structurally zero
 
     def summary(self):
         return (f"n={self.n} nnz_lu={self.nnz_lu} ordering={self.ordering} streams: solve {len(self.solve_stream)} words/"
@@ -279,6 +283,9 @@ def _jds(levels_tasks, pad_a, pad_b, warp=32):
                np.asarray(task_out, i32), np.asarray(task_aux, i32), n_real)
 
 
+DENSE_MAX = 32      # rows of the dense top block (one warp computes its inverse, one lane per column)
+DENSE_TEAM_MIN = 128   # only multi-warp teams use it: the block is applied by rows x lanes spread over the team
+DENSE_MIN_HEIGHTS = 3  # tree heights it must replace to be worth two records
 INV_MAX = 8         # clusters of 2..INV_MAX rows get explicit inverse diagonal blocks
 ONE = object()      # placeholder of the constant-one slot (nnz_lu + 1) while slots are still being handed out
 AUX_U = 0xFFFF      # factor task writes an off-diagonal U entry
@@ -351,6 +358,9 @@ def _build(n, rows, cols, perm_r, perm_c, name, team=128) -> SymbolicLU:
     # the diagonal of row i sits in slot i (the backward solve reads 1/u_ii as lu[row] without a table look-up)
     slot_of = {(i, i): i for i in range(n)}
     clusters, cl, kinds = _seq_clusters(n, Lrows, Urows)
+    dense_rows = None
+    if team >= DENSE_TEAM_MIN and os.environ.get("PBGPU_DENSE_TOP", "1") != "0":
+        clusters, cl, kinds, dense_rows = _dense_top(n, Lrows, clusters, cl, kinds)
     for c, rws in enumerate(clusters):     # chains: L entries in consecutive slots, then U entries in consecutive slots
         if kinds[c] == "chain":
             for k in range(1, len(rws)):
@@ -509,7 +519,10 @@ def _build(n, rows, cols, perm_r, perm_c, name, team=128) -> SymbolicLU:
     return build_streams(SymbolicLU(n, nnz_lu, np.asarray(perm_r), np.asarray(perm_c), slot_of, a_slot, diag_slot,
                                     factor, fwd, bwd, flops, sflops, name, Lrows=Lrows, Urows=Urows,
                                     clusters=clusters, cl=cl, inv_cluster=inv_cluster, cluster_kind=kinds,
-                                    s_ops=s_ops, t_ops=t_ops), team=team)
+                                    s_ops=s_ops, t_ops=t_ops, dense_rows=dense_rows,
+                                    dense_slots=None if dense_rows is None else np.array(
+                                        [[slot_of.get((i, k), nnz_lu) for k in dense_rows] for i in dense_rows], np.int64)),
+                         team=team)
 
 
 # ---------------------------------------------------------------------------
@@ -683,6 +696,38 @@ PAR_MLG_SHAPES = (0, 1, 2, 3, 4, 6, 8, 10, 12, 16, 20, 24, 32)   # operand count
 SEQ_TASK_CYC, SEQ_CHUNK_CYC, SEQ_LONG_CYC, SEQ_REC_CYC = 90, 45, 30, 150
 
 
+def _dense_top(n, Lrows, clusters, cl, kinds):
+    """The top of the elimination tree as ONE dense block.  Every tree height costs a record of several hundred cycles
+    however few rows it has, and the last heights hold a handful of rows each; the clusters above a height h0 (a set
+    closed under ancestors, at most DENSE_MAX rows) are merged into one cluster of kind "dense": the factorisation
+    leaves their L and U entries plain and forms W = (L_TT U_TT)^-1 explicitly, the solve replaces all their records
+    of both sweeps by  r_T = b_T - L_T,desc z_desc  and  x_T = W r_T.  The merged cluster goes last (it depends on
+    everything and only the backward sweep reads it)."""
+    nc = len(clusters)
+    hf = np.zeros(nc, np.int64)
+    for c, rws in enumerate(clusters):
+        for i in rws:
+            for k in Lrows[i]:
+                if cl[k] != c:
+                    hf[c] = max(hf[c], hf[cl[k]] + 1)
+    hmax = int(hf.max())
+    h0 = hmax + 1
+    while h0 > 0 and sum(len(clusters[c]) for c in range(nc) if hf[c] >= h0 - 1) <= DENSE_MAX:
+        h0 -= 1
+    top = [c for c in range(nc) if hf[c] >= h0]
+    rows = sorted(i for c in top for i in clusters[c])
+    # scratch for the inverse (column-major, odd leading dimension) is the solve's w vector: nT * (nT | 1) <= n
+    if hmax + 1 - h0 < DENSE_MIN_HEIGHTS or len(rows) * (len(rows) | 1) > n or any(kinds[c] == "chain" for c in top):
+        return clusters, cl, kinds, None
+    keep = [c for c in range(nc) if hf[c] < h0]
+    clusters = [clusters[c] for c in keep] + [rows]
+    kinds = [kinds[c] for c in keep] + ["dense"]
+    cl = np.full(n, -1, np.int64)
+    for c, rws in enumerate(clusters):
+        cl[rws] = c
+    return clusters, cl, kinds, rows
+
+
 def _seq_clusters(n, Lrows, Urows):
     """Clusters = maximal paths i1 -> i2 -> ... of the elimination tree in which every node has exactly one child."""
     first_below = [None] * n          # first row i > k with L[i, k] != 0
@@ -843,16 +888,20 @@ def build_seq_solve_stream(s: SymbolicLU, team=128):
                             cyc=CHAIN_BASE_CYC + CHAIN_ROW_CYC * K, threads=desc))
         return out
 
-    def par_records(rows_ops, mode, nw):
+    def par_records(rows_ops, mode, nw, split_rows=False):
         """rows_ops: list of (row, [(slot, w index), ...]).  The rows of one cluster stay in one block (= one warp): they
-        read each other's old values, and "every lane reads before any lane writes" only holds inside a warp."""
+        read each other's old values, and "every lane reads before any lane writes" only holds inside a warp.
+        split_rows: the operands are never rows of the record itself (dense top block), rows go to any warp and get
+        as many lanes as the team has."""
         units = {}
         for row, ops in rows_ops:
-            units.setdefault(int(cl[row]), []).append((row, ops))
+            units.setdefault(row if split_rows else int(cl[row]), []).append((row, ops))
         units = sorted(units.values(), key=lambda u: -len(u))
         # lanes per row: as many as the warps can hold (with slack for packing whole clusters into warps)
         maxml_all = max(len(t[1]) for t in rows_ops)
         Gw = 1
+        while split_rows and 2 * Gw * len(rows_ops) <= 32 * nw and Gw < min(maxml_all, 8):
+            Gw *= 2
         while (PAR_WIDE_GROUPS and 2 * Gw * len(rows_ops) <= 24 * nw and 2 * Gw * len(units[0]) <= 32 and Gw < maxml_all
                and nw > 1):
             Gw *= 2
@@ -899,8 +948,13 @@ def build_seq_solve_stream(s: SymbolicLU, team=128):
         for h in range(int(heights.max()) + 1):
             cs = [c for c in range(nc) if heights[c] == h]
             progs, rows_a, rows_b, chains = [], [], [], []
+            dense_c = None
             for c in cs:
                 rws = clusters[c][::-1] if back else clusters[c]
+                if kinds[c] == "dense":       # both sweeps of the block happen in the forward one
+                    if not back:
+                        dense_c = c
+                    continue
                 if kinds[c] == "chain":
                     chains.append(c)
                     continue
@@ -955,13 +1009,28 @@ def build_seq_solve_stream(s: SymbolicLU, team=128):
                     r["first_warp"] = seq_w if beside else 0
                     r["beside"] = beside
                     group.append(r)
+            if dense_c is not None:
+                # r_T = b_T - L_T,desc z_desc (plain L entries, all lanes of the team), then x_T = W r_T
+                T = clusters[dense_c]
+                pre = [(i, [(s.slot_of[(i, k)], k) for k in Lrows[i] if cl[k] != dense_c]) for i in T]
+                pre = [t for t in pre if t[1]]
+                if pre:
+                    for r in par_records(pre, 0, n_warps, split_rows=True):
+                        r["first_warp"], r["beside"], r["pre"], r["wide"] = 0, False, True, True
+                        group.append(r)
+                GD = 1
+                while 2 * GD * len(T) <= team and GD < 8:
+                    GD *= 2
+                group.append(dict(kind=3, mode=0, nblocks=1, param=GD | (len(T) << 8), desc=[len(T)], body=list(T),
+                                  cyc=PAR_BASE_CYC + PAR_SHFL_CYC * 3, threads=[len(T) * GD], first_warp=0,
+                                  beside=False, wide=True, team_need=len(T) * GD))
             for r in group:
                 r["back"], r["height"] = back, h
             recs += group
     # sync codes: nothing between the chain record and the PAR record running beside it; otherwise a warp barrier
     # when this record and the next one involve warp 0 alone, a team barrier in every other case
     def narrow(r):
-        return r["first_warp"] == 0 and r["nblocks"] == 1
+        return r["first_warp"] == 0 and r["nblocks"] == 1 and not r.get("wide")
 
     for k, r in enumerate(recs):
         nxt = recs[k + 1] if k + 1 < len(recs) else None
@@ -1010,11 +1079,11 @@ def build_seq_solve_stream(s: SymbolicLU, team=128):
         r["offset"] = o
     s.solve_program = recs
     s.seq_info = dict(clusters=nc, fwd_heights=int(hf.max()) + 1, bwd_heights=int(hb.max()) + 1,
-                      records=[dict(back=r["back"], height=r["height"], kind=("SEQ", "PAR", "CHAIN")[r["kind"]], mode=r["mode"],
+                      records=[dict(back=r["back"], height=r["height"], kind=("SEQ", "PAR", "CHAIN", "DENSE")[r["kind"]], mode=r["mode"],
                                     sync=r["sync"], first_warp=r["first_warp"], threads=r["threads"],
                                     G=r["param"] & 0xFF, mlg=r["param"] >> 8, words=len(r["body"]), cyc=r["cyc"])
                                for r in recs],
-                      team_min=32 * max(r["first_warp"] + r["nblocks"] for r in recs))
+                      team_min=max(max(32 * (r["first_warp"] + r["nblocks"]), r.get("team_need", 0)) for r in recs))
     return s
 
 
@@ -1047,6 +1116,12 @@ def stream_factor(s: SymbolicLU, a_vals):
                 lu[out[q]] = 1.0 / acc[q]
             else:
                 lu[out[q]] = acc[q] * lu[aux[q]]
+    if s.dense_rows is not None:      # W = (L_TT U_TT)^-1 behind the slots (the device keeps it in global scratch)
+        nT = len(s.dense_rows)
+        D = lu[s.dense_slots]
+        Lm = np.tril(D, -1) + np.eye(nT)
+        Um = np.triu(D, 1) + np.diag(1.0 / np.diag(D))
+        lu = np.concatenate([lu, (np.linalg.inv(Um) @ np.linalg.inv(Lm)).reshape(-1)])
     return lu
 
 
@@ -1094,6 +1169,10 @@ def stream_solve(s: SymbolicLU, lu, b):
                         for k in range(1, K):
                             w[r0 + k] -= lu[L0 + k - 1] * w[r0 + k - 1]
                 base += 3 * nt
+        elif kind == 3:
+            nT = param >> 8
+            rows = st[base:base + nT].astype(np.int64)
+            w[rows] = lu[s.nnz_lu + 3:s.nnz_lu + 3 + nT * nT].reshape(nT, nT) @ w[rows]
         else:
             G, mlg = param & 0xFF, param >> 8
             for v in range(nb):

@@ -77,7 +77,13 @@ def test_cluster_and_record_invariants_on_the_battery_models():
         # clusters partition the rows, in topological (ascending first row) order
         allrows = sorted(i for c in s.clusters for i in c)
         assert allrows == list(range(s.n))
-        assert [c[0] for c in s.clusters] == sorted(c[0] for c in s.clusters)
+        ordered = s.clusters[:-1] if s.dense_rows is not None else s.clusters     # the dense top block goes last
+        assert [c[0] for c in ordered] == sorted(c[0] for c in ordered)
+        if s.dense_rows is not None:
+            assert s.cluster_kind[-1] == "dense" and s.clusters[-1] == sorted(s.dense_rows)
+            assert len(s.dense_rows) <= slu.DENSE_MAX
+            top = set(s.dense_rows)       # closed under ancestors: no row outside it depends on it in the forward sweep
+            assert all(k not in top for i in range(s.n) if i not in top for k in s.Lrows[i])
         for c, kind in zip(s.clusters, s.cluster_kind):
             if kind == "chain":     # consecutive rows, bidiagonal factors, consecutive slots
                 assert c == list(range(c[0], c[0] + len(c))) and len(c) >= 4
@@ -94,7 +100,7 @@ def test_cluster_and_record_invariants_on_the_battery_models():
         assert s.seq_info["team_min"] <= team
         for r in s.solve_program:
             assert r["first_warp"] + r["nblocks"] <= max(team // 32, 1)
-            if r["kind"] != 1:
+            if r["kind"] != 1 or r.get("pre"):     # (the rows of the dense block's first step never read each other)
                 continue
             G, mlg = r["param"] & 0xFF, r["param"] >> 8
             off = 0

@@ -14,9 +14,9 @@ python bench.py --steps 2 --warmup 3 --n-sys 1480 --cpu-sample 64 > $OUT/${TAG}_
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_launches.csv \
     python bench.py --steps 2 --warmup 3 --n-sys 1480 --cpu-sample 64 > $OUT/${TAG}_ncu_launches.log 2>&1
 echo "rc=$?"
-echo "== ncu full (one wave of DFN)"
-python -m tools.gpu_case dfn 148 1 > $OUT/${TAG}_case_plain.log 2>&1 &&
+echo "== ncu full (one wave of DFN: 296 systems = two teams per SM)"
+python -m tools.gpu_case dfn 296 1 > $OUT/${TAG}_case_plain.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:pbgpu_solve_kernel -c 1 -f -o $OUT/${TAG}_dfn_full \
-    python -m tools.gpu_case dfn 148 1 > $OUT/${TAG}_ncu_full.log 2>&1
+    python -m tools.gpu_case dfn 296 1 > $OUT/${TAG}_ncu_full.log 2>&1
 echo "rc=$?"; tail -3 $OUT/${TAG}_ncu_full.log
 ls -la $OUT
