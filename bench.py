@@ -249,6 +249,7 @@ def run_b200_arm(args):
     if world > 1:
         import torch.distributed as dist
 
+        os.environ.setdefault("NCCL_DEBUG", "WARN")   # no "NCCL version" banner on stdout: rank 0 prints ONE line, the JSON
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     from pybamm_b200 import BatchedIDASolver, build
