@@ -711,13 +711,16 @@ def _dense_top(n, Lrows, clusters, cl, kinds):
                 if cl[k] != c:
                     hf[c] = max(hf[c], hf[cl[k]] + 1)
     hmax = int(hf.max())
+    def fits(h):      # rows above height h: at most DENSE_MAX, and the scratch for the inverse (column-major, odd
+        m = sum(len(clusters[c]) for c in range(nc) if hf[c] >= h)   # leading dimension) is the solve's w vector
+        return m <= DENSE_MAX and m * (m | 1) <= n
+
     h0 = hmax + 1
-    while h0 > 0 and sum(len(clusters[c]) for c in range(nc) if hf[c] >= h0 - 1) <= DENSE_MAX:
+    while h0 > 0 and fits(h0 - 1):
         h0 -= 1
     top = [c for c in range(nc) if hf[c] >= h0]
     rows = sorted(i for c in top for i in clusters[c])
-    # scratch for the inverse (column-major, odd leading dimension) is the solve's w vector: nT * (nT | 1) <= n
-    if hmax + 1 - h0 < DENSE_MIN_HEIGHTS or len(rows) * (len(rows) | 1) > n or any(kinds[c] == "chain" for c in top):
+    if hmax + 1 - h0 < DENSE_MIN_HEIGHTS or any(kinds[c] == "chain" for c in top):
         return clusters, cl, kinds, None
     keep = [c for c in range(nc) if hf[c] < h0]
     clusters = [clusters[c] for c in keep] + [rows]

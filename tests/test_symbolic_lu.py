@@ -69,6 +69,34 @@ def test_factor_and_solve_streams_match_scipy(shape, team):
             assert np.max(np.abs(x - xr)) <= 1e-10 * max(1.0, np.max(np.abs(xr)))
 
 
+def test_dense_top_block_replaces_the_last_tree_heights(monkeypatch):
+    """Multi-warp teams: the clusters above a tree height become one dense block (W = (L_TT U_TT)^-1 behind the slots,
+    two records for both sweeps).  Same solutions as without it, fewer records, block closed under ancestors."""
+    rng = np.random.default_rng(7)
+    n, rows, cols, vals = chain_core_matrix(40, 18, 5, rng)
+    samples = [vals, vals * (1 + 0.1 * rng.standard_normal(len(vals)))]
+    s = slu.analyse(n, rows, cols, samples, team=256)
+    monkeypatch.setenv("PBGPU_DENSE_TOP", "0")
+    s0 = slu.analyse(n, rows, cols, samples, team=256)
+    assert s0.dense_rows is None and s.dense_rows is not None
+    assert 8 <= len(s.dense_rows) <= slu.DENSE_MAX and s.cluster_kind[-1] == "dense"
+    assert len(s.solve_program) < len(s0.solve_program)
+    kinds = [r["kind"] for r in s.solve_program]
+    assert kinds.count(3) == 1 and s.solve_program[kinds.index(3)]["back"] is False
+    assert s.seq_info["team_min"] <= 256
+    assert slu.analyse(n, rows, cols, samples, team=32).dense_rows is None      # single-warp teams keep the records
+    for v in samples:
+        A = sp.csc_matrix((v, (rows, cols)), shape=(n, n))
+        lu, lu0 = slu.stream_factor(s, v), slu.stream_factor(s0, v)
+        assert len(lu) == s.nnz_lu + 3 + len(s.dense_rows) ** 2
+        for _ in range(3):
+            b = rng.standard_normal(n)
+            xr = spla.spsolve(A, b)
+            for sym, f in ((s, lu), (s0, lu0)):
+                x = slu.stream_solve(sym, f, b)
+                assert np.max(np.abs(x - xr)) <= 1e-10 * max(1.0, np.max(np.abs(xr)))
+
+
 def test_cluster_and_record_invariants_on_the_battery_models():
     for name in util.BATTERY:
         b = util.bundle(name)
