@@ -421,7 +421,7 @@ def run_b200_arm(args):
         }
         # parity of the GPU results against the oracle on the sampled systems
         y_host, t_host = d_y[:n_cpu].cpu().numpy(), d_t[:n_cpu].cpu().numpy()
-        wv = wt = 0.0
+        wv = wt = wk = 0.0
         agree = True
         for i in range(n_cpu):
             k = int(n_t[i])
@@ -429,10 +429,14 @@ def run_b200_arm(args):
                 agree = False
                 continue
             m = k - 1 if flags[i] == 2 else k
-            wv = max(wv, float(np.max(np.abs(y_host[i, :m, 0] - ref["y"][i][:m, 0]))))
+            dv = np.abs(y_host[i, :m, 0] - ref["y"][i][:m, 0])
+            wv = max(wv, float(np.max(dv)))
+            # the same without the last grid point before a voltage cut-off: on that knee |dV/dt| is ~100x larger and two
+            # integrations at rtol = atol = 1e-8 differ by more than 1e-6 V from EACH OTHER'S tighter-tolerance limit
+            wk = max(wk, float(np.max(dv[:m - 1]))) if flags[i] == 2 and m > 1 else max(wk, float(np.max(dv)))
             wt = max(wt, abs(float(t_host[i, k - 1]) - float(ref["t"][i][-1])))
-        line["parity_vs_oracle"] = {"systems": n_cpu, "max_abs_dV": wv, "max_abs_dt_end": wt, "same_termination": agree,
-                                    "bars": {"dV": 1e-6, "dt": 1e-3}}
+        line["parity_vs_oracle"] = {"systems": n_cpu, "max_abs_dV": wv, "max_abs_dV_before_the_cutoff_knee": wk,
+                                    "max_abs_dt_end": wt, "same_termination": agree, "bars": {"dV": 1e-6, "dt": 1e-3}}
         if world == 1:
             line["cpu_baseline"] = {"value": n_cpu / cpu_s, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"first {n_cpu} of the {n} input sets, one pass",
