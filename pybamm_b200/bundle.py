@@ -67,8 +67,18 @@ class ModelBundle:
             inputs_list = [inputs_list]
         out = np.empty((len(inputs_list), self.n_inputs))
         layout = self.input_layout()
+        names = list(self.input_names)
+        if all(size == 1 for _, size in layout.values()):
+            # scalar inputs (the usual case): one pass over the dicts, no per-entry numpy calls
+            try:
+                out[:, [layout[n][0] for n in names]] = [[d[n] for n in names] for d in inputs_list]
+                return out
+            except KeyError:
+                pass              # fall through to the loop below for the reference's error message
+            except (TypeError, ValueError):
+                pass              # size-1 arrays etc.: the general path handles them
         for i, d in enumerate(inputs_list):
-            missing = [n for n in self.input_names if n not in d]
+            missing = [n for n in names if n not in d]
             if missing:
                 raise ValueError(
                     "No value provided for input: [" + ", ".join(f"'{m}'" for m in missing) + "]"

@@ -54,23 +54,32 @@ class Solution:
     time-major block), ``t_event``, ``y_event``, ``termination``.
     """
 
+    __slots__ = ("t", "_rows", "all_inputs", "flag", "y_event", "_stats", "_variables", "closest_event_idx", "termination")
+
     def __init__(self, t, y_rows, inputs, flag, y_term, stats, variables, event_names, closest_event_idx):
+        # cheap on purpose: a batch builds ten thousand of these; everything derivable is a property
         self.t = t
         self._rows = y_rows
         self.all_inputs = [inputs]
-        self.flag = int(flag)
+        self.flag = flag
         self.y_event = y_term
-        self.t_event = np.array([t[-1]]) if len(t) else np.array([])
-        self.stats = dict(zip(STAT_NAMES, (int(s) for s in stats))) if stats is not None else {}
+        self._stats = stats
         self._variables = variables
         self.closest_event_idx = closest_event_idx
-        if self.flag == IDA_ROOT_RETURN:
-            name = event_names[closest_event_idx] if closest_event_idx is not None else "?"
-            self.termination = f"event: {name}"
-        elif self.flag >= 0:
+        if flag == IDA_ROOT_RETURN:
+            self.termination = "event: " + (event_names[closest_event_idx] if closest_event_idx is not None else "?")
+        elif flag >= 0:
             self.termination = "final time"
         else:
             self.termination = "failure"
+
+    @property
+    def t_event(self):
+        return np.array([self.t[-1]]) if len(self.t) else np.array([])
+
+    @property
+    def stats(self):
+        return dict(zip(STAT_NAMES, (int(s) for s in self._stats))) if self._stats is not None else {}
 
     @property
     def y(self):
@@ -367,24 +376,25 @@ class BatchedIDASolver:
         ev_vals = None
         if self.bundle.n_events and np.any(r["flag"] == IDA_ROOT_RETURN):
             # which event fired: argmin |g| at the final state (idaklu_solver.py:826-834)
-            t_end = np.array([r["t"][i, max(r["n_t"][i] - 1, 0)] for i in range(len(inputs_list))])
+            t_end = r["t"][np.arange(len(inputs_list)), np.maximum(r["n_t"] - 1, 0)]
             ev_vals = np.abs(self.eval("events", r["y_term"], p, t_end))
+        n_t, flags = r["n_t"].tolist(), r["flag"].tolist()
+        closest = np.nanargmin(ev_vals, axis=1).tolist() if ev_vals is not None else None
+        t_all, y_all, yt_all, st_all = r["t"], r["y"], r["y_term"], r["stats"]
+        names = self.bundle.event_names
         for i, d in enumerate(inputs_list):
-            n = int(r["n_t"][i])
-            flag = int(r["flag"][i])
+            n, flag = n_t[i], flags[i]
             if flag < 0:
                 msg = sundials_error_message(flag)
                 if self.on_failure == "error":
                     raise SolverError(msg)
                 if self.on_failure == "warn":
                     warnings.warn(msg + ", returning a partial solution.", stacklevel=2)
-            idx = int(np.nanargmin(ev_vals[i])) if (flag == IDA_ROOT_RETURN and ev_vals is not None) else None
+            idx = closest[i] if (flag == IDA_ROOT_RETURN and closest is not None) else None
             if n == 1 and flag == IDA_ROOT_RETURN:
-                names = [self.bundle.event_names[k] for k in range(self.bundle.n_events)]
-                raise SolverError(f"Events {names} are non-positive at initial conditions")
-            sols.append(Solution(r["t"][i, :n], r["y"][i, :n], d, flag, r["y_term"][i],
-                                 r["stats"][i] if r["stats"] is not None else None, variables,
-                                 self.bundle.event_names, idx))
+                raise SolverError(f"Events {[names[k] for k in range(self.bundle.n_events)]} are non-positive at initial conditions")
+            sols.append(Solution(t_all[i, :n], y_all[i, :n], d, flag, yt_all[i], st_all[i] if st_all is not None else None,
+                                 variables, names, idx))
         return sols[0] if single else sols
 
     # -- device evaluation of the generated functions (parity tests, event identification) ---------
