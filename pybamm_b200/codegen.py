@@ -407,6 +407,13 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
         it_n = _itype(sym.n)
         lines.append(f"static PB_TABLE const {it_n} pbm_perm_r[{sym.n}] = {{{', '.join(str(int(x)) for x in sym.perm_r)}}};")
         lines.append(f"static PB_TABLE const {it_n} pbm_perm_c[{sym.n}] = {{{', '.join(str(int(x)) for x in sym.perm_c)}}};")
+        # inverse permutations: where original row / unknown i sits in the permuted vector (the Newton loop writes its
+        # right-hand side straight into the solve's w vector and reads the correction from it)
+        ipr, ipc = np.empty(sym.n, np.int64), np.empty(sym.n, np.int64)
+        ipr[np.asarray(sym.perm_r)] = np.arange(sym.n)
+        ipc[np.asarray(sym.perm_c)] = np.arange(sym.n)
+        lines.append(f"static PB_TABLE const {it_n} pbm_iperm_r[{sym.n}] = {{{', '.join(str(int(x)) for x in ipr)}}};")
+        lines.append(f"static PB_TABLE const {it_n} pbm_iperm_c[{sym.n}] = {{{', '.join(str(int(x)) for x in ipc)}}};")
         lines.append(f"#define PBM_FAC_NLEV {sym.factor.n_levels}")
         lines.append(f"#define PBM_FWD_NLEV {sym.fwd.n_levels}")
         lines.append(f"#define PBM_BWD_NLEV {sym.bwd.n_levels}")

@@ -675,8 +675,10 @@ static __device__ __noinline__ void pb_solve_program(const unsigned int* PB_REST
 #endif
 
 // Solve (J - cj M) x = b in place (b: shared vector), w = S_W scratch. Ends with a team barrier.
+// INW: the caller has already put the permuted right-hand side into w (w[pbm_iperm_r[i]] = b_i, barrier done) and
+// reads the solution from it (x_j = w[pbm_iperm_c[j]]): no gather / scatter passes (the Newton loop, pb_nls_impl).
 // TRACE (tools/gpu_cycles.py only): thread 0 stores the clock64() cycles of gather, every record, scatter in trace[].
-template <int TRACE>
+template <int TRACE, int INW = 0>
 static PB_DEV void pb_lu_solve_t(pb_sys& S, double* b, double* trace) {
   const double* lu = S_LU(S);
   long long tr0 = 0;
@@ -686,8 +688,10 @@ static PB_DEV void pb_lu_solve_t(pb_sys& S, double* b, double* trace) {
 #if defined(PB_PROFILE) && PB_PROFILE == 2
   PB_T0(tga_);
 #endif
-  for (int i = PB_TID; i < PBM_N; i += PB_TEAM) w[i] = b[(int)PB_LD(pbm_perm_r[i])];
-  PB_SYNC();
+  if (!INW) {
+    for (int i = PB_TID; i < PBM_N; i += PB_TEAM) w[i] = b[(int)PB_LD(pbm_perm_r[i])];
+    PB_SYNC();
+  }
 #if defined(PB_PROFILE) && PB_PROFILE == 2
   PB_T1(S, tga_, 5);   // PB_PROFILE=2: slots 5/6/7 = gather / records / scatter of the triangular solves
   PB_T0(tlv_);
@@ -793,14 +797,17 @@ static PB_DEV void pb_lu_solve_t(pb_sys& S, double* b, double* trace) {
   PB_T1(S, tlv_, 6);
   PB_T0(tsc_);
 #endif
-  for (int i = PB_TID; i < PBM_N; i += PB_TEAM) b[(int)PB_LD(pbm_perm_c[i])] = w[i];
-  PB_SYNC();
+  if (!INW) {
+    for (int i = PB_TID; i < PBM_N; i += PB_TEAM) b[(int)PB_LD(pbm_perm_c[i])] = w[i];
+    PB_SYNC();
+  }
 #if defined(PB_PROFILE) && PB_PROFILE == 2
   PB_T1(S, tsc_, 7);
 #endif
   if (TRACE && PB_TID == 0) trace[trk] = (double)(clock64() - tr0);
 }
 static PB_DEV void pb_lu_solve(pb_sys& S, double* b) { pb_lu_solve_t<0>(S, b, nullptr); }
+static PB_DEV void pb_lu_solve_in_w(pb_sys& S) { pb_lu_solve_t<0, 1>(S, nullptr, nullptr); }
 
 // Evaluate J - cj*M at (t, y) into the LU value array and factor it.  ic_mode: replace the
 // differential rows by identity rows (the algebraic sub-block system of the IC Newton,
@@ -1137,18 +1144,19 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
             yp[k] = (i < PBM_NDIFF) ? yppred[i] : 0.0;
             ev[k] = (i < PBM_NDIFF) ? ee[i] : 0.0;
           }
+          double* PB_RESTRICT w = S_W(S);
           PB_VEC_FOR(k, i) {
             if (i < PBM_N) {
               double r = delta[i];
               if (i < PBM_NDIFF) r -= yp[k] + S.cj * ev[k];
-              delta[i] = -r;
+              w[(int)PB_LD(pbm_iperm_r[i])] = -r;     // straight into the solve's permuted vector
             }
           }
         }
         PB_SYNC();
         {
           PB_T0(ts_);
-          pb_lu_solve(S, delta);
+          pb_lu_solve_in_w(S);
           PB_T1(S, ts_, 1);
         }
         const double scale = (S.scalesol && S.cjratio != 1.0) ? 2.0 / (1.0 + S.cjratio) : 1.0;
@@ -1160,9 +1168,10 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
             pv[k] = (i < PBM_N) ? yypred[i] : 0.0;
             wv[k] = (i < PBM_N) ? ewt[i] : 0.0;
           }
+          const double* PB_RESTRICT w = S_W(S);
           PB_VEC_FOR(k, i) {
             if (i < PBM_N) {
-              const double d = delta[i] * scale;
+              const double d = w[(int)PB_LD(pbm_iperm_c[i])] * scale;
               const double e = ev[k] + d;
               ee[i] = e;
               yy[i] = pv[k] + e;
