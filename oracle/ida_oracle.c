@@ -62,12 +62,14 @@ typedef struct {
   int max_iter_ic;       /* max_num_iterations_ic 100 */
   int max_backtracks_ic; /* max_linesearch_backtracks_ic 5 */
   int scalesol;          /* linear_solution_scaling 1 */
+  double dt_init;        /* 0 -> IDA heuristic */
+  double dt_max;         /* 0 -> unbounded */
 } pbo_options;
 
 void pbo_default_options(pbo_options* o) {
   o->rtol = 1e-4; o->maxord = 5; o->max_num_steps = 100000; o->maxnef = 10; o->maxcor = 40;
   o->maxncf = 100; o->epcon = 0.33; o->epsNewtIC = 0.0033; o->step_tol_ic = 1e-4;
-  o->max_iter_ic = 100; o->max_backtracks_ic = 5; o->scalesol = 1;
+  o->max_iter_ic = 100; o->max_backtracks_ic = 5; o->scalesol = 1; o->dt_init = 0.0; o->dt_max = 0.0;
 }
 
 /* ------------------------------------------------------------------ banded LU */
@@ -164,7 +166,7 @@ typedef struct {
   double psi[MXORDP1], alpha[MXORDP1], beta[MXORDP1], sigma[MXORDP1], gamma[MXORDP1];
   double *ewt, *ee, *delta, *yypredict, *yppredict, *yy, *yp, *tempv, *savres, *jacv, *tmp, *bw;
   double *p;
-  double tn, hh, hused, cj, cjlast, cjold, cjratio, ss, rr, epsNewt, toldel;
+  double tn, hh, hused, cj, cjlast, cjold, cjratio, ss, rr, epsNewt, toldel, hmax_inv;
   int kk, kused, knew, phase, ns;
   long nst;
   double tstop; int tstopset;
@@ -426,8 +428,15 @@ static void complete_step(ida_t* S, double err_k, double err_km1) {
   S->kused = S->kk; S->hused = S->hh;
   if (S->knew == S->kk - 1 || S->kk == S->opt.maxord) S->phase = 1;
   if (S->phase == 0) {
-    S->kk++;
-    S->hh = 2.0 * S->hh;
+    /* IDACompleteStep: "after the first step, the order is not increased, as not all of the necessary
+     * information is available yet" -- the raise-and-double of phase 0 starts with the second step */
+    if (S->nst > 1) {
+      S->kk++;
+      double hnew = 2.0 * S->hh;
+      const double tmp = fabs(hnew) * S->hmax_inv;
+      if (tmp > 1.0) hnew /= tmp;
+      S->hh = hnew;
+    }
   } else {
     enum { UNSET, LOWER, MAINTAIN, RAISE } action = UNSET;
     double err_kp1 = 0.0, err_knew;
@@ -452,7 +461,11 @@ static void complete_step(ida_t* S, double err_k, double err_km1) {
     else err_knew = err_k;
     double hnew = S->hh;
     S->rr = pow(2.0 * err_knew + 0.0001, -1.0 / (S->kk + 1));
-    if (S->rr >= 2.0) hnew = 2.0 * S->hh;
+    if (S->rr >= 2.0) {
+      hnew = 2.0 * S->hh;
+      const double tmp = fabs(hnew) * S->hmax_inv;
+      if (tmp > 1.0) hnew /= tmp;
+    }
     else if (S->rr <= 1.0) { S->rr = fmax(0.5, fmin(0.9, S->rr)); hnew = S->hh * S->rr; }
     S->hh = hnew;
   }
@@ -590,10 +603,15 @@ static int ida_solve_one_step(ida_t* S, double tout, double* tret) {
   if (S->nst == 0) {
     if (ewt_set(S, S->phi[0])) return -22;
     double tdist = fabs(tout - S->tn);
-    S->hh = 0.001 * tdist;
-    double ypnorm = wrms(S, S->phi[1]);
-    if (ypnorm > 0.5 / S->hh) S->hh = 0.5 / ypnorm;
-    if (tout < S->tn) S->hh = -S->hh;
+    if (S->opt.dt_init != 0.0) {
+      S->hh = S->opt.dt_init;
+    } else {
+      S->hh = 0.001 * tdist;
+      double ypnorm = wrms(S, S->phi[1]);
+      if (ypnorm > 0.5 / S->hh) S->hh = 0.5 / ypnorm;
+      if (tout < S->tn) S->hh = -S->hh;
+    }
+    { const double rh = fabs(S->hh) * S->hmax_inv; if (rh > 1.0) S->hh /= rh; }
     if (S->tstopset && (S->tn + S->hh - S->tstop) * S->hh > 0.0) S->hh = (S->tstop - S->tn) * (1.0 - 4.0 * UROUND);
     S->kk = 0; S->kused = 0;
     for (int i = 0; i < S->n; i++) S->phi[1][i] *= S->hh;
@@ -828,6 +846,7 @@ static ida_t* ida_alloc(const pbo_model* m, const pbo_options* opt, const double
   ida_t* S = (ida_t*)calloc(1, sizeof(ida_t));
   const int n = m->n;
   S->m = m; S->opt = *opt; S->atol = atol; S->perm = perm; S->n = n;
+  S->hmax_inv = (opt->dt_max > 0.0) ? 1.0 / opt->dt_max : 0.0;
   S->iperm = (int*)malloc(sizeof(int) * n);
   for (int i = 0; i < n; i++) S->iperm[perm ? perm[i] : i] = i;
   for (int j = 0; j < MXORDP1; j++) S->phi[j] = (double*)calloc(n, sizeof(double));

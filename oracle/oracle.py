@@ -15,7 +15,7 @@ class Options(C.Structure):
     _fields_ = [("rtol", C.c_double), ("maxord", C.c_int), ("max_num_steps", C.c_long), ("maxnef", C.c_int),
                 ("maxcor", C.c_int), ("maxncf", C.c_int), ("epcon", C.c_double), ("epsNewtIC", C.c_double),
                 ("step_tol_ic", C.c_double), ("max_iter_ic", C.c_int), ("max_backtracks_ic", C.c_int),
-                ("scalesol", C.c_int)]
+                ("scalesol", C.c_int), ("dt_init", C.c_double), ("dt_max", C.c_double)]
 
 
 _dp = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")

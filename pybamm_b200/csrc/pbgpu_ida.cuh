@@ -1330,11 +1330,15 @@ static PB_DEV void pb_complete_step(pb_sys& S, double err_k, double err_km1) {
   S.hused = S.hh;
   if (S.knew == S.kk - 1 || S.kk == S.maxord) S.phase = 1;
   if (S.phase == 0) {
-    S.kk++;
-    double hnew = 2.0 * S.hh;
-    const double tmp = fabs(hnew) * S.hmax_inv;
-    if (tmp > 1.0) hnew /= tmp;
-    S.hh = hnew;
+    // "after the first step, the order is not increased, as not all of the necessary information is available yet"
+    // (IDACompleteStep): the raise-and-double of phase 0 starts with the second step
+    if (S.nst > 1) {
+      S.kk++;
+      double hnew = 2.0 * S.hh;
+      const double tmp = fabs(hnew) * S.hmax_inv;
+      if (tmp > 1.0) hnew /= tmp;
+      S.hh = hnew;
+    }
   } else {
     int action = 0;  // 0 unset, 1 lower, 2 maintain, 3 raise
     double err_kp1 = 0.0, err_knew;
