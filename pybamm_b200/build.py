@@ -55,11 +55,11 @@ def _src_digest(paths):
     return h.hexdigest()[:16]
 
 
-def generate(bundle: ModelBundle, dialect: str, outdir=BUILD):
+def generate(bundle: ModelBundle, dialect: str, outdir=BUILD, tag=""):
     text, info = codegen.generate(bundle, dialect)
-    path = os.path.join(outdir, f"{bundle.name}_{dialect}.h")
+    path = os.path.join(outdir, f"{bundle.name}{tag}_{dialect}.h")
     _write_if_changed(path, text)
-    with open(os.path.join(outdir, f"{bundle.name}_{dialect}.json"), "w") as f:
+    with open(os.path.join(outdir, f"{bundle.name}{tag}_{dialect}.json"), "w") as f:
         json.dump(info, f, indent=1)
     return path, info
 
@@ -82,18 +82,21 @@ def build_oracle(bundle: ModelBundle, force=False):
     return out
 
 
-def build_model(bundle: ModelBundle, force=False, team=None, verbose=False, profile=False, tag="", defines=(), extra_flags=()):
+def build_model(bundle: ModelBundle, force=False, team=None, verbose=False, profile=False, tag="", defines=(), extra_flags=(),
+                gvec=None, min_teams=None):
     """Generate + nvcc-compile the sm_100a solver image of a bundle. Returns the .so path."""
     os.makedirs(BUILD, exist_ok=True)
-    header, info = generate(bundle, "cuda", BUILD)
+    header, info = generate(bundle, "cuda", BUILD, tag=tag)
     out = os.path.join(BUILD, f"pbgpu_model_{bundle.name}{('_prof' + (str(int(profile)) if int(profile) > 1 else '')) if profile else ''}{tag}.so")
     kernel_srcs = [os.path.join(CSRC, f) for f in ("pbgpu_model.cu", "pbgpu_ida.cuh", "pbgpu_team.cuh")]
     inc = os.path.join(ROOT, "include")
     srcs = kernel_srcs + [header, os.path.join(inc, "pbgpu.h")]
     if team is None:
         team = default_team(bundle)
-    gvec = 1 if bundle.n_states > 256 else 0   # streamed vectors in global scratch for large models (pbgpu_ida.cuh)
-    min_teams = 2 if gvec else 1               # register cap: two large teams per SM (65536 / (2 * team) registers each)
+    if gvec is None:
+        gvec = 1 if bundle.n_states > 256 else 0   # streamed vectors in global scratch for large models (pbgpu_ida.cuh)
+    if min_teams is None:
+        min_teams = 2 if gvec else 1           # register cap: two large teams per SM (65536 / (2 * team) registers each)
     dig = _src_digest(srcs) + f"-t{team}-g{gvec}-m{min_teams}-p{int(profile)}-{'-'.join(defines)}-{'-'.join(extra_flags)}-" + hashlib.sha256(" ".join(NVCC_FLAGS).encode()).hexdigest()[:8]
     stamp = out + ".stamp"
     if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:

@@ -41,7 +41,7 @@ def _dlit(v):
 
 
 _UN = {
-    ir.NEG: "(-{a})", ir.ABS: "fabs({a})", ir.EXP: "PB_EXP({a})", ir.LOG: "PB_LOG({a})", ir.SQRT: "sqrt({a})",
+    ir.NEG: "(-{a})", ir.ABS: "fabs({a})", ir.EXP: "PB_EXP({a})", ir.LOG: "PB_LOG({a})", ir.SQRT: "PB_SQRT({a})",
     ir.TANH: "PB_TANH({a})", ir.SINH: "PB_SINH({a})", ir.COSH: "PB_COSH({a})", ir.SIN: "sin({a})", ir.COS: "cos({a})",
     ir.ASINH: "PB_ASINH({a})", ir.ATAN: "atan({a})", ir.ERF: "erf({a})", ir.ERFC: "erfc({a})",
     ir.FLOOR: "floor({a})", ir.CEIL: "ceil({a})", ir.RECIP: "(1.0 / {a})", ir.SQR: "({a} * {a})",
@@ -81,6 +81,35 @@ def _itype(maxval):
     return "unsigned short" if maxval < 65536 else "int"
 
 
+# Per-instance tables of mesh models repeat: the stencil coefficients of a particle depend on the radial node only, the
+# state indices advance by a fixed stride from one particle to the next.  Such columns are stored once per period
+# (DFN residual: 50 KB of tables -> 14 KB, which is what decides whether they stay in the 28 KB of L1 left beside the
+# shared-memory carve-out).  PBGPU_TABLE_COMPRESS=0 emits the plain per-instance tables.
+TABLE_COMPRESS = bool(int(__import__("os").environ.get("PBGPU_TABLE_COMPRESS", "1")))
+_MAX_PERIOD = 64
+
+
+def _period(vals):
+    """Smallest P >= 2 with vals[q + P] - vals[q] constant for all q (0 for float columns), or None."""
+    n = len(vals)
+    for P in range(2, min(n // 2, _MAX_PERIOD) + 1):
+        d = vals[P:] - vals[:-P]
+        if np.all(d == d[0]) and (d[0] == 0 or np.issubdtype(vals.dtype, np.integer)):
+            return P, d[0]
+    return None
+
+
+def _blocked(vals):
+    """Smallest B >= 2 dividing n with vals constant inside every block of B, or None."""
+    n = len(vals)
+    for B in range(2, n // 2 + 1):
+        if n % B == 0 and n // B <= 4 * _MAX_PERIOD:
+            m = vals.reshape(-1, B)
+            if np.all(m == m[:, :1]):
+                return B
+    return None
+
+
 def _slot_expr(em, values, q, hint):
     """Expression for per-instance integer ``values`` indexed by instance ``q``."""
     vals = np.asarray(values, dtype=np.int64)
@@ -93,8 +122,34 @@ def _slot_expr(em, values, q, hint):
         return f"({int(vals[0])} + {int(d)} * {q})"
     if len(vals) == 2:
         return f"({int(vals[0])} + {int(d)} * {q})"
+    if TABLE_COMPRESS and len(vals) >= 8:
+        pr = _period(vals)
+        if pr is not None:
+            P, stride = pr
+            base = vals[:P]
+            dd = np.diff(base)
+            if np.all(dd == dd[0]):     # affine inside the period as well: no table at all
+                return f"({int(base[0])} + {int(dd[0])} * ({q} % {P}) + {int(stride)} * ({q} / {P}))"
+            name = em.table(_itype(int(base.max())), base, hint)
+            return f"((int)PB_LD({name}[{q} % {P}]) + {int(stride)} * ({q} / {P}))"
     name = em.table(_itype(int(vals.max())), vals, hint)
     return f"(int)PB_LD({name}[{q}])"
+
+
+def _const_expr(em, col, q):
+    """Expression for a per-instance constant column (not all equal)."""
+    if TABLE_COMPRESS and len(col) >= 8:
+        pr = _period(col)
+        if pr is not None:
+            P = pr[0]
+            name = em.table("double", col[:P], "c")
+            return f"PB_LD({name}[{q} % {P}])"
+        B = _blocked(col)
+        if B is not None:
+            name = em.table("double", col[::B], "c")
+            return f"PB_LD({name}[{q} / {B}])"
+    name = em.table("double", col, "c")
+    return f"PB_LD({name}[{q}])"
 
 
 def _emit_template(em: _Emitter, tp, dest, lines, ind):
@@ -113,9 +168,17 @@ def _emit_template(em: _Emitter, tp, dest, lines, ind):
         if np.all(col == col[0]) or (np.all(np.isnan(col))):
             refs[("c", k)] = _dlit(col[0])
         else:
-            name = em.table("double", col, "c")
-            lines.append(f"{ind}const double c{k} = PB_LD({name}[q]);")
+            lines.append(f"{ind}const double c{k} = {_const_expr(em, col, 'q')};")
             refs[("c", k)] = f"c{k}"
+    i_idx = np.asarray(tp.i_idx, dtype=np.int64).reshape(n, tp.n_i)
+    for k in range(tp.n_i):
+        col = i_idx[:, k]
+        if np.all(col == col[0]):
+            refs[("i", k)] = f"p[{int(col[0])}]"
+        else:
+            e = _slot_expr(em, col, "q", "i")
+            lines.append(f"{ind}const double i{k} = p[{e}];")
+            refs[("i", k)] = f"i{k}"
     for k in range(tp.n_m):
         e = _slot_expr(em, m_idx[:, k], "q", "m")
         lines.append(f"{ind}const double m{k} = tmp[{e}];")
@@ -125,8 +188,6 @@ def _emit_template(em: _Emitter, tp, dest, lines, ind):
         kind = r[0]
         if kind == "v":
             return f"v{r[1]}"
-        if kind == "i":
-            return f"p[{r[1]}]"
         if kind == "t":
             return "t"
         if kind == "j":
@@ -137,6 +198,14 @@ def _emit_template(em: _Emitter, tp, dest, lines, ind):
         a = [ref(r) for r in args]
         if o == ir.SELECT:
             e = f"(({a[0]} != 0.0) ? {a[1]} : {a[2]})"
+        elif o == ir.POW and args[1][0] == "c" and np.all(c_val[:, args[1][1]] == -0.25):
+            e = f"PB_POWM025({a[0]})"     # reg_power's x^-1/4 and its derivative x^-5/4: two square roots instead of pow()
+        elif o == ir.POW and args[1][0] == "c" and np.all(c_val[:, args[1][1]] == -1.25):
+            e = f"PB_POWM125({a[0]})"
+        elif o == ir.DIV:
+            e = f"PB_DIV({a[0]}, {a[1]})"
+        elif o == ir.RECIP:
+            e = f"PB_DIV(1.0, {a[0]})"
         elif o in _UN:
             e = _UN[o].format(a=a[0])
         else:
@@ -199,6 +268,8 @@ def _emit_u32(lines, name, words):
     lines.append(f"static PB_TABLE PB_ALIGN16 const unsigned int {name}[{max(len(words), 1)}] = {{{body}}};")
 
 
+SPLIT_RES = bool(int(__import__("os").environ.get("PBGPU_SPLIT_RES", "0")))   # measured on the DFN: -6 % (two more stage barriers, 580 more tmp slots)
+
 # shared memory the team may spend on the factor stream (bytes); larger streams stay in global memory / L1
 FACTOR_STREAM_SMEM_BUDGET = 24 * 1024
 
@@ -210,7 +281,8 @@ def model_functions(bundle, sym: slu.SymbolicLU | None, dialect: str):
     jroots = [g.sub(int(n), cjn) if (r == c and r < bundle.n_diff) else int(n)
               for n, r, c in zip(bundle.jac_nodes, bundle.jac_rows, bundle.jac_cols)]
     progs = {}
-    progs["res"] = build_program(g, bundle.rhs_alg, "res")
+    # the team-parallel dialect splits heavy narrow templates of the residual over the warps (program.build_program)
+    progs["res"] = build_program(g, bundle.rhs_alg, "res", split=(dialect == "cuda" and SPLIT_RES))
     if dialect == "cuda":
         progs["jac"] = build_program(g, jroots, "jac", out_index=sym.a_slot, n_out=sym.nnz_lu)
     else:
@@ -371,6 +443,16 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
         out.append(f"#define PB_{fn}(x) {fn.lower()}(x)")
     out.append("#define PB_POW(x, y) pow(x, y)")
     out.append("#endif")
+    out.append("#ifndef PB_POWM025")
+    out.append("#define PB_POWM025(x) pow(x, -0.25)")
+    out.append("#define PB_POWM125(x) pow(x, -1.25)")
+    out.append("#endif")
+    out.append("#ifndef PB_SQRT")
+    out.append("#define PB_SQRT(x) sqrt(x)")
+    out.append("#endif")
+    out.append("#ifndef PB_DIV")
+    out.append("#define PB_DIV(a, b) ((a) / (b))")
+    out.append("#endif")
     out.append(f'#define PBM_NAME "{bundle.name}"')
     out.append(f"#define PBM_N {bundle.n_states}")
     out.append(f"#define PBM_NDIFF {bundle.n_diff}")
@@ -433,6 +515,14 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
         lines.append(f"#define PBM_FAC_SMEM {1 if 4 * len(sym.factor_stream) <= FACTOR_STREAM_SMEM_BUDGET else 0}")
         _emit_u32(lines, "pbm_slv_tab", sym.solve_stream)
         _emit_u32(lines, "pbm_fac_tab", sym.factor_stream)
+        if 4 * len(sym.factor_stream) > FACTOR_STREAM_SMEM_BUDGET:
+            # staging plan of pb_lu_factor: consecutive whole records packed into chunks that fit the solve's w scratch
+            chunks = slu.factor_chunks(sym.factor_stream, 2 * sym.n)
+            if chunks is not None:
+                flat = [x for c in chunks for x in c] + [len(sym.factor_stream), 0]
+                lines.append(f"#define PBM_FAC_NCHUNK {len(chunks)}")
+                lines.append(f"#define PBM_FAC_CHUNK_WORDS {max(b - a for (a, _), (b, _) in zip(chunks, chunks[1:] + [(len(sym.factor_stream), 0)]))}")
+                lines.append(f"static PB_CTABLE const unsigned int pbm_fac_chunk[{len(flat)}] = {{" + ", ".join(f"{x}u" for x in flat) + "};")
         lines.append(emit_solve_program(sym))
         out.append("\n".join(lines))
         out.append(f"#define PBM_FLOPS_FACTOR {sym.flops_factor}")

@@ -66,9 +66,14 @@
 #define PB_SCRATCH_DOUBLES 0
 #endif
 #define PB_OFF_YY (PB_OFF_DELTA + PBM_N)
-#define PB_OFF_W (PB_OFF_YY + PBM_N)
-#define PB_OFF_TMP (PB_OFF_W + PBM_N + 1)
-#define PB_OFF_LU (PB_OFF_TMP + PBM_NTMP_SMALL)
+// The temporaries of the generated functions (residual, events, output variables) ALIAS the solve's w scratch: no
+// generated function runs while w is live (w holds a right-hand side only between the Newton loop's rhs pass and its
+// update pass, and inside pb_lu_solve / pb_lu_factor).  tmp[0, PB_TMP_EXTRA) is private, the rest is w[0, N); w[N], the
+// zero operand of the padded solve records, is never touched.
+#define PB_TMP_EXTRA ((PBM_NTMP_SMALL > PBM_N) ? (PBM_NTMP_SMALL - PBM_N) : 0)
+#define PB_OFF_TMP (PB_OFF_YY + PBM_N)
+#define PB_OFF_W (PB_OFF_TMP + PB_TMP_EXTRA)
+#define PB_OFF_LU (PB_OFF_W + PBM_N + 1)
 #define PB_OFF_P (PB_OFF_LU + PBM_NNZ_LU + 3)
 #define PB_OFF_G (PB_OFF_P + PBM_NP)
 #define PB_OFF_COEF (PB_OFF_G + 3 * PB_NEV_PAD)
@@ -184,110 +189,54 @@ struct pb_sys {
 #define PB_F_TEAM 4u
 #define PB_F_GROUP 8u
 
+// Where the factor stream is read from:
+//   PBM_FAC_SMEM   the whole stream sits in the team's shared memory (small models);
+//   PB_FAC_STAGE   large models: the stream (DFN: 95 KB) stays in global memory and is *staged* through the solve's w
+//                  scratch (free during a factorisation) in chunks of whole records (table pbm_fac_chunk, built by
+//                  codegen).  The next chunk travels from L2 into registers while the current one is being processed,
+//                  so a record costs shared-memory round trips only -- read straight from global memory every record
+//                  paid three dependent L2 round trips (meta, task words, operand words; ~1 800 cycles, 197 records);
+//   otherwise      direct global reads (host emulation).
 #if PBM_FAC_SMEM
 #define PB_FAC_LD(x) (x)
+#define PB_FAC_STAGE 0
+#elif !defined(PB_EMU) && defined(PBM_FAC_NCHUNK) && !defined(PB_NO_FAC_STAGE)
+#define PB_FAC_LD(x) (x)
+#define PB_FAC_STAGE 1
 #else
 #define PB_FAC_LD(x) PB_LDU(x)
+#define PB_FAC_STAGE 0
 #endif
 
-// Entry-parallel left-looking factorisation of the values already scattered into lu[] by pbm_jac.
-// Returns non-zero (team-uniform) when a pivot is zero / not finite.
-static PB_DEV int pb_lu_factor(pb_sys& S) {
-  double* lu = S_LU(S);
-  const unsigned int* st = S.fac;
-  double bad = 0.0;
-  int off = 0;
-  unsigned int meta = PB_FAC_LD(st[0]);
-  for (int rec = 0; rec < PBM_FAC_NREC; rec++) {
-    const int nt = (int)(meta & 0xFFFFu), ml = (int)((meta >> 16) & 0xFFFu);
-    const unsigned int fl = meta >> 28;
-    const int base = off + 1;
-    off = base + nt * (1 + ml);
-    if (rec + 1 < PBM_FAC_NREC) meta = PB_FAC_LD(st[off]);
-    const int wide = (fl & PB_F_TEAM) != 0;
-    if (fl & PB_F_GROUP) {   // narrow level, few long tasks: warp 0, 32/nt lanes per task
-      if (PB_WARP == 0) {
+// One record of the factor stream at st[off] (meta already fetched). Returns the offset of the next record.
+static PB_DEV int pb_lu_factor_record(double* PB_RESTRICT lu, const unsigned int* PB_RESTRICT st, const int off,
+                                      const unsigned int meta, double& bad) {
+  const int nt = (int)(meta & 0xFFFFu), ml = (int)((meta >> 16) & 0xFFFu);
+  const unsigned int fl = meta >> 28;
+  const int base = off + 1;
+  const int wide = (fl & PB_F_TEAM) != 0;
+  if (fl & PB_F_GROUP) {   // narrow level, few long tasks: warp 0, 32/nt lanes per task
+    if (PB_WARP == 0) {
 #ifndef PB_EMU
-        const unsigned int tw = PB_FAC_LD(st[base + (PB_LANE & (nt - 1))]);
-        const unsigned int* op = st + base + nt + PB_LANE;
-        const int k_n = (ml * nt) >> 5;
-        double a0 = 0.0, a1 = 0.0;
-        for (int k = 0; k < k_n; k += 8) {   // operand words in batches of eight: one L2 round trip per batch
-          unsigned int o[8];
+      const unsigned int tw = PB_FAC_LD(st[base + (PB_LANE & (nt - 1))]);
+      const unsigned int* op = st + base + nt + PB_LANE;
+      const int k_n = (ml * nt) >> 5;
+      double a0 = 0.0, a1 = 0.0;
+      for (int k = 0; k < k_n; k += 8) {   // operand words in batches of eight
+        unsigned int o[8];
 #pragma unroll
-          for (int j = 0; j < 8; j++) o[j] = (k + j < k_n) ? PB_FAC_LD(op[32 * (k + j)]) : PB_FAC_PAD;
+        for (int j = 0; j < 8; j++) o[j] = (k + j < k_n) ? PB_FAC_LD(op[32 * (k + j)]) : PB_FAC_PAD;
 #pragma unroll
-          for (int j = 0; j < 8; j += 2) {
-            a0 += lu[o[j] & 0xFFFFu] * lu[o[j] >> 16];
-            a1 += lu[o[j + 1] & 0xFFFFu] * lu[o[j + 1] >> 16];
-          }
+        for (int j = 0; j < 8; j += 2) {
+          a0 += lu[o[j] & 0xFFFFu] * lu[o[j] >> 16];
+          a1 += lu[o[j + 1] & 0xFFFFu] * lu[o[j + 1] >> 16];
         }
-        a0 += a1;
-        for (int o = nt; o < 32; o <<= 1) a0 += __shfl_xor_sync(0xffffffffu, a0, o);
-        if (PB_LANE < nt) {
-          const int out = (int)(tw & 0xFFFFu), aux = (int)(tw >> 16);
-          const double acc = (aux == PB_AUX_NEG ? 0.0 : lu[out]) - a0;
-          if (aux == PB_AUX_U || aux == PB_AUX_NEG) {
-            lu[out] = acc;
-          } else if (aux == PB_AUX_DIAG) {
-            const double inv = 1.0 / acc;
-            if (!(fabs(inv) <= 1.7e308) || acc == 0.0) bad = 1.0;
-            lu[out] = inv;
-          } else {
-            lu[out] = acc * lu[aux];
-          }
-        }
-#else
-        for (int q = 0; q < nt; q++) {
-          const unsigned int tw = st[base + q];
-          const int out = (int)(tw & 0xFFFFu), aux = (int)(tw >> 16);
-          double dot = 0.0;
-          for (int p = 0; p < ml; p++) {
-            const unsigned int o0 = st[base + nt + p * nt + q];
-            dot += lu[o0 & 0xFFFFu] * lu[o0 >> 16];
-          }
-          const double acc = (aux == PB_AUX_NEG ? 0.0 : lu[out]) - dot;
-          if (aux == PB_AUX_U || aux == PB_AUX_NEG) {
-            lu[out] = acc;
-          } else if (aux == PB_AUX_DIAG) {
-            const double inv = 1.0 / acc;
-            if (!(fabs(inv) <= 1.7e308) || acc == 0.0) bad = 1.0;
-            lu[out] = inv;
-          } else {
-            lu[out] = acc * lu[aux];
-          }
-        }
-#endif
       }
-      if (fl & PB_F_END) PB_SYNCWARP();
-      continue;
-    }
-    if (wide || PB_WARP == 0) {
-      const int stride = wide ? PB_TEAM : PB_LANES;
-      for (int q = wide ? PB_TID : PB_LANE; q < nt; q += stride) {
-        const unsigned int tw = PB_FAC_LD(st[base + q]);
+      a0 += a1;
+      for (int o = nt; o < 32; o <<= 1) a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+      if (PB_LANE < nt) {
         const int out = (int)(tw & 0xFFFFu), aux = (int)(tw >> 16);
-        const unsigned int* op = st + base + nt + q;
-        double acc0 = (aux == PB_AUX_NEG) ? 0.0 : lu[out], acc1 = 0.0;
-#ifndef PB_EMU
-        for (int p = 0; p < ml; p += 8) {   // operand words in batches of eight: one L2 round trip per batch
-          unsigned int o[8];
-#pragma unroll
-          for (int j = 0; j < 8; j++) o[j] = (p + j < ml) ? PB_FAC_LD(op[(p + j) * nt]) : PB_FAC_PAD;
-#pragma unroll
-          for (int j = 0; j < 8; j += 2) {
-            acc0 -= lu[o[j] & 0xFFFFu] * lu[o[j] >> 16];
-            acc1 -= lu[o[j + 1] & 0xFFFFu] * lu[o[j + 1] >> 16];
-          }
-        }
-#else
-        for (int p = 0; p < ml; p++) {
-          const unsigned int o0 = op[p * nt];
-          if (p & 1) acc1 -= lu[o0 & 0xFFFFu] * lu[o0 >> 16];
-          else acc0 -= lu[o0 & 0xFFFFu] * lu[o0 >> 16];
-        }
-#endif
-        const double acc = acc0 + acc1;
+        const double acc = (aux == PB_AUX_NEG ? 0.0 : lu[out]) - a0;
         if (aux == PB_AUX_U || aux == PB_AUX_NEG) {
           lu[out] = acc;
         } else if (aux == PB_AUX_DIAG) {
@@ -298,12 +247,130 @@ static PB_DEV int pb_lu_factor(pb_sys& S) {
           lu[out] = acc * lu[aux];
         }
       }
+#else
+      for (int q = 0; q < nt; q++) {
+        const unsigned int tw = st[base + q];
+        const int out = (int)(tw & 0xFFFFu), aux = (int)(tw >> 16);
+        double dot = 0.0;
+        for (int p = 0; p < ml; p++) {
+          const unsigned int o0 = st[base + nt + p * nt + q];
+          dot += lu[o0 & 0xFFFFu] * lu[o0 >> 16];
+        }
+        const double acc = (aux == PB_AUX_NEG ? 0.0 : lu[out]) - dot;
+        if (aux == PB_AUX_U || aux == PB_AUX_NEG) {
+          lu[out] = acc;
+        } else if (aux == PB_AUX_DIAG) {
+          const double inv = 1.0 / acc;
+          if (!(fabs(inv) <= 1.7e308) || acc == 0.0) bad = 1.0;
+          lu[out] = inv;
+        } else {
+          lu[out] = acc * lu[aux];
+        }
+      }
+#endif
     }
-    if (fl & PB_F_END) {
-      if (wide) PB_SYNC();
-      else PB_SYNCWARP();
+    if (fl & PB_F_END) PB_SYNCWARP();
+    return base + nt * (1 + ml);
+  }
+  if (wide || PB_WARP == 0) {
+    const int stride = wide ? PB_TEAM : PB_LANES;
+    for (int q = wide ? PB_TID : PB_LANE; q < nt; q += stride) {
+      const unsigned int tw = PB_FAC_LD(st[base + q]);
+      const int out = (int)(tw & 0xFFFFu), aux = (int)(tw >> 16);
+      const unsigned int* op = st + base + nt + q;
+      double acc0 = (aux == PB_AUX_NEG) ? 0.0 : lu[out], acc1 = 0.0;
+#ifndef PB_EMU
+      for (int p = 0; p < ml; p += 8) {   // operand words in batches of eight
+        unsigned int o[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) o[j] = (p + j < ml) ? PB_FAC_LD(op[(p + j) * nt]) : PB_FAC_PAD;
+#pragma unroll
+        for (int j = 0; j < 8; j += 2) {
+          acc0 -= lu[o[j] & 0xFFFFu] * lu[o[j] >> 16];
+          acc1 -= lu[o[j + 1] & 0xFFFFu] * lu[o[j + 1] >> 16];
+        }
+      }
+#else
+      for (int p = 0; p < ml; p++) {
+        const unsigned int o0 = op[p * nt];
+        if (p & 1) acc1 -= lu[o0 & 0xFFFFu] * lu[o0 >> 16];
+        else acc0 -= lu[o0 & 0xFFFFu] * lu[o0 >> 16];
+      }
+#endif
+      const double acc = acc0 + acc1;
+      if (aux == PB_AUX_U || aux == PB_AUX_NEG) {
+        lu[out] = acc;
+      } else if (aux == PB_AUX_DIAG) {
+        const double inv = 1.0 / acc;
+        if (!(fabs(inv) <= 1.7e308) || acc == 0.0) bad = 1.0;
+        lu[out] = inv;
+      } else {
+        lu[out] = acc * lu[aux];
+      }
     }
   }
+  if (fl & PB_F_END) {
+    if (wide) PB_SYNC();
+    else PB_SYNCWARP();
+  }
+  return base + nt * (1 + ml);
+}
+
+// Entry-parallel left-looking factorisation of the values already scattered into lu[] by pbm_jac.
+// Returns non-zero (team-uniform) when a pivot is zero / not finite.
+static PB_DEV int pb_lu_factor(pb_sys& S) {
+  double* lu = S_LU(S);
+  double bad = 0.0;
+#if PB_FAC_STAGE
+  {
+    constexpr int WPT = (PBM_FAC_CHUNK_WORDS + PB_TEAM - 1) / PB_TEAM;
+    static_assert(PBM_FAC_CHUNK_WORDS <= 2 * PBM_N, "factor chunk larger than the w scratch (w[N] is the solve's zero slot)");
+    unsigned int* buf = (unsigned int*)S_W(S);
+    unsigned int pre[WPT];
+    int c_off = (int)pbm_fac_chunk[0], c_len = (int)pbm_fac_chunk[2] - c_off;
+#pragma unroll
+    for (int k = 0; k < WPT; k++) {
+      const int i = PB_TID + k * PB_TEAM;
+      pre[k] = (i < c_len) ? PB_LDU(pbm_fac_tab[c_off + i]) : 0u;
+    }
+    for (int c = 0; c < PBM_FAC_NCHUNK; c++) {
+      const int nrec = (int)pbm_fac_chunk[2 * c + 1];
+      PB_SYNC();   // everybody is done with the previous chunk (and with w before the first one)
+#pragma unroll
+      for (int k = 0; k < WPT; k++) {
+        const int i = PB_TID + k * PB_TEAM;
+        if (i < c_len) buf[i] = pre[k];
+      }
+      PB_SYNC();
+      if (c + 1 < PBM_FAC_NCHUNK) {   // next chunk: L2 -> registers while this one is processed
+        c_off = (int)pbm_fac_chunk[2 * c + 2];
+        c_len = (int)pbm_fac_chunk[2 * c + 4] - c_off;
+#pragma unroll
+        for (int k = 0; k < WPT; k++) {
+          const int i = PB_TID + k * PB_TEAM;
+          pre[k] = (i < c_len) ? PB_LDU(pbm_fac_tab[c_off + i]) : 0u;
+        }
+      }
+      int off = 0;
+      unsigned int meta = buf[0];
+      for (int rec = 0; rec < nrec; rec++) {
+        const int nxt = pb_lu_factor_record(lu, buf, off, meta, bad);
+        off = nxt;
+        if (rec + 1 < nrec) meta = buf[off];
+      }
+    }
+  }
+#else
+  {
+    const unsigned int* st = S.fac;
+    int off = 0;
+    unsigned int meta = PB_FAC_LD(st[0]);
+    for (int rec = 0; rec < PBM_FAC_NREC; rec++) {
+      off = pb_lu_factor_record(lu, st, off, meta, bad);
+      if (rec + 1 < PBM_FAC_NREC) meta = PB_FAC_LD(st[off]);
+    }
+  }
+#endif
   PB_SYNC();
 #if PBM_DENSE_N > 0
   {
@@ -872,28 +939,35 @@ struct pb_interp {
   double c[PB_MXORDP1], d[PB_MXORDP1];
   int kord;
 };
-static PB_DEV void pb_interp_coeffs(const pb_sys& S, double t, pb_interp& I) {
-  const double* psi = S_PSI(S);
-  int kord = S.kused;
+// One out-of-line copy: eleven FP64 divisions (twenty instructions each, inline) at a dozen call sites of
+// pb_get_solution were 40 KB of the kernel; the integration is bound by instruction fetch.
+#ifndef PB_EMU
+static __device__ __noinline__
+#else
+static
+#endif
+void pb_interp_coeffs_impl(const double* psi, int kord, const double delt, pb_interp* I) {
   if (kord == 0) kord = 1;
-  const double delt = t - S.tn;
   double c = 1.0, d = 0.0, gam = delt / psi[0];
-  I.c[0] = c;
-  I.d[0] = 0.0;
-#pragma unroll
+  I->c[0] = c;
+  I->d[0] = 0.0;
+#pragma unroll 1
   for (int j = 1; j < PB_MXORDP1; j++) {
     if (j <= kord) {
       d = d * gam + c / psi[j - 1];
       c = c * gam;
       gam = (delt + psi[j - 1]) / psi[j < PB_MXORDP1 - 1 ? j : PB_MXORDP1 - 1];
-      I.c[j] = c;
-      I.d[j] = d;   // multiplies phi[j] in y'
+      I->c[j] = c;
+      I->d[j] = d;   // multiplies phi[j] in y'
     } else {
-      I.c[j] = 0.0;
-      I.d[j] = 0.0;
+      I->c[j] = 0.0;
+      I->d[j] = 0.0;
     }
   }
-  I.kord = kord;
+  I->kord = kord;
+}
+static PB_DEV void pb_interp_coeffs(const pb_sys& S, double t, pb_interp& I) {
+  pb_interp_coeffs_impl(S_PSI(S), S.kused, t - S.tn, &I);
 }
 // y(t) -> dst (shared or global). No barrier.
 static PB_DEV void pb_get_solution(const pb_sys& S, double t, double* dst) {
@@ -948,47 +1022,59 @@ static PB_DEV void pb_reinit(pb_sys& S, double t0) {
   S.toldel = 1e-4 * S.epsNewt;
 }
 
-// IDASetCoeffs: thread 0 updates the coefficient arrays, everybody gets cj / ck. Ends with a barrier.
+// IDASetCoeffs.  Thread 0 updates the coefficient arrays (one out-of-line copy: five divisions per order) and leaves
+// cj and ck in the two spare slots of the coefficient block; everybody reads them after the barrier.
 // The phi -> phi* scaling (phi[i] *= beta[i], i >= ns) is folded into the predictor pass of pb_nls.
-static PB_DEV void pb_set_coeffs(pb_sys& S, double* ck) {
-  const int kk = S.kk;
-  if (S.hh != S.hused || kk != S.kused) S.ns = 0;
-  S.ns = (S.ns + 1 < S.kused + 2) ? S.ns + 1 : S.kused + 2;
-  double* psi = S_PSI(S);
-  double* alpha = S_ALPHA(S);
-  double* beta = S_BETA(S);
-  double* sigma = S_SIGMA(S);
-  double* gamma = S_GAMMA(S);
-  if (PB_TID == 0) {
-    if (kk + 1 >= S.ns) {
-      beta[0] = 1.0;
-      alpha[0] = 1.0;
-      gamma[0] = 0.0;
-      sigma[0] = 1.0;
-      double temp1 = S.hh;
-      for (int i = 1; i <= kk; i++) {
-        const double temp2 = psi[i - 1];
-        psi[i - 1] = temp1;
-        beta[i] = beta[i - 1] * psi[i - 1] / temp2;
-        temp1 = temp2 + S.hh;
-        alpha[i] = S.hh / temp1;
-        sigma[i] = i * sigma[i - 1] * alpha[i];
-        gamma[i] = gamma[i - 1] + alpha[i - 1] / S.hh;
-      }
-      psi[kk] = temp1;
+#define S_CJCK(S) ((S).sm + PB_OFF_COEF + 30)
+#ifndef PB_EMU
+static __device__ __noinline__
+#else
+static
+#endif
+void pb_set_coeffs_t0(double* coef, const int kk, const int ns, const double hh) {
+  double* psi = coef;
+  double* alpha = coef + 6;
+  double* beta = coef + 12;
+  double* sigma = coef + 18;
+  double* gamma = coef + 24;
+  if (kk + 1 >= ns) {
+    beta[0] = 1.0;
+    alpha[0] = 1.0;
+    gamma[0] = 0.0;
+    sigma[0] = 1.0;
+    double temp1 = hh;
+#pragma unroll 1
+    for (int i = 1; i <= kk; i++) {
+      const double temp2 = psi[i - 1];
+      psi[i - 1] = temp1;
+      beta[i] = beta[i - 1] * psi[i - 1] / temp2;
+      temp1 = temp2 + hh;
+      alpha[i] = hh / temp1;
+      sigma[i] = i * sigma[i - 1] * alpha[i];
+      gamma[i] = gamma[i - 1] + alpha[i - 1] / hh;
     }
+    psi[kk] = temp1;
   }
-  PB_SYNC();
   double alphas = 0.0, alpha0 = 0.0;
+#pragma unroll 1
   for (int i = 0; i < kk; i++) {
     alphas -= 1.0 / (i + 1);
     alpha0 -= alpha[i];
   }
-  S.cjlast = S.cj;
-  S.cj = -alphas / S.hh;
   double c = fabs(alpha[kk] + alphas - alpha0);
   if (alpha[kk] > c) c = alpha[kk];
-  *ck = c;
+  coef[30] = -alphas / hh;
+  coef[31] = c;
+}
+static PB_DEV void pb_set_coeffs(pb_sys& S, double* ck) {
+  const int kk = S.kk;
+  if (S.hh != S.hused || kk != S.kused) S.ns = 0;
+  S.ns = (S.ns + 1 < S.kused + 2) ? S.ns + 1 : S.kused + 2;
+  if (PB_TID == 0) pb_set_coeffs_t0(S_PSI(S), kk, S.ns, S.hh);
+  PB_SYNC();
+  S.cjlast = S.cj;
+  S.cj = S_CJCK(S)[0];
+  *ck = S_CJCK(S)[1];
   S.tn += S.hh;
 }
 

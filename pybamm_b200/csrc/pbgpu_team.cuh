@@ -85,6 +85,24 @@ static __device__ __noinline__ double pb_f_pow(double x, double y) { return pow(
 #define PB_COSH(x) pb_f_cosh(x)
 #define PB_ASINH(x) pb_f_asinh(x)
 #define PB_POW(x, y) pb_f_pow(x, y)
+// reg_power (functions.py:412-431) is x / (x^2 + delta^2)^(1/4): its only powers are x^-1/4 and, in the Jacobian, x^-5/4.
+// Two square roots (correctly rounded each) replace libdevice's 150-instruction pow() on the critical path of the
+// electrode-kinetics templates.  PBGPU_LIBM_POW=1 at build time keeps pow() (A/B switch).
+#ifndef PB_LIBM_POW
+static __device__ __noinline__ double pb_f_powm025(double x) { return rsqrt(sqrt(x)); }
+static __device__ __noinline__ double pb_f_powm125(double x) { return rsqrt(sqrt(x)) / x; }
+#define PB_POWM025(x) pb_f_powm025(x)
+#define PB_POWM125(x) pb_f_powm125(x)
+#endif
+// FP64 division is a 20-instruction sequence with a slow path: one shared copy (PB_INLINE_DIV=1 inlines it again).
+#ifndef PB_INLINE_SQRT
+static __device__ __noinline__ double pb_f_sqrt(double x) { return sqrt(x); }
+#define PB_SQRT(x) pb_f_sqrt(x)
+#endif
+#ifndef PB_INLINE_DIV
+static __device__ __noinline__ double pb_f_div(double a, double b) { return a / b; }
+#define PB_DIV(a, b) pb_f_div(a, b)
+#endif
 
 struct pb_team_ctx {
   double* red;   // 2 * 32 doubles of shared memory for cross-warp reductions (double buffered)

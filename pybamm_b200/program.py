@@ -28,6 +28,7 @@ import numpy as np
 
 from . import ir
 
+MERGE_INPUTS = bool(int(__import__("os").environ.get("PBGPU_MERGE_INPUTS", "1")))   # see extract(): input leaves are slots
 MATERIALISE_COST = 6      # DFMA-equivalents: shared sub-expressions at least this costly get a tmp slot
 SPLIT_COST = 40           # for functions with few roots: split big trees at nodes at least this costly
 FEW_ROOTS = 64
@@ -41,10 +42,13 @@ class Template:
     n_s: int
     n_c: int
     n_m: int
+    n_i: int = 0                    # input-parameter slots ('i', slot): per instance an index into p[]
     out: list = field(default_factory=list)       # per instance: output index (into out vector or tmp)
     s_idx: list = field(default_factory=list)     # per instance: list of state indices
     c_val: list = field(default_factory=list)     # per instance: list of constants
     m_idx: list = field(default_factory=list)     # per instance: list of tmp slots
+    i_idx: list = field(default_factory=list)     # per instance: list of input indices
+    tops: list = field(default_factory=list)      # per instance: the DAG node this instance evaluates
     cost: int = 0
 
     @property
@@ -66,14 +70,59 @@ class Program:
     stages: list
     flops: int = 0            # DFMA-equivalent cost of one evaluation (OP_COST model)
     n_transcendental: int = 0
+    tmp_nodes: frozenset = frozenset()   # DAG nodes that own a tmp slot
 
 
+_SPLIT_OPS = {ir.EXP, ir.LOG, ir.TANH, ir.SINH, ir.COSH, ir.SIN, ir.COS, ir.ASINH, ir.ATAN, ir.ERF, ir.ERFC, ir.LOG10, ir.POW}
 _TRANSCENDENTAL = {ir.EXP, ir.LOG, ir.TANH, ir.SINH, ir.COSH, ir.SIN, ir.COS, ir.ASINH, ir.ATAN,
                    ir.ERF, ir.ERFC, ir.LOG10, ir.POW, ir.SQRT, ir.HYPOT, ir.DIV, ir.RECIP}
 
 
-def build_program(g: ir.Graph, roots, name="f", out_index=None, n_out=None) -> Program:
+# Splitting of heavy, narrow templates (``split=True``): the electrode-kinetics rows of the DFN are two templates of 20
+# instances and ~500 DFMA-equivalents each -- fifteen transcendental calls in a row on 20 lanes of one warp while the
+# other seven warps of the team wait at the stage barrier (a third of the residual's critical path).  A second pass
+# materialises the transcendental nodes inside such templates: each becomes an instance of a small shared template
+# (``tanh(c0 * s0 + c1)`` x 60) in an earlier stage, spread over all the warps.
+SPLIT_TEMPLATE_COST = 100     # a template at least this costly ...
+SPLIT_TEMPLATE_INST = 64      # ... with at most this many instances is split
+
+
+def build_program(g: ir.Graph, roots, name="f", out_index=None, n_out=None, split=False) -> Program:
     """roots: node ids; root k is written to out[out_index[k]] (default k)."""
+    prog = _build_program(g, roots, name, out_index, n_out, frozenset())
+    if not split:
+        return prog
+    forced = set()
+    for _ in range(4):    # materialising a node exposes the (now shorter) templates around it: iterate to a fixed point
+        new = set()
+        for st in prog.stages:
+            for t in st.to_tmp + st.to_out:
+                if t.cost >= SPLIT_TEMPLATE_COST and t.n_inst <= SPLIT_TEMPLATE_INST:
+                    for top in t.tops:
+                        new |= _heavy_nodes(g, top, prog.tmp_nodes)
+        new -= forced
+        if not new:
+            break
+        forced |= new
+        prog = _build_program(g, roots, name, out_index, n_out, frozenset(forced))
+    return prog
+
+
+def _heavy_nodes(g, top, tmp_nodes):
+    """Transcendental nodes strictly inside the local DAG of ``top`` (down to leaves / materialised nodes)."""
+    out, seen, stack = set(), set(), [a for a in g.args(top)]
+    while stack:
+        x = stack.pop()
+        if x in seen or x in tmp_nodes or g.op[x] in ir.LEAF_OPS:
+            continue
+        seen.add(x)
+        if g.op[x] in _SPLIT_OPS:
+            out.add(x)
+        stack.extend(g.args(x))
+    return out
+
+
+def _build_program(g: ir.Graph, roots, name, out_index, n_out, forced) -> Program:
     roots = [int(r) for r in roots]
     if out_index is None:
         out_index = list(range(len(roots)))
@@ -112,7 +161,10 @@ def build_program(g: ir.Graph, roots, name="f", out_index=None, n_out=None) -> P
         n = int(n)
         o = owner[n]
         if op[n] not in ir.LEAF_OPS:
-            if o == MULTI:
+            if n in forced and not (o != MULTI and o[0] == 0 and roots[o[1]] == n):
+                materialised.add(n)
+                o = (1, n)
+            elif o == MULTI:
                 if tc[n] >= MATERIALISE_COST:
                     materialised.add(n)
                     o = (1, n)
@@ -130,7 +182,7 @@ def build_program(g: ir.Graph, roots, name="f", out_index=None, n_out=None) -> P
 
     # local DAG extraction ------------------------------------------------------
     shash = {}
-    H_S, H_C, H_T, H_J, H_M = 101, 102, 103, 104, 105
+    H_S, H_C, H_T, H_J, H_M, H_I = 101, 102, 103, 104, 105, 106
 
     def struct_hash(n):
         """Structure hash with leaves abstracted (deterministic: ints only)."""
@@ -148,7 +200,7 @@ def build_program(g: ir.Graph, roots, name="f", out_index=None, n_out=None) -> P
             elif o == ir.CONST:
                 shash[x] = H_C
             elif o == ir.INPUT:
-                shash[x] = hash((200, int(g.val[x])))
+                shash[x] = H_I if MERGE_INPUTS else hash((200, int(g.val[x])))
             elif o == ir.TIME:
                 shash[x] = H_T
             elif o == ir.CJ:
@@ -173,8 +225,8 @@ def build_program(g: ir.Graph, roots, name="f", out_index=None, n_out=None) -> P
         (it is expanded even though it has a tmp slot)."""
         local = {}
         body = []
-        s_list, c_list, m_list = [], [], []
-        s_slot, c_slot, m_slot = {}, {}, {}
+        s_list, c_list, m_list, i_list = [], [], [], []
+        s_slot, c_slot, m_slot, i_slot = {}, {}, {}, {}
 
         def leaf_ref(x):
             o = op[x]
@@ -195,7 +247,18 @@ def build_program(g: ir.Graph, roots, name="f", out_index=None, n_out=None) -> P
                     c_list.append(g.val[x])
                 return ("c", c_slot[x])
             if o == ir.INPUT:
-                return ("i", int(g.val[x]))
+                # a slot, not the index itself: the negative- and positive-electrode copies of an expression differ only in
+                # which input (diffusivity, ...) they read, and share one template this way
+                j = int(g.val[x])
+                if not MERGE_INPUTS:
+                    i_slot.setdefault(j, j)
+                    while len(i_list) <= j:
+                        i_list.append(len(i_list))
+                    return ("i", j)
+                if j not in i_slot:
+                    i_slot[j] = len(i_list)
+                    i_list.append(j)
+                return ("i", i_slot[j])
             if o == ir.TIME:
                 return ("t",)
             if o == ir.CJ:
@@ -226,7 +289,7 @@ def build_program(g: ir.Graph, roots, name="f", out_index=None, n_out=None) -> P
             body.append((op[x], refs))
         result = local[top]
         key = (tuple(body), result)
-        return key, body, result, s_list, c_list, m_list
+        return key, body, result, s_list, c_list, m_list, i_list
 
     # levels --------------------------------------------------------------------
     templates_tmp: dict = {}
@@ -234,7 +297,7 @@ def build_program(g: ir.Graph, roots, name="f", out_index=None, n_out=None) -> P
     level_of_tmp = {}
 
     def add(top, dest_index, to_tmp):
-        key, body, result, s_list, c_list, m_list = extract(top, to_tmp)
+        key, body, result, s_list, c_list, m_list, i_list = extract(top, to_tmp)
         lvl = 0
         for slot in m_list:
             lvl = max(lvl, level_of_tmp[slot] + 1)
@@ -243,12 +306,14 @@ def build_program(g: ir.Graph, roots, name="f", out_index=None, n_out=None) -> P
         t = store.get(tk)
         if t is None:
             cost = sum(ir.OP_COST[o] for o, _ in body)
-            t = Template(key, body, result, len(s_list), len(c_list), len(m_list), cost=cost)
+            t = Template(key, body, result, len(s_list), len(c_list), len(m_list), n_i=len(i_list), cost=cost)
             store[tk] = t
         t.out.append(dest_index)
+        t.tops.append(top)
         t.s_idx.append(s_list)
         t.c_val.append(c_list)
         t.m_idx.append(m_list)
+        t.i_idx.append(i_list)
         return lvl
 
     # materialised nodes in topological (id) order so dependencies have levels first
@@ -268,6 +333,7 @@ def build_program(g: ir.Graph, roots, name="f", out_index=None, n_out=None) -> P
         st.to_out.sort(key=lambda t: -t.cost * t.n_inst)
 
     prog = Program(name, n_out, len(mat_list), stages)
+    prog.tmp_nodes = frozenset(mat_list)
     for st in stages:
         for t in st.to_tmp + st.to_out:
             prog.flops += t.cost * t.n_inst
@@ -282,7 +348,7 @@ def run_program(prog: Program, t=0.0, y=None, p=None, cj=0.0):
     out = np.zeros(prog.n_out)
     tmp = np.zeros(max(prog.n_tmp, 1))
 
-    def val(ref, vals, s, c, m):
+    def val(ref, vals, s, c, m, ii):
         k = ref[0]
         if k == "v":
             return vals[ref[1]]
@@ -293,7 +359,7 @@ def run_program(prog: Program, t=0.0, y=None, p=None, cj=0.0):
         if k == "m":
             return tmp[m[ref[1]]]
         if k == "i":
-            return p[ref[1]]
+            return p[ii[ref[1]]]
         if k == "t":
             return t
         return cj
@@ -303,10 +369,10 @@ def run_program(prog: Program, t=0.0, y=None, p=None, cj=0.0):
             for dest, tl in ((tmp, st.to_tmp), (out, st.to_out)):
                 for tp in tl:
                     for q in range(tp.n_inst):
-                        s, c, m = tp.s_idx[q], tp.c_val[q], tp.m_idx[q]
+                        s, c, m, ii = tp.s_idx[q], tp.c_val[q], tp.m_idx[q], tp.i_idx[q]
                         vals = []
                         for o, refs in tp.body:
-                            a = [np.float64(val(r, vals, s, c, m)) for r in refs]
+                            a = [np.float64(val(r, vals, s, c, m, ii)) for r in refs]
                             if o == ir.SELECT:
                                 v = a[1] if a[0] != 0.0 else a[2]
                             elif o in ir._UNARY_NUMPY:
@@ -314,5 +380,5 @@ def run_program(prog: Program, t=0.0, y=None, p=None, cj=0.0):
                             else:
                                 v = ir._BINARY_NUMPY[o](a[0], a[1])
                             vals.append(np.float64(v))
-                        dest[tp.out[q]] = val(tp.result, vals, s, c, m)
+                        dest[tp.out[q]] = val(tp.result, vals, s, c, m, ii)
     return out

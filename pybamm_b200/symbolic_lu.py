@@ -1099,6 +1099,25 @@ def _walk(stream):
         off += 1 + nt * (1 + ml)
 
 
+def factor_chunks(stream, max_words):
+    """Pack consecutive whole records of the factor stream into chunks of at most ``max_words`` words.
+    Returns [(word offset, number of records), ...] or None when a single record does not fit."""
+    chunks, start, nrec, end = [], 0, 0, 0
+    for off, nt, ml, fl in _walk(stream):
+        size = 1 + nt * (1 + ml)
+        if size > max_words:
+            return None
+        if off + size - start > max_words:
+            chunks.append((start, nrec))
+            start, nrec = off, 0
+        nrec += 1
+        end = off + size
+    if nrec:
+        chunks.append((start, nrec))
+    assert end == len(stream)
+    return chunks
+
+
 def stream_factor(s: SymbolicLU, a_vals):
     """numpy emulation of the device factorisation driven by the packed stream (validation of the tables)."""
     lu = np.zeros(s.nnz_lu + 3)
