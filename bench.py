@@ -71,7 +71,7 @@ def workload_config(args, world):
         "output": "Voltage [V]",
         "sharding": f"batch rows over {world} rank(s), no collective",
         "l2": "flushed between timed steps (256 MiB write)",
-        "launch_order": "rows handed to the teams by descending cost proxy (|current|), results in row order",
+        "launch_order": "rows handed to the teams by descending predicted step count (log-linear fit on a previous solve), results in row order",
     }
 
 
@@ -282,12 +282,14 @@ def run_b200_arm(args):
     # launch order of the persistent kernel: expensive rows first (shard.launch_order; results stay in row order)
     from pybamm_b200.shard import launch_order
 
-    order = np.ascontiguousarray(launch_order(p, bundle.input_names), dtype=np.int32)
+    # the cost model is fitted on the step counts of one untimed solve of a 512-row sample (model-free: shard.CostModel)
+    solver.solve_arrays(T_EVAL, p[:512], t_interp=T_INTERP)
+    order = np.ascontiguousarray(launch_order(p, solver._cost_model), dtype=np.int32)
     if lib.pbgpu_solver_set_launch_order(solver._solver, order.ctypes.data_as(vp), n):
         raise RuntimeError(lib.pbgpu_last_error().decode())
 
     def launch():
-        rc = lib.pbgpu_solve_device(solver._solver, n, vp(d_te.data_ptr()), len(te), vp(d_ti.data_ptr()), len(ti), None,
+        rc = lib.pbgpu_solve_device(solver._solver, n, vp(d_te.data_ptr()), len(te), vp(d_ti.data_ptr()), len(ti), None, None,
                                     vp(d_p.data_ptr()), 1, C.byref(res), vp(stream.cuda_stream), 0)
         if rc:
             raise RuntimeError(lib.pbgpu_last_error().decode())
@@ -337,7 +339,7 @@ def run_b200_arm(args):
                     flush.zero_()
                     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                     e0.record(stream)
-                    if lib.pbgpu_solve_device(solver._solver, n, vp(d_te.data_ptr()), len(te), vp(d_ti.data_ptr()), len(ti), None,
+                    if lib.pbgpu_solve_device(solver._solver, n, vp(d_te.data_ptr()), len(te), vp(d_ti.data_ptr()), len(ti), None, None,
                                               vp(d_p.data_ptr()), 0, C.byref(resf), vp(stream.cuda_stream), 0):
                         raise RuntimeError(lib.pbgpu_last_error().decode())
                     e1.record(stream)

@@ -37,7 +37,7 @@ extern "C" {
 #endif
 
 #define PBGPU_QUEUE_WORDS (32 + 8 * 256)
-#define PBGPU_ABI_VERSION 3
+#define PBGPU_ABI_VERSION 4
 
 typedef struct pbgpu_model_s* pbgpu_model_t;
 typedef struct pbgpu_solver_s* pbgpu_solver_t;
@@ -77,6 +77,8 @@ typedef struct {
   int calc_ic;                                  /* 1 */
   double dt_init;                               /* 0 -> IDA heuristic */
   double dt_max;                                /* 0 -> unbounded */
+  int num_steps_no_progress;                    /* 0 (off); window of the NoProgressGuard (NoProgressGuard.hpp:12-66), <= 32 */
+  double t_no_progress;                         /* 0.0 (off); the window's steps must advance t by at least this much */
 } pbgpu_options;
 
 /* Caller-owned output block of one batch (host pointers for pbgpu_solve, device for pbgpu_solve_device). */
@@ -85,10 +87,16 @@ typedef struct {
   int n_ret;            /* row length: n_states (output_mode 0) or n_vars (output_mode 1) */
   double* t;            /* [n_sys][n_max]  */
   double* y;            /* [n_sys][n_max][n_ret], time-major rows like solution.y */
-  int* n_t;             /* [n_sys] number of stored time points */
+  int* n_t;             /* [n_sys] number of time points the system produced; only the first n_max are stored, so
+                           n_t > n_max means the block was too small (adaptive-step mode): re-solve with n_max >= n_t */
   int* flag;            /* [n_sys] IDA-style return code */
   double* y_term;       /* [n_sys][n_states] final state (y_event), may be NULL */
   long long* stats;     /* [n_sys][8]: nsteps nrevals nlinsetups netfails nniters nncfails njevals nge; may be NULL */
+  double* yp;           /* [n_sys][n_max][n_states] dy/dt at the stored points (solution.yp, Solution.hpp:9-39: the Hermite
+                           data of IDAKLUSolverOpenMP.inl:447-457), output_mode 0 only; may be NULL */
+  int* event_idx;       /* [n_sys] index of the termination event closest to zero at the final state when flag == 2
+                           (closest_event_idx, idaklu_solver.py:826-834), else -1; may be NULL */
+  double* t_event;      /* [n_sys] time of the last stored point (t_event of idaklu_solver.py:814); may be NULL */
   float kernel_ms;      /* out: device time of the integration kernel (CUDA events) */
   float total_ms;       /* out: device time including copies (pbgpu_solve only) */
 } pbgpu_result;
@@ -123,17 +131,21 @@ int pbgpu_result_capacity(int n_teval, int n_tinterp);
  *   t_eval   [n_teval]   sorted, unique, >= 2 entries (breakpoints; IDA stop times)
  *   t_interp [n_tinterp] sorted, unique, t_eval values removed (may be empty: n_tinterp = 0 -> adaptive steps stored)
  *   y0       [n_sys][n_states] or NULL (-> the model's initial conditions y0(p) evaluated on device)
+ *   yp0      [n_sys][n_states] or NULL: ydot0full of IDAKLUSolverGroup.solve.  Used as given only when calc_ic is off
+ *            (SetupInitialState, IDAKLUSolverOpenMP.inl:514-563); with calc_ic the derivatives are recomputed from the
+ *            consistent state (RecoverYp, :868-873), so NULL is the normal call
  *   inputs   [n_sys][n_inputs]
  */
 int pbgpu_solve(pbgpu_solver_t solver, int n_sys, const double* t_eval, int n_teval, const double* t_interp,
-                int n_tinterp, const double* y0, const double* inputs, int output_mode, pbgpu_result* out);
+                int n_tinterp, const double* y0, const double* yp0, const double* inputs, int output_mode,
+                pbgpu_result* out);
 
 /* Same, but every pointer (inputs and the result block's arrays) is device memory on the solver's
  * device; nothing is copied.  stream: a cudaStream_t (NULL = default stream).  Asynchronous unless
  * sync != 0; kernel_ms is only filled when sync != 0. */
 int pbgpu_solve_device(pbgpu_solver_t solver, int n_sys, const double* t_eval, int n_teval, const double* t_interp,
-                       int n_tinterp, const double* y0, const double* inputs, int output_mode, pbgpu_result* out,
-                       void* stream, int sync);
+                       int n_tinterp, const double* y0, const double* yp0, const double* inputs, int output_mode,
+                       pbgpu_result* out, void* stream, int sync);
 
 /* Evaluate generated model functions / the sparse LU on the device for n_sys (y, p) pairs (parity tests
  * of the code generator).  which: 0 res, 1 jac (bundle CSC order), 2 events, 3 ic, 4 vars,
@@ -152,6 +164,7 @@ typedef struct {
   const double* t_interp;
   const double* inputs;
   const double* y0;
+  const double* yp0;
   const double* atol;
   double* t_out;
   double* y_out;
@@ -159,6 +172,9 @@ typedef struct {
   int* flag;
   double* y_term;
   long long* stats;
+  double* yp_out;
+  int* event_idx;
+  double* t_event;
   unsigned int* queue;   /* [PBGPU_QUEUE_WORDS], zeroed before every launch: word 0 = next system to hand out; from word
                             32 on, 8 words per SM: the mailbox through which the two teams resident on one SM keep their
                             Newton iterations in phase (pbgpu_ida.cuh, pb_align) */

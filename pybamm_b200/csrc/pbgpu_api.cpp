@@ -31,8 +31,8 @@ int cuda_fail(const char* what, cudaError_t e) { return fail(std::string(what) +
   } while (0)
 
 typedef int (*describe_fn)(pbgpu_model_desc*);
-typedef int (*launch_fn)(const pbgpu_launch*, void*, int*, char*, size_t);
-typedef int (*eval_fn)(const pbgpu_eval_launch*, void*, char*, size_t);
+typedef int (*launch_fn)(const pbgpu_launch*, void*, int, char*, size_t);
+typedef int (*eval_fn)(const pbgpu_eval_launch*, void*, int, char*, size_t);
 typedef int (*plan_fn)(int, int*, char*, size_t);
 
 struct DevBuf {
@@ -72,7 +72,8 @@ struct pbgpu_solver_s {
   pbgpu_options opt;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-  DevBuf atol, t_eval, t_interp, inputs, y0, t_out, y_out, n_out, flag, y_term, stats, queue, scratch_a, scratch_b, team_scratch, order;
+  DevBuf atol, t_eval, t_interp, inputs, y0, yp0, t_out, y_out, yp_out, n_out, flag, y_term, stats, event_idx, t_event, queue,
+      scratch_a, scratch_b, team_scratch, order;
   int last_grid = 0;
   int order_n = 0;
 };
@@ -97,6 +98,8 @@ void pbgpu_default_options(pbgpu_options* o) {
   o->calc_ic = 1;
   o->dt_init = 0.0;
   o->dt_max = 0.0;
+  o->num_steps_no_progress = 0;
+  o->t_no_progress = 0.0;
 }
 
 int pbgpu_model_load(const char* path, pbgpu_model_t* model) {
@@ -138,10 +141,14 @@ int pbgpu_model_describe(pbgpu_model_t model, pbgpu_model_desc* desc) {
 
 int pbgpu_model_unload(pbgpu_model_t model) {
   if (!model) return 0;
-  // the image stays mapped (its kernels may still be registered with the CUDA runtime)
+  // The image registers its kernels with the CUDA runtime when it is mapped and unregisters them from a static
+  // destructor, so it can be unmapped once no solver uses it (the caller destroys its solvers first).
+  if (model->handle) dlclose(model->handle);
   delete model;
   return 0;
 }
+
+int pbgpu_solver_destroy(pbgpu_solver_t s);
 
 int pbgpu_solver_create(pbgpu_model_t model, const double* atol, const pbgpu_options* opt, int device,
                         pbgpu_solver_t* solver) {
@@ -164,23 +171,26 @@ int pbgpu_solver_create(pbgpu_model_t model, const double* atol, const pbgpu_opt
     delete s;
     return fail("pbgpu_solver_create: rtol must be non-negative");
   }
+  if (s->opt.num_steps_no_progress > 32) {
+    delete s;
+    return fail("pbgpu_solver_create: num_steps_no_progress is limited to 32 on this path");
+  }
   cudaError_t e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) {
     delete s;
     return cuda_fail("cudaStreamCreate", e);
   }
   for (int i = 0; i < 4; i++) cudaEventCreate(&s->ev[i]);
-  if (s->atol.ensure(sizeof(double) * model->desc.n_states)) {
-    delete s;
-    return 1;
+  int rc = s->atol.ensure(sizeof(double) * model->desc.n_states);
+  if (!rc) {
+    e = cudaMemcpy(s->atol.p, atol, sizeof(double) * model->desc.n_states, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) rc = cuda_fail("cudaMemcpy(atol)", e);
   }
-  e = cudaMemcpy(s->atol.p, atol, sizeof(double) * model->desc.n_states, cudaMemcpyHostToDevice);
-  if (e != cudaSuccess) {
-    delete s;
-    return cuda_fail("cudaMemcpy(atol)", e);
-  }
-  if (s->queue.ensure(sizeof(unsigned int) * PBGPU_QUEUE_WORDS)) {
-    delete s;
+  if (!rc) rc = s->queue.ensure(sizeof(unsigned int) * PBGPU_QUEUE_WORDS);
+  if (rc) {
+    const std::string msg = g_err;
+    pbgpu_solver_destroy(s);   // releases the stream, the events and whatever was allocated
+    g_err = msg;
     return 1;
   }
   *solver = s;
@@ -191,8 +201,9 @@ int pbgpu_solver_destroy(pbgpu_solver_t s) {
   if (!s) return 0;
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
-  DevBuf* bufs[] = {&s->atol, &s->t_eval, &s->t_interp, &s->inputs, &s->y0, &s->t_out, &s->y_out, &s->n_out,
-                    &s->flag, &s->y_term, &s->stats, &s->queue, &s->scratch_a, &s->scratch_b, &s->team_scratch, &s->order};
+  DevBuf* bufs[] = {&s->atol, &s->t_eval, &s->t_interp, &s->inputs, &s->y0, &s->yp0, &s->t_out, &s->y_out, &s->yp_out,
+                    &s->n_out, &s->flag, &s->y_term, &s->stats, &s->event_idx, &s->t_event, &s->queue, &s->scratch_a,
+                    &s->scratch_b, &s->team_scratch, &s->order};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 4; i++)
     if (s->ev[i]) cudaEventDestroy(s->ev[i]);
@@ -218,21 +229,32 @@ static int check_grids(const double* t_eval, int n_teval, const double* t_interp
   return 0;
 }
 
-// Per-team global scratch (streamed vectors of large models), sized for the grid the image will launch.
-static int ensure_team_scratch(pbgpu_solver_s* s, int n_sys) {
-  const long long per_team = s->model->desc.scratch_doubles_per_team;
-  if (per_team <= 0) return 0;
+// Plan the launch (teams on this device for n_sys systems) and size the per-team global scratch (streamed vectors of
+// large models) for exactly that grid.
+static int plan_launch(pbgpu_solver_s* s, int n_sys, int* teams) {
   char err[512];
   err[0] = 0;
-  int teams = 0;
-  if (s->model->plan(n_sys, &teams, err, sizeof(err))) return fail(err);
-  return s->team_scratch.ensure(sizeof(double) * (size_t)per_team * (size_t)teams);
+  if (s->model->plan(n_sys, teams, err, sizeof(err))) return fail(err);
+  const long long per_team = s->model->desc.scratch_doubles_per_team;
+  if (per_team <= 0) return 0;
+  return s->team_scratch.ensure(sizeof(double) * (size_t)per_team * (size_t)*teams);
 }
 
+struct DevResult {
+  double* t;
+  double* y;
+  double* yp;
+  int* n;
+  int* flag;
+  double* yterm;
+  long long* stats;
+  int* event_idx;
+  double* t_event;
+};
+
 static int launch_common(pbgpu_solver_s* s, int n_sys, const double* d_t_eval, int n_teval, const double* d_t_interp,
-                         int n_tinterp, const double* d_y0, const double* d_inputs, int output_mode, int n_max,
-                         double* d_t, double* d_y, int* d_n, int* d_flag, double* d_yterm, long long* d_stats,
-                         cudaStream_t stream) {
+                         int n_tinterp, const double* d_y0, const double* d_yp0, const double* d_inputs, int output_mode,
+                         int n_max, const DevResult& R, cudaStream_t stream) {
   const pbgpu_model_desc& D = s->model->desc;
   pbgpu_launch L;
   memset(&L, 0, sizeof(L));
@@ -246,28 +268,34 @@ static int launch_common(pbgpu_solver_s* s, int n_sys, const double* d_t_eval, i
   L.t_interp = d_t_interp;
   L.inputs = d_inputs;
   L.y0 = d_y0;
+  L.yp0 = d_yp0;
   L.atol = (const double*)s->atol.p;
-  L.t_out = d_t;
-  L.y_out = d_y;
-  L.n_out = d_n;
-  L.flag = d_flag;
-  L.y_term = d_yterm;
-  L.stats = d_stats;
+  L.t_out = R.t;
+  L.y_out = R.y;
+  L.yp_out = L.save_vars ? nullptr : R.yp;
+  L.n_out = R.n;
+  L.flag = R.flag;
+  L.y_term = R.yterm;
+  L.stats = R.stats;
+  L.event_idx = R.event_idx;
+  L.t_event = R.t_event;
   L.queue = (unsigned int*)s->queue.p;
-  if (ensure_team_scratch(s, n_sys)) return 1;
+  int teams = 0;
+  if (plan_launch(s, n_sys, &teams)) return 1;
   L.scratch = (double*)s->team_scratch.p;
   L.order = (s->order_n == n_sys && n_sys > 0) ? (const int*)s->order.p : nullptr;
   L.opt = s->opt;
   CK(cudaMemsetAsync(s->queue.p, 0, sizeof(unsigned int) * PBGPU_QUEUE_WORDS, stream));
   char err[512];
   err[0] = 0;
-  if (s->model->launch(&L, (void*)stream, &s->last_grid, err, sizeof(err))) return fail(err);
+  if (s->model->launch(&L, (void*)stream, teams, err, sizeof(err))) return fail(err);
+  s->last_grid = teams;
   return 0;
 }
 
 int pbgpu_solve_device(pbgpu_solver_t s, int n_sys, const double* t_eval, int n_teval, const double* t_interp,
-                       int n_tinterp, const double* y0, const double* inputs, int output_mode, pbgpu_result* out,
-                       void* stream, int sync) {
+                       int n_tinterp, const double* y0, const double* yp0, const double* inputs, int output_mode,
+                       pbgpu_result* out, void* stream, int sync) {
   if (!s || !out) return fail("pbgpu_solve_device: null argument");
   if (n_sys < 1) return fail("pbgpu_solve_device: n_sys must be positive");
   const pbgpu_model_desc& D = s->model->desc;
@@ -277,8 +305,8 @@ int pbgpu_solve_device(pbgpu_solver_t s, int n_sys, const double* t_eval, int n_
   CK(cudaSetDevice(s->device));
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
   if (sync) CK(cudaEventRecord(s->ev[0], st));
-  if (launch_common(s, n_sys, t_eval, n_teval, t_interp, n_tinterp, y0, inputs, output_mode, out->n_max, out->t, out->y,
-                    out->n_t, out->flag, out->y_term, out->stats, st))
+  const DevResult R = {out->t, out->y, out->yp, out->n_t, out->flag, out->y_term, out->stats, out->event_idx, out->t_event};
+  if (launch_common(s, n_sys, t_eval, n_teval, t_interp, n_tinterp, y0, yp0, inputs, output_mode, out->n_max, R, st))
     return 1;
   if (sync) {
     CK(cudaEventRecord(s->ev[1], st));
@@ -290,13 +318,14 @@ int pbgpu_solve_device(pbgpu_solver_t s, int n_sys, const double* t_eval, int n_
 }
 
 int pbgpu_solve(pbgpu_solver_t s, int n_sys, const double* t_eval, int n_teval, const double* t_interp, int n_tinterp,
-                const double* y0, const double* inputs, int output_mode, pbgpu_result* out) {
+                const double* y0, const double* yp0, const double* inputs, int output_mode, pbgpu_result* out) {
   if (!s || !out) return fail("pbgpu_solve: null argument");
   if (n_sys < 1) return fail("pbgpu_solve: n_sys must be positive");
   const pbgpu_model_desc& D = s->model->desc;
   if (check_grids(t_eval, n_teval, t_interp, n_tinterp)) return 1;
   if (output_mode != PBGPU_OUTPUT_STATES && output_mode != PBGPU_OUTPUT_VARS) return fail("invalid output_mode");
   if (output_mode == PBGPU_OUTPUT_VARS && D.n_vars < 1) return fail("the model image has no compiled output variables");
+  if (output_mode == PBGPU_OUTPUT_VARS && out->yp) return fail("yp is only stored with the full state (output_mode 0)");
   const int n_ret = output_mode == PBGPU_OUTPUT_VARS ? D.n_vars : D.n_states;
   if (out->n_ret != n_ret)
     return fail("result block has wrong row length. Expected " + std::to_string(n_ret) + " but got " + std::to_string(out->n_ret));
@@ -310,12 +339,16 @@ int pbgpu_solve(pbgpu_solver_t s, int n_sys, const double* t_eval, int n_teval, 
   if (s->t_interp.ensure(sizeof(double) * (n_tinterp > 0 ? n_tinterp : 1))) return 1;
   if (s->inputs.ensure(sizeof(double) * (size_t)n_sys * (D.n_inputs > 0 ? D.n_inputs : 1))) return 1;
   if (y0 && s->y0.ensure(sizeof(double) * n_sys * N)) return 1;
+  if (yp0 && s->yp0.ensure(sizeof(double) * n_sys * N)) return 1;
   if (s->t_out.ensure(sizeof(double) * n_sys * nm)) return 1;
   if (s->y_out.ensure(sizeof(double) * n_sys * nm * n_ret)) return 1;
+  if (out->yp && s->yp_out.ensure(sizeof(double) * n_sys * nm * N)) return 1;
   if (s->n_out.ensure(sizeof(int) * n_sys)) return 1;
   if (s->flag.ensure(sizeof(int) * n_sys)) return 1;
   if (out->y_term && s->y_term.ensure(sizeof(double) * n_sys * N)) return 1;
   if (out->stats && s->stats.ensure(sizeof(long long) * n_sys * 8)) return 1;
+  if (out->event_idx && s->event_idx.ensure(sizeof(int) * n_sys)) return 1;
+  if (out->t_event && s->t_event.ensure(sizeof(double) * n_sys)) return 1;
   cudaStream_t st = s->stream;
   CK(cudaEventRecord(s->ev[0], st));
   CK(cudaMemcpyAsync(s->t_eval.p, t_eval, sizeof(double) * n_teval, cudaMemcpyHostToDevice, st));
@@ -323,19 +356,26 @@ int pbgpu_solve(pbgpu_solver_t s, int n_sys, const double* t_eval, int n_teval, 
   if (D.n_inputs > 0)
     CK(cudaMemcpyAsync(s->inputs.p, inputs, sizeof(double) * (size_t)n_sys * D.n_inputs, cudaMemcpyHostToDevice, st));
   if (y0) CK(cudaMemcpyAsync(s->y0.p, y0, sizeof(double) * n_sys * N, cudaMemcpyHostToDevice, st));
+  if (yp0) CK(cudaMemcpyAsync(s->yp0.p, yp0, sizeof(double) * n_sys * N, cudaMemcpyHostToDevice, st));
   CK(cudaEventRecord(s->ev[1], st));
+  const DevResult R = {(double*)s->t_out.p, (double*)s->y_out.p, out->yp ? (double*)s->yp_out.p : nullptr, (int*)s->n_out.p,
+                       (int*)s->flag.p, out->y_term ? (double*)s->y_term.p : nullptr,
+                       out->stats ? (long long*)s->stats.p : nullptr, out->event_idx ? (int*)s->event_idx.p : nullptr,
+                       out->t_event ? (double*)s->t_event.p : nullptr};
   if (launch_common(s, n_sys, (const double*)s->t_eval.p, n_teval, n_tinterp > 0 ? (const double*)s->t_interp.p : nullptr,
-                    n_tinterp, y0 ? (const double*)s->y0.p : nullptr, (const double*)s->inputs.p, output_mode, out->n_max,
-                    (double*)s->t_out.p, (double*)s->y_out.p, (int*)s->n_out.p, (int*)s->flag.p,
-                    out->y_term ? (double*)s->y_term.p : nullptr, out->stats ? (long long*)s->stats.p : nullptr, st))
+                    n_tinterp, y0 ? (const double*)s->y0.p : nullptr, yp0 ? (const double*)s->yp0.p : nullptr,
+                    (const double*)s->inputs.p, output_mode, out->n_max, R, st))
     return 1;
   CK(cudaEventRecord(s->ev[2], st));
   CK(cudaMemcpyAsync(out->t, s->t_out.p, sizeof(double) * n_sys * nm, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(out->y, s->y_out.p, sizeof(double) * n_sys * nm * n_ret, cudaMemcpyDeviceToHost, st));
+  if (out->yp) CK(cudaMemcpyAsync(out->yp, s->yp_out.p, sizeof(double) * n_sys * nm * N, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(out->n_t, s->n_out.p, sizeof(int) * n_sys, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(out->flag, s->flag.p, sizeof(int) * n_sys, cudaMemcpyDeviceToHost, st));
   if (out->y_term) CK(cudaMemcpyAsync(out->y_term, s->y_term.p, sizeof(double) * n_sys * N, cudaMemcpyDeviceToHost, st));
   if (out->stats) CK(cudaMemcpyAsync(out->stats, s->stats.p, sizeof(long long) * n_sys * 8, cudaMemcpyDeviceToHost, st));
+  if (out->event_idx) CK(cudaMemcpyAsync(out->event_idx, s->event_idx.p, sizeof(int) * n_sys, cudaMemcpyDeviceToHost, st));
+  if (out->t_event) CK(cudaMemcpyAsync(out->t_event, s->t_event.p, sizeof(double) * n_sys, cudaMemcpyDeviceToHost, st));
   CK(cudaEventRecord(s->ev[3], st));
   cudaError_t e = cudaStreamSynchronize(st);
   if (e != cudaSuccess) return cuda_fail("integration kernel", e);
@@ -392,11 +432,12 @@ int pbgpu_model_eval(pbgpu_solver_t s, int which, int n_sys, const double* y, co
   E.t = t;
   E.cj = cj;
   E.out = (double*)s->scratch_b.p;
-  if (ensure_team_scratch(s, n_sys)) return 1;
+  int teams = 0;
+  if (plan_launch(s, n_sys, &teams)) return 1;
   E.scratch = (double*)s->team_scratch.p;
   char err[512];
   err[0] = 0;
-  if (s->model->eval(&E, (void*)st, err, sizeof(err))) return fail(err);
+  if (s->model->eval(&E, (void*)st, teams, err, sizeof(err))) return fail(err);
   CK(cudaMemcpyAsync(out, s->scratch_b.p, sizeof(double) * (size_t)n_sys * out_len, cudaMemcpyDeviceToHost, st));
   cudaError_t e = cudaStreamSynchronize(st);
   if (e != cudaSuccess) return cuda_fail("evaluation kernel", e);

@@ -79,7 +79,9 @@
 #define PB_OFF_COEF (PB_OFF_G + 3 * PB_NEV_PAD)
 #define PB_OFF_RED (PB_OFF_COEF + 32)
 #define PB_OFF_STATS (PB_OFF_RED + 64)
-#define PB_OFF_SLV (PB_OFF_STATS + 8)                          /* packed solve stream (u32 words) */
+#define PB_OFF_NPG (PB_OFF_STATS + 8)                          /* NoProgressGuard window: 32 step sizes + verdict */
+#define PB_NPG_MAX 32
+#define PB_OFF_SLV (PB_OFF_NPG + PB_NPG_MAX + 2)               /* packed solve stream (u32 words) */
 #define PB_OFF_FAC (PB_OFF_SLV + (PBM_SLV_ALLOC + 1) / 2)      /* packed factor stream when it fits (PBM_FAC_SMEM) */
 #if PBM_FAC_SMEM
 #define PB_OFF_END0 (PB_OFF_FAC + (PBM_FAC_WORDS + 1) / 2)
@@ -152,6 +154,7 @@ struct pb_sys {
 #define S_SIGMA(S) ((S).sm + PB_OFF_COEF + 18)
 #define S_GAMMA(S) ((S).sm + PB_OFF_COEF + 24)
 #define S_STATS(S) ((S).sm + PB_OFF_STATS)
+#define S_NPG(S) ((S).sm + PB_OFF_NPG)
 
 #ifndef PB_PROFILE
 #define PB_STAT(S, k)                        \
@@ -1914,10 +1917,16 @@ static PB_DEV double pb_perturb_time(double t) {
   return (1.0 + delta) * t + delta;
 }
 
+// Store the solution at time t (a point inside the last step) as output point *i_save.  Points beyond the block's
+// capacity are counted but not stored: n_t > n_max tells the host that the block was too small (the reference grows
+// its arrays without bound, ExtendAdaptiveArrays, IDAKLUSolverOpenMP.inl:608-612; the host re-solves with n_max = n_t).
 static PB_DEV void pb_store_point(pb_sys& S, const pbgpu_launch& L, int sys, double t, int* i_save, double* t_last) {
-  if (*i_save >= L.n_max) return;
-  PB_T0(to_);
   *t_last = t;
+  if (*i_save >= L.n_max) {
+    (*i_save)++;
+    return;
+  }
+  PB_T0(to_);
   const size_t slot = (size_t)sys * L.n_max + *i_save;
   double* row = L.y_out + slot * L.n_ret;
   if (L.save_vars) {
@@ -1927,6 +1936,10 @@ static PB_DEV void pb_store_point(pb_sys& S, const pbgpu_launch& L, int sys, dou
     pbm_vars(S_YY(S), S_P(S), t, 0.0, row, S_TMP(S));
     PB_SYNC();
 #endif
+  } else if (L.yp_out) {
+    // Hermite data: y and dy/dt from the same interpolating polynomial (IDAGetDky k = 0, 1; save_hermite,
+    // IDAKLUSolverOpenMP.inl:432-435, 447-457)
+    pb_get_solution2(S, t, row, L.yp_out + slot * PBM_N);
   } else {
     pb_get_solution(S, t, row);
   }
@@ -1950,6 +1963,24 @@ static PB_DEV void pb_solve_system(pb_sys& S, const pbgpu_launch& L, int sys) {
   }
   PB_SYNC();
   pb_consistent_init(S, t0, L.opt.calc_ic);
+  if (L.yp0 && !L.opt.calc_ic) {
+    // calc_ic off: the caller's derivatives are used as given (SetupInitialState, IDAKLUSolverOpenMP.inl:514-563)
+    double* phi1 = S_PHI(S, 1);
+    for (int i = PB_TID; i < PBM_N; i += PB_TEAM) phi1[i] = L.yp0[(size_t)sys * PBM_N + i];
+    PB_SYNC();
+  }
+  // NoProgressGuard (NoProgressGuard.hpp:12-66): thread 0 keeps a window of the last step sizes, initialised with the
+  // threshold so that it cannot trip before the window is full; the verdict travels through shared memory
+  const int npg_n = (L.opt.t_no_progress != 0.0) ? L.opt.num_steps_no_progress : 0;
+  int npg_idx = 0;
+  if (npg_n > 0) {
+    if (PB_TID == 0) {
+      for (int k = 0; k < npg_n; k++) S_NPG(S)[k] = L.opt.t_no_progress;
+      S_NPG(S)[PB_NPG_MAX] = 0.0;
+    }
+    PB_SYNC();
+  }
+  int ev_idx = -1;
   int i_save = 0, i_eval = 1, i_interp = 0;
   double t_eval_next = PB_LDU(L.t_eval[1]);
   S.tstop = t_eval_next;
@@ -1962,7 +1993,17 @@ static PB_DEV void pb_solve_system(pb_sys& S, const pbgpu_launch& L, int sys) {
     double* g = S_GHI(S);
     pb_gfun(S, t0, S_PHI(S, 0), g);
     int trig = 0;
-    for (int i = 0; i < PBM_NEV; i++) trig |= (g[i] <= 0.0);
+    {
+      double best = PB_INF;
+      for (int i = 0; i < PBM_NEV; i++) {
+        trig |= (g[i] <= 0.0);
+        if (fabs(g[i]) < best) {
+          best = fabs(g[i]);
+          ev_idx = i;
+        }
+      }
+      if (!trig) ev_idx = -1;
+    }
     PB_SYNC();
     if (trig) {
       // IDA has not stepped: psi is not set, store phi[0] directly
@@ -1976,11 +2017,15 @@ static PB_DEV void pb_solve_system(pb_sys& S, const pbgpu_launch& L, int sys) {
 #endif
         } else {
           const double* phi0 = S_PHI(S, 0);
-          for (int i = PB_TID; i < PBM_N; i += PB_TEAM) row[i] = phi0[i];
+          const double* phi1 = S_PHI(S, 1);
+          for (int i = PB_TID; i < PBM_N; i += PB_TEAM) {
+            row[i] = phi0[i];
+            if (L.yp_out) L.yp_out[slot * PBM_N + i] = phi1[i];
+          }
         }
         if (PB_TID == 0) L.t_out[slot] = t0;
-        i_save = 1;
       }
+      i_save = 1;
       retval = PB_IDA_ROOT_RETURN;
       done = 1;
       if (L.y_term) {
@@ -1994,9 +2039,33 @@ static PB_DEV void pb_solve_system(pb_sys& S, const pbgpu_launch& L, int sys) {
     retval = pb_ida_solve_one_step(S, tf_perturbed, &t_val);
     if (retval >= 0) pb_store_point(S, L, sys, t0, &i_save, &t_last);
     long long guard = 0;
+    if (npg_n > 0) {
+      if (PB_TID == 0) {
+        S_NPG(S)[0] = t_val - t0;
+        npg_idx = 1 % npg_n;
+      }
+    }
     for (;;) {
       if (retval < 0) break;
-      if (t_prev == t_val) {
+      int stalled = 0;
+      if (npg_n > 0) {
+        PB_SYNC();
+        if (PB_TID == 0) {
+          double sum = 0.0;
+          int viol = 1;
+          for (int k = 0; k < npg_n; k++) {
+            sum += S_NPG(S)[k];
+            if (sum >= L.opt.t_no_progress) {
+              viol = 0;
+              break;
+            }
+          }
+          S_NPG(S)[PB_NPG_MAX] = viol ? 1.0 : 0.0;
+        }
+        PB_SYNC();
+        stalled = S_NPG(S)[PB_NPG_MAX] != 0.0;
+      }
+      if (t_prev == t_val || stalled) {
         retval = PB_IDA_ERR_FAIL;
         break;
       }
@@ -2033,6 +2102,13 @@ static PB_DEV void pb_solve_system(pb_sys& S, const pbgpu_launch& L, int sys) {
         pb_consistent_init(S, t_val, 1);
         S.tstop = t_eval_next;
         S.tstopset = 1;
+        if (npg_n > 0) {   // HandleBreakpoint re-initialises the guard
+          PB_SYNC();
+          if (PB_TID == 0) {
+            for (int k = 0; k < npg_n; k++) S_NPG(S)[k] = L.opt.t_no_progress;
+            npg_idx = 0;
+          }
+        }
       }
       t_prev = t_val;
       if (++guard > S.max_num_steps) {
@@ -2040,7 +2116,26 @@ static PB_DEV void pb_solve_system(pb_sys& S, const pbgpu_launch& L, int sys) {
         break;
       }
       retval = pb_ida_solve_one_step(S, tf_perturbed, &t_val);
+      if (npg_n > 0 && PB_TID == 0) {
+        S_NPG(S)[npg_idx] = t_val - t_prev;
+        npg_idx = (npg_idx + 1) % npg_n;
+      }
     }
+#if PBM_NEV > 0
+    if (retval == PB_IDA_ROOT_RETURN) {
+      // which event ended the run: the one closest to zero at the root (closest_event_idx, idaklu_solver.py:826-834);
+      // S_GROUT holds g(t_root, y(t_root)) of the root finder
+      const double* gr = S_GROUT(S);
+      double best = PB_INF;
+      for (int i = 0; i < PBM_NEV; i++) {
+        const double a = fabs(gr[i]);
+        if (a < best) {
+          best = a;
+          ev_idx = i;
+        }
+      }
+    }
+#endif
     if (L.y_term) {
       PB_SYNC();
       if (S.nst > 0 || S.kused > 0) pb_get_solution(S, t_val, L.y_term + (size_t)sys * PBM_N);
@@ -2054,6 +2149,8 @@ static PB_DEV void pb_solve_system(pb_sys& S, const pbgpu_launch& L, int sys) {
   if (PB_TID == 0) {
     L.n_out[sys] = i_save;
     L.flag[sys] = retval;
+    if (L.event_idx) L.event_idx[sys] = (retval == PB_IDA_ROOT_RETURN) ? ev_idx : -1;
+    if (L.t_event) L.t_event[sys] = t_last;
     if (L.stats)
       for (int k = 0; k < 8; k++) L.stats[(size_t)sys * 8 + k] = (long long)S_STATS(S)[k];
   }

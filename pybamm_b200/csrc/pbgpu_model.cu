@@ -183,17 +183,27 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_e
   }
 }
 
-static int g_configured_device = -1;
-static int g_blocks_per_sm = 0, g_num_sms = 0;
+// Launch configuration per device ordinal: the multi-device path runs one host thread per device through the same
+// image, so nothing here may be a single file-scope value.
+#include <mutex>
+struct pb_dev_cfg {
+  int ready, blocks_per_sm, num_sms;
+};
+static pb_dev_cfg g_cfg[64];
+static std::mutex g_cfg_mutex;
 
-static int pb_configure(char* err, size_t errlen) {
+static int pb_configure(pb_dev_cfg* out, char* err, size_t errlen) {
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess) {
-    snprintf(err, errlen, "cudaGetDevice: %s", cudaGetErrorString(e));
+  if (e != cudaSuccess || dev < 0 || dev >= 64) {
+    snprintf(err, errlen, "cudaGetDevice: %s", e != cudaSuccess ? cudaGetErrorString(e) : "ordinal out of range");
     return 1;
   }
-  if (dev == g_configured_device) return 0;
+  std::lock_guard<std::mutex> lock(g_cfg_mutex);
+  if (g_cfg[dev].ready) {
+    *out = g_cfg[dev];
+    return 0;
+  }
   e = cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
@@ -204,7 +214,8 @@ static int pb_configure(char* err, size_t errlen) {
   }
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, dev);
-  g_num_sms = prop.multiProcessorCount;
+  pb_dev_cfg c;
+  c.num_sms = prop.multiProcessorCount;
   // Shared-memory carve-out.  The integration is latency-bound (dependent shared-memory round trips in the
   // triangular solves), so resident teams per SM is what buys throughput: large teams (> 48 KB: DFN) take all the
   // shared memory they can use; small ones (SPM / SPMe: one warp per system, the CTA-per-SM limit binds first) leave
@@ -216,26 +227,28 @@ static int pb_configure(char* err, size_t errlen) {
   if (carve_kb > 227) carve_kb = 227;
   const int total_kb = (int)(prop.sharedMemPerMultiprocessor / 1024);
   e = cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_blocks_per_sm, pbgpu_solve_kernel, PB_TEAM_SIZE, PB_SMEM_BYTES);
-  if (e != cudaSuccess || g_blocks_per_sm < 1) {
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c.blocks_per_sm, pbgpu_solve_kernel, PB_TEAM_SIZE, PB_SMEM_BYTES);
+  if (e != cudaSuccess || c.blocks_per_sm < 1) {
     snprintf(err, errlen, "occupancy query failed for model '%s': %s", PBM_NAME, cudaGetErrorString(e));
     return 1;
   }
   int by_carve = carve_kb * 1024 / per_team;
   if (by_carve < 1) by_carve = 1;
-  if (g_blocks_per_sm > by_carve) g_blocks_per_sm = by_carve;
+  if (c.blocks_per_sm > by_carve) c.blocks_per_sm = by_carve;
   if (const char* env = getenv("PBGPU_TEAMS_PER_SM")) {
     const int v = atoi(env);
-    if (v >= 1 && v < g_blocks_per_sm) g_blocks_per_sm = v;
+    if (v >= 1 && v < c.blocks_per_sm) c.blocks_per_sm = v;
   }
   // give the rest back to L1: carve out exactly what the resident teams use
-  int use_kb = (g_blocks_per_sm * per_team + 1023) / 1024;
+  int use_kb = (c.blocks_per_sm * per_team + 1023) / 1024;
   if (use_kb > carve_kb) use_kb = carve_kb;
   int pct = (use_kb * 100 + total_kb - 1) / total_kb;
   if (pct > 100) pct = 100;
   cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-  g_configured_device = dev;
+  c.ready = 1;
+  g_cfg[dev] = c;
+  *out = c;
   return 0;
 }
 
@@ -266,37 +279,43 @@ extern "C" int pbgpu_image_describe(pbgpu_model_desc* d) {
   return 0;
 }
 
-// Teams a launch for n_sys systems will use on the current device (the solver handle sizes its scratch block with it).
+// Teams a launch for n_sys systems will use on the current device (the solver handle sizes its scratch block with it
+// and passes the same number back to pbgpu_image_launch / pbgpu_image_eval).
 extern "C" int pbgpu_image_plan(int n_sys, int* teams, char* err, size_t errlen) {
-  if (pb_configure(err, errlen)) return 1;
-  int grid = g_blocks_per_sm * g_num_sms;
+  pb_dev_cfg c;
+  if (pb_configure(&c, err, errlen)) return 1;
+  int grid = c.blocks_per_sm * c.num_sms;
   if (n_sys > 0 && grid > n_sys) grid = n_sys;
   if (grid < 1) grid = 1;
   *teams = grid;
   return 0;
 }
 
-// All pointers in L are device pointers on the current device. grid_out: teams launched.
-extern "C" int pbgpu_image_launch(const pbgpu_launch* L, void* stream, int* grid_out, char* err, size_t errlen) {
-  if (pb_configure(err, errlen)) return 1;
-  int grid = g_blocks_per_sm * g_num_sms;
-  if (grid > L->n_sys) grid = L->n_sys;
-  if (grid < 1) grid = 1;
+// All pointers in L are device pointers on the current device.  grid: the number of teams pbgpu_image_plan returned
+// for this n_sys (the caller's scratch block holds exactly that many team slots).
+extern "C" int pbgpu_image_launch(const pbgpu_launch* L, void* stream, int grid, char* err, size_t errlen) {
+  pb_dev_cfg c;
+  if (pb_configure(&c, err, errlen)) return 1;
+  if (grid < 1 || grid > c.blocks_per_sm * c.num_sms) {
+    snprintf(err, errlen, "pbgpu_image_launch: grid %d was not planned for this device", grid);
+    return 1;
+  }
   pbgpu_solve_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*L);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     snprintf(err, errlen, "pbgpu_solve_kernel launch: %s", cudaGetErrorString(e));
     return 1;
   }
-  if (grid_out) *grid_out = grid;
   return 0;
 }
 
-extern "C" int pbgpu_image_eval(const pbgpu_eval_launch* E, void* stream, char* err, size_t errlen) {
-  if (pb_configure(err, errlen)) return 1;
-  int grid = g_blocks_per_sm * g_num_sms;
-  if (grid > E->n_sys) grid = E->n_sys;
-  if (grid < 1) grid = 1;
+extern "C" int pbgpu_image_eval(const pbgpu_eval_launch* E, void* stream, int grid, char* err, size_t errlen) {
+  pb_dev_cfg c;
+  if (pb_configure(&c, err, errlen)) return 1;
+  if (grid < 1 || grid > c.blocks_per_sm * c.num_sms) {
+    snprintf(err, errlen, "pbgpu_image_eval: grid %d was not planned for this device", grid);
+    return 1;
+  }
   pbgpu_eval_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*E);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {

@@ -28,6 +28,8 @@ class Options(C.Structure):
         ("calc_ic", C.c_int),
         ("dt_init", C.c_double),
         ("dt_max", C.c_double),
+        ("num_steps_no_progress", C.c_int),
+        ("t_no_progress", C.c_double),
     ]
 
 
@@ -43,8 +45,8 @@ class ModelDesc(C.Structure):
 class Result(C.Structure):
     _fields_ = [
         ("n_max", C.c_int), ("n_ret", C.c_int), ("t", C.c_void_p), ("y", C.c_void_p), ("n_t", C.c_void_p),
-        ("flag", C.c_void_p), ("y_term", C.c_void_p), ("stats", C.c_void_p), ("kernel_ms", C.c_float),
-        ("total_ms", C.c_float),
+        ("flag", C.c_void_p), ("y_term", C.c_void_p), ("stats", C.c_void_p), ("yp", C.c_void_p),
+        ("event_idx", C.c_void_p), ("t_event", C.c_void_p), ("kernel_ms", C.c_float), ("total_ms", C.c_float),
     ]
 
 
@@ -52,8 +54,9 @@ class LaunchArgs(C.Structure):
     _fields_ = [
         ("n_sys", C.c_int), ("n_eval", C.c_int), ("n_interp", C.c_int), ("n_max", C.c_int), ("save_vars", C.c_int),
         ("n_ret", C.c_int), ("t_eval", C.c_void_p), ("t_interp", C.c_void_p), ("inputs", C.c_void_p),
-        ("y0", C.c_void_p), ("atol", C.c_void_p), ("t_out", C.c_void_p), ("y_out", C.c_void_p),
+        ("y0", C.c_void_p), ("yp0", C.c_void_p), ("atol", C.c_void_p), ("t_out", C.c_void_p), ("y_out", C.c_void_p),
         ("n_out", C.c_void_p), ("flag", C.c_void_p), ("y_term", C.c_void_p), ("stats", C.c_void_p),
+        ("yp_out", C.c_void_p), ("event_idx", C.c_void_p), ("t_event", C.c_void_p),
         ("queue", C.c_void_p), ("scratch", C.c_void_p), ("order", C.c_void_p), ("opt", Options),
     ]
 
@@ -64,6 +67,7 @@ OPTION_DEFAULTS = dict(
     max_convergence_failures=100, nonlinear_convergence_coefficient=0.33,
     nonlinear_convergence_coefficient_ic=0.0033, newton_step_tol=1e-4, max_num_iterations_ic=100,
     max_linesearch_backtracks_ic=5, linear_solution_scaling=True, calc_ic=True, dt_init=0.0, dt_max=0.0,
+    num_steps_no_progress=0, t_no_progress=0.0,
 )
 
 

@@ -12,23 +12,55 @@ from __future__ import annotations
 import numpy as np
 
 
-def cost_proxy(inputs: np.ndarray, input_names=None) -> np.ndarray:
-    """Expected work per system.  Measured on the DFN bench (10 000 sets, 2.5-7.5 A): the step count GROWS with the
-    current (correlation +0.55; 371 to 4 030 steps around a mean of 731) -- a fast discharge ends on the steep knee of the
-    voltage curve, where the step size collapses, while a slow one just runs to the final time.  Falls back to uniform
-    cost when the model has no current input."""
+class CostModel:
+    """Model-free predictor of the work of a system from its inputs: a least-squares fit of log(steps) on the logs
+    of the input magnitudes, learned from the step counts of the previous solve of the same solver (``stats[:, 0]``).
+    It only has to rank systems (launch order, shard balance), so a crude fit is enough: on the DFN bench the step
+    count correlates +0.55 with the current alone (a fast discharge ends on the steep knee of the voltage curve)."""
+
+    def __init__(self):
+        self.coef = None
+
+    @staticmethod
+    def _features(inputs):
+        x = np.asarray(inputs, dtype=np.float64)
+        f = np.log(np.abs(x) + 1e-300)
+        f = np.where(np.isfinite(f), f, 0.0)
+        return np.column_stack([np.ones(len(x)), f])
+
+    def fit(self, inputs, steps):
+        steps = np.asarray(steps, dtype=np.float64).reshape(-1)
+        inputs = np.asarray(inputs, dtype=np.float64)
+        if inputs.ndim != 2 or len(steps) != len(inputs) or len(steps) < 4 * (inputs.shape[1] + 1) or inputs.shape[1] == 0:
+            return
+        A = self._features(inputs)
+        ok = steps > 0
+        if ok.sum() < A.shape[1] + 1:
+            return
+        self.coef, *_ = np.linalg.lstsq(A[ok], np.log(steps[ok]), rcond=None)
+        self.n_inputs = inputs.shape[1]
+
+    def predict(self, inputs):
+        inputs = np.asarray(inputs, dtype=np.float64)
+        if self.coef is None or inputs.ndim != 2 or inputs.shape[1] != self.n_inputs:
+            return None
+        return np.exp(np.clip(self._features(inputs) @ self.coef, -50.0, 50.0))
+
+
+def cost_proxy(inputs: np.ndarray, model: CostModel | None = None) -> np.ndarray:
+    """Expected work per system: the fitted cost model of previous solves when there is one, else uniform."""
     inputs = np.asarray(inputs, dtype=np.float64)
-    n = inputs.shape[0]
-    if input_names is not None and "Current function [A]" in input_names and inputs.shape[1]:
-        cur = np.abs(inputs[:, list(input_names).index("Current function [A]")])
-        return np.where(np.isfinite(cur), cur, 0.0)
-    return np.ones(n)
+    if model is not None:
+        c = model.predict(inputs)
+        if c is not None:
+            return c
+    return np.ones(inputs.shape[0])
 
 
-def launch_order(inputs: np.ndarray, input_names=None) -> np.ndarray:
+def launch_order(inputs: np.ndarray, model: CostModel | None = None) -> np.ndarray:
     """Row order for one device: most expensive systems first, so that the persistent kernel's teams do not end the
     batch waiting for one long straggler (the queue hands out rows in index order)."""
-    return np.argsort(-cost_proxy(inputs, input_names), kind="stable")
+    return np.argsort(-cost_proxy(inputs, model), kind="stable")
 
 
 def partition(n_sys: int, n_shards: int, cost=None):

@@ -8,8 +8,8 @@ call per batch, inputs ``(n_sys, n_p)`` ordered by sorted input name, results pe
 of ``include/pbgpu.h`` with ctypes.  There is no CPU fallback: constructing the solver without a
 usable GPU (or without the compiled libraries) raises ``SolverError``.
 
-``pybamm_b200.idaklu_solver.IDAKLUSolver`` wraps this class behind ``pybamm.BaseSolver`` where pybamm
-is importable.
+``pybamm_b200.idaklu_solver.IDAKLUSolver`` (a ``pybamm.BaseSolver`` subclass, importable where pybamm is)
+drives this class from ``solve(model, t_eval, inputs=[...])`` and returns ``pybamm.Solution`` objects.
 """
 from __future__ import annotations
 
@@ -54,7 +54,8 @@ class Solution:
     time-major block), ``t_event``, ``y_event``, ``termination``.
     """
 
-    __slots__ = ("t", "_rows", "all_inputs", "flag", "y_event", "_stats", "_variables", "closest_event_idx", "termination")
+    __slots__ = ("t", "_rows", "all_inputs", "flag", "y_event", "_stats", "_variables", "closest_event_idx", "termination",
+                 "_yp_rows")
 
     def __init__(self, t, y_rows, inputs, flag, y_term, stats, variables, event_names, closest_event_idx):
         # cheap on purpose: a batch builds ten thousand of these; everything derivable is a property
@@ -66,6 +67,7 @@ class Solution:
         self._stats = stats
         self._variables = variables
         self.closest_event_idx = closest_event_idx
+        self._yp_rows = None
         if flag == IDA_ROOT_RETURN:
             self.termination = "event: " + (event_names[closest_event_idx] if closest_event_idx is not None else "?")
         elif flag >= 0:
@@ -76,6 +78,11 @@ class Solution:
     @property
     def t_event(self):
         return np.array([self.t[-1]]) if len(self.t) else np.array([])
+
+    @property
+    def yp(self):
+        """dy/dt at the stored points, shape (n_states, n_t) (all_yps of idaklu_solver.py:819), or None."""
+        return None if self._yp_rows is None else self._yp_rows.T
 
     @property
     def stats(self):
@@ -132,8 +139,8 @@ class _Lib:
             lib.pbgpu_solver_create.argtypes = [vp, vp, C.POINTER(Options), C.c_int, C.POINTER(vp)]
             lib.pbgpu_solver_destroy.argtypes = [vp]
             lib.pbgpu_result_capacity.argtypes = [C.c_int, C.c_int]
-            lib.pbgpu_solve.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int, vp, vp, C.c_int, C.POINTER(Result)]
-            lib.pbgpu_solve_device.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int, vp, vp, C.c_int,
+            lib.pbgpu_solve.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int, vp, vp, vp, C.c_int, C.POINTER(Result)]
+            lib.pbgpu_solve_device.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int, vp, vp, vp, C.c_int,
                                                C.POINTER(Result), vp, C.c_int]
             lib.pbgpu_model_eval.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_double, C.c_double, vp, vp, C.c_int]
             cls._inst = lib
@@ -160,9 +167,13 @@ class BatchedIDASolver:
     IGNORED_OPTIONS = {"print_stats", "compile", "jacobian", "preconditioner", "precon_half_bandwidth",
                        "precon_half_bandwidth_keep", "num_threads", "num_solvers", "linear_solver",
                        "linsol_max_iterations", "epsilon_linear_tolerance", "increment_factor",
-                       "silence_sundials_errors", "suppress_algebraic_error", "hermite_interpolation",
+                       "silence_sundials_errors", "suppress_algebraic_error",
                        "hermite_reduction_factor", "max_num_steps_ic", "max_num_jacobians_ic", "linesearch_off_ic",
-                       "init_all_y_ic", "newton_mode", "num_steps_no_progress", "t_no_progress", "dt_min"}
+                       "init_all_y_ic", "newton_mode", "dt_min"}
+    # options of this front end itself: hermite_interpolation (store dy/dt with the adaptive steps, idaklu_solver.py:318),
+    # max_saved_steps (first guess of the adaptive-step capacity; the block is re-sized and the affected rows re-solved
+    # when a system takes more steps: the reference grows its arrays instead, IDAKLUSolverOpenMP.inl:608-612)
+    FRONT_END_OPTIONS = {"hermite_interpolation": True, "max_saved_steps": 4096}
 
     def __init__(self, model, rtol=1e-4, atol=1e-6, options=None, output_variables=None, device=0,
                  on_failure="warn", image_path=None, devices=None, reuse_buffers=False):
@@ -177,11 +188,14 @@ class BatchedIDASolver:
             if v not in self.bundle.variables:
                 raise SolverError(f"output variable '{v}' is not compiled into model bundle '{self.bundle.name}'")
         options = dict(options or {})
-        unknown = [k for k in options if k not in OPTION_DEFAULTS and k not in self.IGNORED_OPTIONS]
+        unknown = [k for k in options if k not in OPTION_DEFAULTS and k not in self.IGNORED_OPTIONS
+                   and k not in self.FRONT_END_OPTIONS]
         if unknown:
             raise SolverError(f"unknown IDAKLU option(s): {unknown}")
         if options.get("num_solvers", 1) > options.get("num_threads", options.get("num_solvers", 1)):
             raise SolverError("Number of solvers must be less than or equal to the number of threads")
+        if int(options.get("num_steps_no_progress", 0)) > 32:
+            raise SolverError("num_steps_no_progress is limited to 32 on this path")
         self.options = options
         # devices: CUDA ordinals the batch is sharded over inside this process (one solver handle and one host
         # thread per device, no collective: SURVEY.md section 8e).  Default: the single ordinal ``device``.
@@ -198,6 +212,9 @@ class BatchedIDASolver:
         self.desc = None
         self.last_kernel_ms = None
         self.last_total_ms = None
+        from .shard import CostModel
+
+        self._cost_model = CostModel()
 
     # -- native handles ---------------------------------------------------------------------
     def _ensure(self):
@@ -252,9 +269,16 @@ class BatchedIDASolver:
         d["_pinned"] = {}
         return d
 
+    def __setstate__(self, d):
+        self.__dict__.update(d)
+
     # -- batch solve --------------------------------------------------------------------------
-    def solve_arrays(self, t_eval, inputs, t_interp=None, y0=None, output_mode=None, want_stats=True):
-        """Array-level entry: returns dict(t, y, n_t, flag, y_term, stats) of padded arrays."""
+    def solve_arrays(self, t_eval, inputs, t_interp=None, y0=None, output_mode=None, want_stats=True, yp0=None,
+                     want_yp=None):
+        """Array-level entry: returns dict(t, y, yp, n_t, flag, y_term, stats, event_idx, t_event) of padded arrays.
+
+        ``want_yp``: also return dy/dt at the stored points (full-state mode only).  Default: the reference's rule
+        ``hermite_interpolation and adaptive steps and not output_variables`` (save_hermite, IDAKLUSolverOpenMP.inl:447-457)."""
         self._ensure()
         lib, D = self._lib, self.desc
         try:
@@ -268,24 +292,68 @@ class BatchedIDASolver:
         if inputs.shape[1] != D.n_inputs:
             raise SolverError(f"inputs has wrong number of cols. Expected {D.n_inputs} but got {inputs.shape[1]}")
         inputs = np.ascontiguousarray(inputs)
-        if y0 is not None:
-            y0 = np.asarray(y0, dtype=np.float64)
-            if y0.ndim != 2:
-                raise SolverError(f"y0 has wrong number of dimensions. Expected 2 but got {y0.ndim}")
-            if y0.shape[1] != D.n_states:
-                raise SolverError(f"y0 has wrong number of cols. Expected {D.n_states} but got {y0.shape[1]}")
-            if y0.shape[0] != n_sys:
-                raise SolverError(f"y0 has wrong number of rows. Expected {n_sys} but got {y0.shape[0]}")
-            y0 = np.ascontiguousarray(y0)
+
+        def state_block(a, what):
+            if a is None:
+                return None
+            a = np.asarray(a, dtype=np.float64)
+            if a.ndim != 2:
+                raise SolverError(f"{what} has wrong number of dimensions. Expected 2 but got {a.ndim}")
+            if a.shape[1] != D.n_states:
+                raise SolverError(f"{what} has wrong number of cols. Expected {D.n_states} but got {a.shape[1]}")
+            if a.shape[0] != n_sys:
+                raise SolverError(f"{what} has wrong number of rows. Expected {n_sys} but got {a.shape[0]}")
+            return np.ascontiguousarray(a)
+
+        y0, yp0 = state_block(y0, "y0"), state_block(yp0, "yp0")
         if output_mode is None:
             output_mode = 1 if self.output_variables else 0
         n_ret = D.n_vars if output_mode == 1 else D.n_states
-        if len(t_interp):
+        adaptive = len(t_interp) == 0
+        if want_yp is None:
+            want_yp = bool(self.options.get("hermite_interpolation", True)) and adaptive
+        want_yp = bool(want_yp) and output_mode == 0
+        if not adaptive:
             n_max = lib.pbgpu_result_capacity(len(t_eval), len(t_interp))
         else:
-            n_max = int(self.options.get("max_saved_steps", 4096))
+            n_max = max(int(self.options.get("max_saved_steps", 4096)), len(t_eval) + 2)
+        r = self._solve_batch(t_eval, t_interp, inputs, y0, yp0, output_mode, n_ret, n_max, want_stats, want_yp)
+        over = np.nonzero(r["n_t"] > n_max)[0]
+        if len(over):
+            # adaptive-step mode: some systems took more steps than the block holds.  The kernel counted them all, so one
+            # more pass over those rows with an exact capacity completes them.
+            n_big = int(r["n_t"][over].max())
+            sub = self._solve_batch(t_eval, t_interp, np.ascontiguousarray(inputs[over]),
+                                    None if y0 is None else np.ascontiguousarray(y0[over]),
+                                    None if yp0 is None else np.ascontiguousarray(yp0[over]), output_mode, n_ret, n_big,
+                                    want_stats, want_yp)
+
+            def grow(a):
+                if a is None:
+                    return None
+                b = np.zeros((a.shape[0], n_big) + a.shape[2:], dtype=a.dtype)
+                b[:, :a.shape[1]] = a
+                return b
+
+            for key in ("t", "y", "yp"):
+                if r[key] is not None:
+                    big = grow(np.asarray(r[key]))
+                    big[over] = sub[key]
+                    r[key] = big
+            for key in ("n_t", "flag", "y_term", "stats", "event_idx", "t_event"):
+                if r[key] is not None:
+                    r[key] = np.array(r[key])
+                    r[key][over] = sub[key]
+            r["n_max"] = n_big
+            r["_keep"] = None
+        if want_stats and r["stats"] is not None:
+            self._cost_model.fit(inputs, r["stats"][:, 0])
+        return r
+
+    def _solve_batch(self, t_eval, t_interp, inputs, y0, yp0, output_mode, n_ret, n_max, want_stats, want_yp):
+        n_sys = inputs.shape[0]
         if len(self._solvers) == 1 or n_sys < 2 * len(self._solvers):
-            r = self._solve_shard(0, t_eval, t_interp, inputs, y0, output_mode, n_ret, n_max, want_stats)
+            r = self._solve_shard(0, t_eval, t_interp, inputs, y0, yp0, output_mode, n_ret, n_max, want_stats, want_yp)
             self.last_kernel_ms, self.last_total_ms = r.pop("kernel_ms"), r.pop("total_ms")
             return r
         # shard over the devices: one host thread per device (ctypes releases the GIL during pbgpu_solve)
@@ -293,15 +361,16 @@ class BatchedIDASolver:
 
         from .shard import cost_proxy, gather_rows, partition
 
-        shards = partition(n_sys, len(self._solvers), cost_proxy(inputs, self.bundle.input_names))
+        shards = partition(n_sys, len(self._solvers), cost_proxy(inputs, self._cost_model))
         parts, errors = [None] * len(shards), []
 
         def work(k):
             try:
                 idx = shards[k]
                 parts[k] = self._solve_shard(k, t_eval, t_interp, np.ascontiguousarray(inputs[idx]),
-                                             None if y0 is None else np.ascontiguousarray(y0[idx]), output_mode, n_ret,
-                                             n_max, want_stats)
+                                             None if y0 is None else np.ascontiguousarray(y0[idx]),
+                                             None if yp0 is None else np.ascontiguousarray(yp0[idx]), output_mode, n_ret,
+                                             n_max, want_stats, want_yp)
             except Exception as e:  # re-raised on the calling thread
                 errors.append(e)
 
@@ -314,13 +383,15 @@ class BatchedIDASolver:
             raise errors[0]
         self.last_kernel_ms = max(p_["kernel_ms"] for p_ in parts)
         self.last_total_ms = max(p_["total_ms"] for p_ in parts)
-        out = {k: gather_rows([p_[k] for p_ in parts], shards, n_sys) for k in ("t", "y", "n_t", "flag", "y_term")}
+        out = {k: gather_rows([p_[k] for p_ in parts], shards, n_sys)
+               for k in ("t", "y", "n_t", "flag", "y_term", "event_idx", "t_event")}
+        out["yp"] = gather_rows([p_["yp"] for p_ in parts], shards, n_sys) if want_yp else None
         out["stats"] = gather_rows([p_["stats"] for p_ in parts], shards, n_sys) if want_stats else None
         out["n_max"] = n_max
         out["_keep"] = None
         return out
 
-    def _solve_shard(self, k, t_eval, t_interp, inputs, y0, output_mode, n_ret, n_max, want_stats):
+    def _solve_shard(self, k, t_eval, t_interp, inputs, y0, yp0, output_mode, n_ret, n_max, want_stats, want_yp):
         """One pbgpu_solve call on device slot k with host buffers (pinned result block, reused across calls)."""
         lib, D = self._lib, self.desc
         n_sys = inputs.shape[0]
@@ -335,26 +406,31 @@ class BatchedIDASolver:
             (t_out, k1), (y_out, k2) = cache[key]
         else:
             (t_out, k1), (y_out, k2) = _pinned_empty((n_sys, n_max), np.float64), _pinned_empty((n_sys, n_max, n_ret), np.float64)
+        yp_out, k3 = _pinned_empty((n_sys, n_max, D.n_states), np.float64) if want_yp else (None, None)
         n_t = np.zeros(n_sys, np.int32)
         flag = np.zeros(n_sys, np.int32)
+        event_idx = np.zeros(n_sys, np.int32)
+        t_event = np.zeros(n_sys)
         y_term = np.zeros((n_sys, D.n_states))
         stats = np.zeros((n_sys, 8), np.int64) if want_stats else None
         res = Result()
         res.n_max, res.n_ret = n_max, n_ret
         res.t, res.y, res.n_t, res.flag = _ptr(t_out), _ptr(y_out), _ptr(n_t), _ptr(flag)
-        res.y_term, res.stats = _ptr(y_term), _ptr(stats)
+        res.y_term, res.stats, res.yp = _ptr(y_term), _ptr(stats), _ptr(yp_out)
+        res.event_idx, res.t_event = _ptr(event_idx), _ptr(t_event)
         # expensive systems first: the batch ends when its slowest system does (results stay in row order)
         from .shard import launch_order
 
-        order = np.ascontiguousarray(launch_order(inputs, self.bundle.input_names), dtype=np.int32)
+        order = np.ascontiguousarray(launch_order(inputs, self._cost_model), dtype=np.int32)
         if lib.pbgpu_solver_set_launch_order(self._solvers[k], _ptr(order), n_sys):
             raise SolverError(_err(lib))
         rc = lib.pbgpu_solve(self._solvers[k], n_sys, _ptr(t_eval), len(t_eval), _ptr(t_interp) if len(t_interp) else None,
-                             len(t_interp), _ptr(y0), _ptr(inputs), output_mode, C.byref(res))
+                             len(t_interp), _ptr(y0), _ptr(yp0), _ptr(inputs), output_mode, C.byref(res))
         if rc:
             raise SolverError(_err(lib))
-        return dict(t=t_out, y=y_out, n_t=n_t, flag=flag, y_term=y_term, stats=stats, n_max=n_max, _keep=(k1, k2),
-                    kernel_ms=float(res.kernel_ms), total_ms=float(res.total_ms))
+        return dict(t=t_out, y=y_out, yp=yp_out, n_t=n_t, flag=flag, y_term=y_term, stats=stats, event_idx=event_idx,
+                    t_event=t_event, n_max=n_max, _keep=(k1, k2, k3), kernel_ms=float(res.kernel_ms),
+                    total_ms=float(res.total_ms))
 
     def solve(self, t_eval, inputs=None, t_interp=None, y0=None):
         """solve(t_eval, inputs=[{...}, ...]) -> list[Solution] (a single Solution for a single dict)."""
@@ -373,14 +449,10 @@ class BatchedIDASolver:
                 variables[name] = slice(off, off + n)
                 off += n
         sols = []
-        ev_vals = None
-        if self.bundle.n_events and np.any(r["flag"] == IDA_ROOT_RETURN):
-            # which event fired: argmin |g| at the final state (idaklu_solver.py:826-834)
-            t_end = r["t"][np.arange(len(inputs_list)), np.maximum(r["n_t"] - 1, 0)]
-            ev_vals = np.abs(self.eval("events", r["y_term"], p, t_end))
-        n_t, flags = r["n_t"].tolist(), r["flag"].tolist()
-        closest = np.nanargmin(ev_vals, axis=1).tolist() if ev_vals is not None else None
-        t_all, y_all, yt_all, st_all = r["t"], r["y"], r["y_term"], r["stats"]
+        n_t, flags = np.minimum(r["n_t"], r["n_max"]).tolist(), r["flag"].tolist()
+        # which event ended each system: found by the kernel at the root (argmin |g|, idaklu_solver.py:826-834)
+        closest = r["event_idx"].tolist()
+        t_all, y_all, yt_all, st_all, yp_all = r["t"], r["y"], r["y_term"], r["stats"], r["yp"]
         names = self.bundle.event_names
         for i, d in enumerate(inputs_list):
             n, flag = n_t[i], flags[i]
@@ -390,11 +462,14 @@ class BatchedIDASolver:
                     raise SolverError(msg)
                 if self.on_failure == "warn":
                     warnings.warn(msg + ", returning a partial solution.", stacklevel=2)
-            idx = closest[i] if (flag == IDA_ROOT_RETURN and closest is not None) else None
+            idx = closest[i] if (flag == IDA_ROOT_RETURN and closest[i] >= 0) else None
             if n == 1 and flag == IDA_ROOT_RETURN:
                 raise SolverError(f"Events {[names[k] for k in range(self.bundle.n_events)]} are non-positive at initial conditions")
-            sols.append(Solution(t_all[i, :n], y_all[i, :n], d, flag, yt_all[i], st_all[i] if st_all is not None else None,
-                                 variables, names, idx))
+            sol = Solution(t_all[i, :n], y_all[i, :n], d, flag, yt_all[i], st_all[i] if st_all is not None else None,
+                           variables, names, idx)
+            if yp_all is not None:
+                sol._yp_rows = yp_all[i, :n]
+            sols.append(sol)
         return sols[0] if single else sols
 
     # -- device evaluation of the generated functions (parity tests, event identification) ---------

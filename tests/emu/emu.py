@@ -53,16 +53,20 @@ class Emu:
                                y2.ctypes.data_as(vp), out.ctypes.data_as(vp))
         return out, rc
 
-    def solve(self, t_eval, inputs, t_interp=None, rtol=1e-4, atol=1e-6, y0=None, save_vars=False, options=None):
+    def solve(self, t_eval, inputs, t_interp=None, rtol=1e-4, atol=1e-6, y0=None, save_vars=False, options=None, n_max=None,
+              want_yp=False, yp0=None):
         t_eval, t_interp = canonical_time_grids(t_eval, t_interp)
         inputs = np.ascontiguousarray(np.atleast_2d(np.asarray(inputs, dtype=np.float64)))
         n_sys = inputs.shape[0]
         atol_v = np.ascontiguousarray(np.broadcast_to(np.asarray(atol, dtype=np.float64), (self.n,)).copy())
         n_ret = self.n_var if save_vars else self.n
-        n_max = (len(t_interp) + len(t_eval) + 2) if len(t_interp) else 20000
+        if n_max is None:
+            n_max = (len(t_interp) + len(t_eval) + 2) if len(t_interp) else 20000
         t_out = np.zeros((n_sys, n_max)); y_out = np.zeros((n_sys, n_max, n_ret))
         n_out = np.zeros(n_sys, np.int32); flag = np.zeros(n_sys, np.int32)
         y_term = np.zeros((n_sys, self.n)); stats = np.zeros((n_sys, 8), np.int64)
+        event_idx = np.full(n_sys, -7, np.int32); t_event = np.zeros(n_sys)
+        yp_out = np.zeros((n_sys, n_max, self.n)) if (want_yp and not save_vars) else None
         queue = np.zeros(1, np.uint32)
         opt = default_options(rtol=rtol, **(options or {}))
         L = LaunchArgs()
@@ -80,6 +84,13 @@ class Emu:
         L.t_out = t_out.ctypes.data_as(vp); L.y_out = y_out.ctypes.data_as(vp); L.n_out = n_out.ctypes.data_as(vp)
         L.flag = flag.ctypes.data_as(vp); L.y_term = y_term.ctypes.data_as(vp); L.stats = stats.ctypes.data_as(vp)
         L.queue = queue.ctypes.data_as(vp); L.opt = opt
+        L.event_idx = event_idx.ctypes.data_as(vp); L.t_event = t_event.ctypes.data_as(vp)
+        L.yp_out = yp_out.ctypes.data_as(vp) if yp_out is not None else None
+        if yp0 is not None:
+            yp0 = np.ascontiguousarray(np.atleast_2d(np.asarray(yp0, dtype=np.float64))); keep.append(yp0)
+            L.yp0 = yp0.ctypes.data_as(vp)
         self.lib.emu_solve(C.byref(L))
-        return dict(t=[t_out[i, :n_out[i]] for i in range(n_sys)], y=[y_out[i, :n_out[i]] for i in range(n_sys)],
-                    flag=flag, y_term=y_term, stats=stats, n_out=n_out)
+        ns = np.minimum(n_out, n_max)
+        return dict(t=[t_out[i, :ns[i]] for i in range(n_sys)], y=[y_out[i, :ns[i]] for i in range(n_sys)],
+                    yp=None if yp_out is None else [yp_out[i, :ns[i]] for i in range(n_sys)],
+                    flag=flag, y_term=y_term, stats=stats, n_out=n_out, event_idx=event_idx, t_event=t_event)

@@ -245,7 +245,7 @@ def test_device_pointer_entry_point():
     res = Result()
     res.n_max, res.n_ret = n_max, 1
     res.t, res.y, res.n_t, res.flag = t_out.data_ptr(), y_out.data_ptr(), n_t.data_ptr(), flag.data_ptr()
-    rc = s._lib.pbgpu_solve_device(s._solver, n, C.c_void_p(te.data_ptr()), 2, C.c_void_p(ti.data_ptr()), len(ti), None,
+    rc = s._lib.pbgpu_solve_device(s._solver, n, C.c_void_p(te.data_ptr()), 2, C.c_void_p(ti.data_ptr()), len(ti), None, None,
                                    C.c_void_p(pin.data_ptr()), 1, C.byref(res), None, 1)
     assert rc == 0 and res.kernel_ms > 0
     np.testing.assert_array_equal(n_t.cpu().numpy(), ref["n_t"])
@@ -345,3 +345,44 @@ def test_multi_device_sharding_matches_single_device():
     for i in range(len(p)):
         np.testing.assert_array_equal(r["y"][i, :n1[i]], y1[i, :n1[i]])
         np.testing.assert_array_equal(r["t"][i, :n1[i]], t1[i, :n1[i]])
+
+
+@pytest.mark.gpu
+def test_adaptive_steps_beyond_the_first_block_are_re_solved_not_truncated():
+    # a system with more steps than max_saved_steps used to come back short with a success flag
+    from pybamm_b200 import BatchedIDASolver
+
+    b = util.bundle("kat_decay")
+    s = BatchedIDASolver(b, rtol=1e-8, atol=1e-10, options={"max_saved_steps": 8})
+    big = BatchedIDASolver(b, rtol=1e-8, atol=1e-10)
+    p = np.array([[0.3], [0.05], [1.0]])
+    r, q = s.solve_arrays([0.0, 10.0], p), big.solve_arrays([0.0, 10.0], p)
+    np.testing.assert_array_equal(r["n_t"], q["n_t"])
+    assert int(r["n_t"].max()) > 8 and r["n_max"] == int(r["n_t"].max())
+    for i in range(3):
+        k = int(q["n_t"][i])
+        np.testing.assert_array_equal(r["t"][i, :k], q["t"][i, :k])
+        np.testing.assert_array_equal(r["y"][i, :k], q["y"][i, :k])
+        assert r["t"][i, k - 1] == 10.0
+    sols = s.solve([0.0, 10.0], inputs=[{"rate": 0.3}])
+    assert sols[0].t[-1] == 10.0 and sols[0].termination == "final time"
+
+
+@pytest.mark.gpu
+def test_hermite_data_event_index_and_event_time_from_the_device():
+    from pybamm_b200 import BatchedIDASolver
+
+    s = BatchedIDASolver(util.bundle("kat_decay"), rtol=1e-9, atol=1e-11)
+    sol = s.solve([0.0, 10.0], inputs=[{"rate": 0.3}])[0]
+    assert sol.yp is not None and sol.yp.shape == sol.y.shape           # adaptive steps + full state: hermite_interpolation
+    np.testing.assert_allclose(sol.yp[0], -0.3 * sol.y[0], rtol=1e-4, atol=1e-9)
+    assert s.solve([0.0, 10.0], inputs=[{"rate": 0.3}], t_interp=np.linspace(0, 10, 11))[0].yp is None
+    e = util.emu("kat_decay").solve([0.0, 10.0], np.array([[0.3]]), rtol=1e-9, atol=1e-11, want_yp=True)
+    np.testing.assert_allclose(sol.t, e["t"][0], rtol=0, atol=1e-9)
+    rb = BatchedIDASolver(util.bundle("kat_roberts"), rtol=1e-8, atol=1e-8)
+    r = rb.solve_arrays([0.0, 5.0], np.zeros((2, 0)), t_interp=np.linspace(0, 5, 11))
+    assert list(r["flag"]) == [2, 2] and list(r["event_idx"]) == [0, 0]
+    np.testing.assert_allclose(r["t_event"], 2.0, atol=1e-6)
+    st = BatchedIDASolver(util.bundle("kat_decay"), rtol=1e-8, atol=1e-10, on_failure="ignore",
+                          options={"num_steps_no_progress": 5, "t_no_progress": 1e9})
+    assert st.solve_arrays([0.0, 10.0], np.array([[0.3]]))["flag"][0] == -3

@@ -135,7 +135,7 @@ dist.init_process_group("gloo")
 rank, world = dist.get_rank(), dist.get_world_size()
 b = util.bundle("spm")
 p = util.sample_inputs(b, 9, np.random.default_rng(7))
-parts = shard.partition(len(p), world, shard.cost_proxy(p, b.input_names))
+parts = shard.partition(len(p), world, shard.cost_proxy(p))
 mine = parts[rank]
 e = util.emu("spm")          # tests only: the emulation stands in for the per-rank GPU solve
 r = e.solve(util.T_EVAL, p[mine], t_interp=util.T_INTERP, rtol=1e-6, atol=1e-8, save_vars=True)

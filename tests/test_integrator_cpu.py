@@ -94,3 +94,65 @@ def test_failure_is_a_flag_not_an_exception():
     p = util.sample_inputs(b, 1, np.random.default_rng(2))
     r = e.solve(util.T_EVAL, p, t_interp=util.T_INTERP, rtol=1e-8, atol=1e-8, options={"max_num_steps": 20})
     assert r["flag"][0] == -1 and 1 <= len(r["t"][0]) < len(util.T_INTERP)
+
+
+def test_adaptive_block_overflow_is_counted_not_silently_truncated():
+    # ExtendAdaptiveArrays (IDAKLUSolverOpenMP.inl:608-612) grows without bound; the fixed block counts every point
+    # so that the host can re-solve with the exact capacity (solver.solve_arrays)
+    e = util.emu("kat_decay")
+    full = e.solve([0.0, 10.0], np.array([[0.3]]), rtol=1e-8, atol=1e-10)
+    n_full = int(full["n_out"][0])
+    assert n_full > 20 and len(full["t"][0]) == n_full
+    small = e.solve([0.0, 10.0], np.array([[0.3]]), rtol=1e-8, atol=1e-10, n_max=10)
+    assert int(small["n_out"][0]) == n_full           # counted past the capacity
+    np.testing.assert_array_equal(small["t"][0], full["t"][0][:10])
+    assert small["flag"][0] == full["flag"][0] and small["t_event"][0] == full["t"][0][-1]
+
+
+def test_hermite_derivatives_are_stored_with_the_adaptive_steps():
+    # save_hermite (IDAKLUSolverOpenMP.inl:432-435, 447-457): yp = IDAGetDky(t, 1) at every stored step
+    e = util.emu("kat_decay")
+    rate = 0.3
+    r = e.solve([0.0, 10.0], np.array([[rate]]), rtol=1e-9, atol=1e-11, want_yp=True)
+    t, y, yp = r["t"][0], r["y"][0][:, 0], r["yp"][0][:, 0]
+    np.testing.assert_allclose(y, 2.0 * np.exp(-rate * t), rtol=1e-6)
+    # the derivative of the interpolating polynomial satisfies the ODE to integration accuracy
+    np.testing.assert_allclose(yp, -rate * y, rtol=1e-4, atol=1e-9)
+
+
+def test_event_index_and_time_come_back_from_the_kernel():
+    # closest_event_idx (idaklu_solver.py:826-834): roberts ends on event 0 ("0.2 - u") at t = 2
+    e = util.emu("kat_roberts")
+    r = e.solve([0.0, 5.0], np.zeros((1, 0)), t_interp=np.linspace(0, 5, 11), rtol=1e-8, atol=1e-8)
+    assert r["flag"][0] == 2 and r["event_idx"][0] == 0
+    assert abs(r["t_event"][0] - 2.0) < 1e-6 and r["t_event"][0] == r["t"][0][-1]
+    d = util.emu("kat_decay").solve([0.0, 1.0], np.array([[0.1]]), rtol=1e-6, atol=1e-8)
+    assert d["flag"][0] in (0, 1) and d["event_idx"][0] == -1
+
+
+def test_no_progress_guard_ends_a_stalled_integration():
+    # NoProgressGuard.hpp:12-66: fewer than t_no_progress seconds over the last num_steps_no_progress steps -> IDA_ERR_FAIL
+    e = util.emu("kat_decay")
+    ok = e.solve([0.0, 10.0], np.array([[0.3]]), rtol=1e-8, atol=1e-10,
+                 options={"num_steps_no_progress": 5, "t_no_progress": 1e-9})
+    assert ok["flag"][0] in (0, 1)
+    stalled = e.solve([0.0, 10.0], np.array([[0.3]]), rtol=1e-8, atol=1e-10,
+                      options={"num_steps_no_progress": 5, "t_no_progress": 1e9})
+    assert stalled["flag"][0] == -3 and stalled["t"][0][-1] < 10.0
+    off = e.solve([0.0, 10.0], np.array([[0.3]]), rtol=1e-8, atol=1e-10,
+                  options={"num_steps_no_progress": 0, "t_no_progress": 1e9})
+    assert off["flag"][0] in (0, 1)
+
+
+def test_yp0_is_used_only_without_calc_ic():
+    # SetupInitialState (IDAKLUSolverOpenMP.inl:514-563): with calc_ic the derivatives are recomputed, without it the
+    # caller's ydot0 is what IDA starts from
+    e = util.emu("kat_decay")
+    p = np.array([[0.3]])
+    base = e.solve([0.0, 1.0], p, rtol=1e-8, atol=1e-10)
+    with_ic = e.solve([0.0, 1.0], p, rtol=1e-8, atol=1e-10, yp0=np.array([[123.0]]))
+    np.testing.assert_array_equal(with_ic["t"][0], base["t"][0])
+    good = e.solve([0.0, 1.0], p, rtol=1e-8, atol=1e-10, yp0=np.array([[-0.6]]), options={"calc_ic": False})
+    np.testing.assert_allclose(good["y"][0][-1, 0], 2.0 * np.exp(-0.3), rtol=1e-6)
+    bad = e.solve([0.0, 1.0], p, rtol=1e-8, atol=1e-10, yp0=np.array([[123.0]]), options={"calc_ic": False})
+    assert not np.array_equal(bad["t"][0], base["t"][0])      # the wrong derivative changes the first step

@@ -14,7 +14,7 @@ s = BatchedIDASolver(bundle, rtol=1e-8, atol=1e-8, output_variables=["Voltage [V
 ti = np.linspace(0, 3600, 361)
 r = s.solve_arrays([0.0, 3700.0], p, t_interp=ti, want_stats=True)
 work = r["stats"][:, 1] + 8.0 * r["stats"][:, 2]      # residuals + 8 x set-ups: roughly proportional to time
-c = cost_proxy(p, bundle.input_names)
+c = cost_proxy(p, s._cost_model)      # fitted on the step counts of the solve above
 print("inputs:", bundle.input_names)
 X = np.column_stack([np.ones(n)] + [p[:, k] for k in range(p.shape[1])] + [np.log(np.abs(p[:, k]) + 1e-300) for k in range(p.shape[1])])
 coef, *_ = np.linalg.lstsq(X, work, rcond=None)
