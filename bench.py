@@ -1,22 +1,29 @@
 #!/usr/bin/env python
-"""bench.py -- BASELINE.json's metric: DFN simulations / second (10k input sets per GPU, rtol = atol = 1e-8).
+"""bench.py -- BASELINE.json's metric: DFN simulations / second (10k input sets, rtol = atol = 1e-8).
 
   python bench.py --gpus N --steps K --warmup W                (N > 1: launched by torch.distributed.run, one rank per GPU)
   python bench.py --impl reference --gpus N --steps K --warmup W     (CPU arm: the reference algorithm on the host cores)
+  python bench.py --scaling strong --gpus N ...                (the metric's own batch: 10 000 sets in TOTAL, split over the ranks)
+  python bench.py --inproc-devices N                           (one process, one BatchedIDASolver(devices=range(N)).solve call)
+  python bench.py --model spm --n-sys 1000 | --model spme      (BASELINE configs 1 and 2)
 
-A "step" is one batched solve of the workload: DFN (Chen2020, default mesh, 962 states), constant-current
-discharge, t_eval = [0, 3700] s, t_interp = linspace(0, 3600, 361), 10 000 input sets per GPU varying four
-parameters (current, both particle diffusivities, initial electrolyte concentration),
-output_variables = ["Voltage [V]"].  The batch is sharded by rank with no collective inside the integration
-(weak scaling: every rank integrates its own 10k sets).
+A "step" is one batched solve of the workload: DFN (Chen2020, default mesh, 962 states), constant-current discharge,
+t_eval = [0, 3700] s, t_interp = linspace(0, 3600, 361), 10 000 input sets per GPU varying four parameters (current, both
+particle diffusivities, initial electrolyte concentration), output_variables = ["Voltage [V]"].
+The batch is sharded by rank with no collective inside the integration (weak scaling: every rank integrates its own 10k
+sets; --scaling strong: shard.partition of one 10k batch).
 
-`value`  : device-resident inputs, pbgpu_solve_device on a CUDA stream, CUDA events around each step.
-`e2e`    : the public call BatchedIDASolver.solve(t_eval, inputs=[{...}, ...]) with host buffers: flattening the
-           input dicts, H2D, kernel, D2H and building the Solution objects are all inside the timed region.
-`roofline`: FP64 pipe. achieved = W(algorithmic flop per simulation) * sims / kernel time; peak = DFMA
-           rate measured live on this box by pybamm_b200/csrc/pbgpu_peak.cu.  The HBM fraction is reported beside it.
-`cpu_baseline`: the CPU oracle (oracle/ida_oracle.c, "port": the reference IDAKLU cannot be built here) on all host
-           cores over a bounded sample of the same input sets; its IDA counters also feed W.
+`value`   : device-resident inputs, pbgpu_solve_device on a CUDA stream, CUDA events around each step.
+`e2e`     : the public call BatchedIDASolver.solve(t_eval, inputs=[{...}, ...]) with host buffers: flattening the input
+            dicts, H2D, kernel, D2H and building the Solution objects are all inside the timed region.
+`roofline`: FP64 pipe. achieved = W(algorithmic flop per simulation) * sims / kernel time; peak = DFMA rate
+            measured live on this box by pybamm_b200/csrc/pbgpu_peak.cu.  The HBM fraction is reported beside it.
+`cpu_baseline`: the CPU restatement of the reference algorithm (oracle/ida_oracle.c, "port": the reference IDAKLU cannot
+            be built here) in its baseline build -- static-pattern sparse LU (what KLU's refactor does), -O3 -march=native,
+            OpenMP over systems, all host cores -- on a bounded sample of the same input sets; its IDA counters feed W.
+`parity`  : the first --parity-sample systems against the checker build of the oracle (banded LU with partial pivoting) at
+            1e-8 and against the oracle at 1e-11 ("truth").  The line's `parity_ok` is False -- and the exit code 3 -- when a
+            bar is exceeded (BASELINE.md section 6 states the bars).
 """
 from __future__ import annotations
 
@@ -38,8 +45,14 @@ if ROOT not in sys.path:
 T_EVAL = [0.0, 3700.0]
 T_INTERP = np.linspace(0.0, 3600.0, 361)
 RTOL = ATOL = 1e-8
-METRIC = "DFN simulations/sec (10k input sets)"   # --model spm/spme rename it below (parity-config side runs)
 UNIT = "simulations/s"
+V_BAR, T_BAR = 1e-6, 1e-3          # north_star: terminal voltage within 1e-6 V, event times within 1e-3 s
+
+
+def metric_name(args):
+    if args.model == "dfn":
+        return "DFN simulations/sec (10k input sets)"
+    return f"{args.model.upper()} simulations/sec ({args.n_sys} input sets)"
 
 
 def sample_inputs(bundle, n, rng):
@@ -59,43 +72,63 @@ def sample_inputs(bundle, n, rng):
     return np.ascontiguousarray(np.column_stack(cols))
 
 
-def workload_config(args, world):
+def workload_config(args, world, n_total):
     return {
         "workload": f"{args.model.upper()} Chen2020 default mesh, 1C-range constant-current discharge, "
-                    f"{args.n_sys} input sets per GPU varying {4 if args.model == 'dfn' else 2} parameters",
+                    f"{n_total} input sets varying {4 if args.model == 'dfn' else 2} parameters"
+                    + (", 3.0 V cut-off" if args.model == "spme" else ""),
         "model_states": None,  # filled by the caller
-        "n_sys_per_gpu": args.n_sys,
-        "n_sys_total": args.n_sys * world,
+        "n_sys_per_gpu": args.n_sys if args.scaling == "weak" else None,
+        "n_sys_total": n_total,
         "rtol": RTOL, "atol": ATOL,
         "t_eval": T_EVAL, "t_interp": "linspace(0, 3600, 361)",
         "output": "Voltage [V]",
         "sharding": f"batch rows over {world} rank(s), no collective",
         "l2": "flushed between timed steps (256 MiB write)",
-        "launch_order": "rows handed to the teams by descending predicted step count (log-linear fit on a previous solve), results in row order",
+        "launch_order": "rows handed to the teams by descending predicted step count (log-linear fit on a previous solve), "
+                        "results in row order",
     }
 
 
-def ncu_dram_traffic(n_sys):
-    """dram__bytes_read.sum + dram__bytes_write.sum of pbgpu_solve_kernel from the committed `ncu --set full` capture
-    (profiles/r01_dfn_full_ncu_raw.csv: `ncu --page raw --csv` of one launch with one DFN system per team, so the
-    grid size is the number of systems), scaled to this launch's system count.
-    Returns (bytes per launch or None, provenance)."""
-    path = os.path.join(ROOT, "profiles", "r01_dfn_full_ncu_raw.csv")
+def reference_install_probe():
+    """is a real reference install importable on this box?  (It replaces the port if it ever is.)"""
+    code = ("import sys; sys.path.insert(0, 'baseline/_ref')\n"
+            "import importlib\n"
+            "out = {}\n"
+            "for m in ('pybamm', 'pybammsolvers', 'casadi'):\n"
+            "    try:\n"
+            "        importlib.import_module(m); out[m] = True\n"
+            "    except Exception as e:\n"
+            "        out[m] = type(e).__name__\n"
+            "print(out)\n")
     try:
-        import csv
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120, cwd=ROOT)
+        return {"importable": "True" in r.stdout and "Error" not in r.stdout, "detail": r.stdout.strip()[:200]}
+    except Exception as e:
+        return {"importable": False, "detail": str(e)[:200]}
 
-        rows = [r for r in csv.reader(open(path)) if r]
-        hdr, units, vals = rows[0], rows[1], rows[2]
-        col = {h: k for k, h in enumerate(hdr)}
-        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-        total = sum(float(vals[col[m]].replace(",", "")) * scale[units[col[m]]]
-                    for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
-        n_cap = int(float(vals[col["launch__grid_size"]].replace(",", "")))
-        per_sim = total / n_cap
-        return per_sim * n_sys, (f"profiles/r01_dfn_full_ncu_raw.csv: ncu --set full, one launch of {n_cap} systems "
-                                 f"({per_sim / 1e3:.1f} KB per simulation), scaled to {n_sys} systems")
-    except Exception:
-        pass
+
+def ncu_dram_traffic(n_sys):
+    """dram__bytes_read.sum + dram__bytes_write.sum of pbgpu_solve_kernel from the newest committed `ncu --set full`
+    capture (profiles/r0X_dfn_full_ncu_raw.csv: `ncu --page raw --csv` of one launch with one DFN system per team, so the
+    grid size is the number of systems), scaled to this launch's system count.  Returns (bytes per launch or None, provenance)."""
+    import csv
+    import glob
+
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r0*_dfn_full_ncu_raw.csv")), reverse=True):
+        try:
+            rows = [r for r in csv.reader(open(path)) if r]
+            hdr, units, vals = rows[0], rows[1], rows[2]
+            col = {h: k for k, h in enumerate(hdr)}
+            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+            total = sum(float(vals[col[m]].replace(",", "")) * scale[units[col[m]]]
+                        for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+            n_cap = int(float(vals[col["launch__grid_size"]].replace(",", "")))
+            per_sim = total / n_cap
+            return per_sim * n_sys, (f"{os.path.relpath(path, ROOT)}: ncu --set full, one launch of {n_cap} systems "
+                                     f"({per_sim / 1e3:.1f} KB per simulation), scaled to {n_sys} systems")
+        except Exception:
+            continue
     return None, "no ncu capture found"
 
 
@@ -177,16 +210,27 @@ def work_model(desc, stats_mean, n_out, n_states):
                    n_fac=nsetups, n_slv=nni, n_att=n_att, n_out=n_out)
 
 
-def run_cpu_oracle(bundle, p, n_threads):
-    """Reference algorithm on the host cores (the CPU oracle; test/bench infrastructure only)."""
+# ---- the CPU legs (oracle/ is test + baseline infrastructure: never on the product path) ------------------------------
+def cpu_oracle(bundle, fast):
+    """fast: the baseline build (static sparse LU, -O3 -march=native, compiled on this machine); else the checker."""
     from oracle.oracle import Oracle
     from pybamm_b200 import build
 
-    o = Oracle(build.build_oracle(bundle))
+    o = Oracle(build.build_oracle(bundle, fast=fast))
     o.set_rcm(bundle.jac_rows, bundle.jac_cols)
+    o.set_sparse(*build.lu_order(bundle))
+    return o
+
+
+def run_cpu(o, p, n_threads, lu, tol=RTOL):
     t0 = time.perf_counter()
-    r = o.solve(T_EVAL, p, t_interp=T_INTERP, rtol=RTOL, atol=ATOL, save_vars=True, n_threads=n_threads)
+    r = o.solve(T_EVAL, p, t_interp=T_INTERP, rtol=tol, atol=tol, save_vars=True, n_threads=n_threads, lu=lu)
     return r, time.perf_counter() - t0
+
+
+CPU_NOTE = ("CPU restatement of the reference algorithm (IDA-style BDF, oracle/ida_oracle.c), baseline build: static-pattern "
+            "sparse LU in the device's ordering (what klu_refactor does), gcc -O3 -march=native, OpenMP schedule(dynamic) over "
+            "systems; not IDAKLU (pybamm / pybammsolvers / casadi / SUNDIALS / KLU are not installable here)")
 
 
 def _env_ranks(args):
@@ -199,9 +243,9 @@ def _env_ranks(args):
 
 
 def run_reference_arm(args):
-    """--impl reference: the reference algorithm for this path on the box's host cores.  pybamm / pybammsolvers / casadi /
-    SUNDIALS / KLU cannot be installed or built here, so this runs the CPU oracle ("port") with all host threads
-    on a bounded sample of rank 0's input sets per step."""
+    """--impl reference: the reference algorithm for this path on the box's host cores, all host threads.  The K timed steps
+    together cover the batch exactly once (step k = rows k::K of rank 0's 10 000 input sets) unless that would exceed the
+    time budget, in which case a prefix of every slice is taken and `sample` says how many rows ran."""
     rank, world, _ = _env_ranks(args)
     if rank != 0:
         return 0
@@ -209,33 +253,82 @@ def run_reference_arm(args):
 
     bundle = build.load_bundle(args.model)
     cores = os.cpu_count() or 1
+    o = cpu_oracle(bundle, fast=True)
     p_all = sample_inputs(bundle, args.n_sys, np.random.default_rng(20260))
-    _, t_cal = run_cpu_oracle(bundle, p_all[:2 * cores], cores)          # calibration (also warms the library)
+    _, t_cal = run_cpu(o, p_all[:2 * cores], cores, "sparse")          # calibration (also warms the library)
     per_sim = t_cal / (2 * cores)
-    budget_s = 150.0
-    n_sample = int(max(cores, min(args.n_sys, budget_s / max(per_sim, 1e-6) / (args.steps + args.warmup))))
-    n_sample = min(n_sample, args.cpu_sample_max)
-    p = np.ascontiguousarray(p_all[:n_sample])
-    for _ in range(args.warmup):
-        run_cpu_oracle(bundle, p, cores)
-    total = 0.0
-    for _ in range(args.steps):
-        _, dt = run_cpu_oracle(bundle, p, cores)
+    steps = max(1, args.steps)
+    slices = [np.ascontiguousarray(p_all[k::steps]) for k in range(steps)]
+    budget_s = float(args.cpu_budget_s)
+    est = per_sim * args.n_sys
+    frac = min(1.0, budget_s / max(est, 1e-9))
+    if frac < 1.0:
+        slices = [s[:max(cores, int(len(s) * frac))] for s in slices]
+    for w in range(min(args.warmup, 1)):
+        run_cpu(o, slices[0][:4 * cores], cores, "sparse")
+    total, n_done = 0.0, 0
+    for s in slices:
+        _, dt = run_cpu(o, s, cores, "sparse")
         total += dt
-    value = n_sample * args.steps / total
-    cfg = workload_config(args, 1)
+        n_done += len(s)
+    value = n_done / total
+    cfg = workload_config(args, 1, args.n_sys)
     cfg["model_states"] = bundle.n_states
-    sample = f"first {n_sample} of the {args.n_sys} input sets of rank 0, per step"
+    sample = (f"all {args.n_sys} input sets of rank 0, {steps} timed steps of {len(slices[0])} rows each (rows k::{steps})"
+              if frac >= 1.0 else
+              f"{n_done} of the {args.n_sys} input sets of rank 0 ({steps} steps x {len(slices[0])} rows; budget {budget_s:.0f} s)")
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "impl": "reference", "metric": metric_name(args), "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / steps, "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
-                         "note": "CPU oracle (IDA restatement + banded LU), OpenMP over systems; not IDAKLU"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "note": CPU_NOTE},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "reference_install": reference_install_probe(),
     }
     print(json.dumps(line), flush=True)
     return 0
+
+
+def parity_block(bundle, p, n_t, flags, v_gpu, t_end_gpu, n_par, cores):
+    """GPU vs the checker oracle at 1e-8 (banded LU, partial pivoting) and vs the oracle at 1e-11 ("truth"), per system."""
+    o = cpu_oracle(bundle, fast=False)
+    ref, _ = run_cpu(o, p[:n_par], cores, "band")
+    tru, _ = run_cpu(o, p[:n_par], cores, "sparse", tol=1e-11)
+    redo = np.nonzero(tru["flag"] < 0)[0]          # 1e-11 is at the edge of what the first step's error test accepts
+    if len(redo):
+        again, _ = run_cpu(o, np.ascontiguousarray(p[:n_par][redo]), cores, "band", tol=1e-10)
+        for k, i in enumerate(redo):
+            for key in ("t", "y"):
+                tru[key][i] = again[key][k]
+            tru["flag"][i] = again["flag"][k]
+    e_gr, e_gt, e_rt, dt_gr, dt_gt = (np.zeros(n_par) for _ in range(5))
+    same = True
+    for i in range(n_par):
+        k = int(n_t[i])
+        if k != len(ref["t"][i]) or k != len(tru["t"][i]) or int(flags[i]) != int(ref["flag"][i]) or int(flags[i]) != int(tru["flag"][i]):
+            same = False
+            e_gr[i] = e_gt[i] = np.inf
+            continue
+        m = k - 1 if flags[i] == 2 else k          # the event point has its own time in every run
+        g, r, t = v_gpu[i, :m], ref["y"][i][:m, 0], tru["y"][i][:m, 0]
+        e_gr[i], e_gt[i], e_rt[i] = np.max(np.abs(g - r)), np.max(np.abs(g - t)), np.max(np.abs(r - t))
+        dt_gr[i] = abs(t_end_gpu[i] - ref["t"][i][-1])
+        dt_gt[i] = abs(t_end_gpu[i] - tru["t"][i][-1])
+    # bars (BASELINE.md section 6): event times within 1e-3 s; voltage within 1e-6 V of the reference algorithm's solution, or,
+    # where the 1e-8 tolerances themselves do not deliver 1e-6 V (the last grid point before a cut-off, |dV/dt| ~ 0.1 V/s),
+    # no further from the 1e-11 truth than twice the reference algorithm's own error there
+    ok_v = (e_gr <= V_BAR) | (e_gt <= np.maximum(V_BAR, 2.0 * e_rt))
+    ok = bool(same and ok_v.all() and dt_gr.max() <= T_BAR and dt_gt.max() <= T_BAR)
+    return {"systems": n_par, "same_termination": same, "ok": ok,
+            "max_abs_dV_gpu_vs_oracle_1e-8": float(e_gr.max()), "max_abs_dV_gpu_vs_truth_1e-11": float(e_gt.max()),
+            "max_abs_dV_oracle_1e-8_vs_truth": float(e_rt.max()),
+            "systems_above_1e-6_V": {"gpu_vs_oracle": int((e_gr > V_BAR).sum()), "gpu_vs_truth": int((e_gt > V_BAR).sum()),
+                                     "oracle_vs_truth": int((e_rt > V_BAR).sum())},
+            "median_abs_dV_gpu_vs_truth": float(np.median(e_gt)), "median_abs_dV_oracle_vs_truth": float(np.median(e_rt)),
+            "max_abs_dt_end_gpu_vs_oracle": float(dt_gr.max()), "max_abs_dt_end_gpu_vs_truth": float(dt_gt.max()),
+            "systems_failing_the_bar": int((~ok_v).sum()),
+            "bars": {"dV": V_BAR, "dt": T_BAR,
+                     "rule": "per system: |V_gpu - V_oracle(1e-8)| <= 1e-6 V, or |V_gpu - V_truth| <= max(1e-6 V, 2 |V_oracle(1e-8) - V_truth|)"}}, ref
 
 
 def run_b200_arm(args):
@@ -254,10 +347,19 @@ def run_b200_arm(args):
 
     from pybamm_b200 import BatchedIDASolver, build
     from pybamm_b200.host import Result, canonical_time_grids
+    from pybamm_b200.shard import launch_order, partition
 
     bundle = build.load_bundle(args.model)
-    n = args.n_sys
-    p = sample_inputs(bundle, n, np.random.default_rng(20260 + rank))
+    if args.scaling == "strong":
+        # the metric's own batch: args.n_sys input sets in TOTAL, dealt to the ranks by shard.partition
+        p_all = sample_inputs(bundle, args.n_sys, np.random.default_rng(20260))
+        rows = partition(args.n_sys, world)[rank]
+        p = np.ascontiguousarray(p_all[rows])
+        n_total = args.n_sys
+    else:
+        p = sample_inputs(bundle, args.n_sys, np.random.default_rng(20260 + rank))
+        n_total = args.n_sys * world
+    n = len(p)
     solver = BatchedIDASolver(bundle, rtol=RTOL, atol=ATOL, output_variables=["Voltage [V]"], device=local_rank,
                               on_failure="ignore", reuse_buffers=True)
     solver._ensure()
@@ -279,10 +381,8 @@ def run_b200_arm(args):
     stream = torch.cuda.Stream(device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     vp = C.c_void_p
-    # launch order of the persistent kernel: expensive rows first (shard.launch_order; results stay in row order)
-    from pybamm_b200.shard import launch_order
-
-    # the cost model is fitted on the step counts of one untimed solve of a 512-row sample (model-free: shard.CostModel)
+    # launch order of the persistent kernel: expensive rows first (shard.launch_order; results stay in row order).  The cost
+    # model is fitted on the step counts of one untimed solve of a 512-row sample (model-free: shard.CostModel)
     solver.solve_arrays(T_EVAL, p[:512], t_interp=T_INTERP)
     order = np.ascontiguousarray(launch_order(p, solver._cost_model), dtype=np.int32)
     if lib.pbgpu_solver_set_launch_order(solver._solver, order.ctypes.data_as(vp), n):
@@ -367,40 +467,65 @@ def run_b200_arm(args):
     e2e_s = time.perf_counter() - t0
     e2e_kernel_ms = solver.last_kernel_ms
     h2d = 8 * (p.size + len(te) + len(ti))
-    d2h = n * (8 * n_max * (1 + D.n_vars) + 4 + 4 + 8 * D.n_states + 64)
+    d2h = n * (8 * n_max * (1 + D.n_vars) + 4 + 4 + 8 * D.n_states + 64 + 4 + 8)
+
+    # ---- e2e with the full state brought back to the host (what a default solve() user pays), on a bounded sub-batch:
+    # 10 000 DFN systems are 28 GB of host memory, so the first --full-state-e2e rows are timed (2.8 GB for 1 000)
+    e2e_full = None
+    n_fs = min(args.full_state_e2e, n)
+    if world == 1 and n_fs > 0 and not args.no_full_state:
+        try:
+            fs = BatchedIDASolver(bundle, rtol=RTOL, atol=ATOL, device=local_rank, on_failure="ignore", reuse_buffers=True)
+            fs._cost_model = solver._cost_model
+            fs.solve(T_EVAL, inputs=inputs_list[:n_fs], t_interp=T_INTERP)
+            t0 = time.perf_counter()
+            sl = fs.solve(T_EVAL, inputs=inputs_list[:n_fs], t_interp=T_INTERP)
+            _ = float(sl[-1].y[0, -1])
+            dt_fs = time.perf_counter() - t0
+            e2e_full = {"value": n_fs / dt_fs, "unit": UNIT, "n_sys": n_fs, "kernel_ms": fs.last_kernel_ms,
+                        "d2h_bytes": int(n_fs * 8 * n_max * (1 + D.n_states)),
+                        "call": "BatchedIDASolver(output_variables=None).solve(...): y (n_states x n_t) of every system on the host"}
+            fs.close()
+            del fs, sl
+        except Exception as e:
+            e2e_full = {"value": None, "error": str(e)[:200]}
 
     if dist is not None:
         tt = torch.tensor([total_ms, e2e_s, 0.0 if ok else 1.0], dtype=torch.float64, device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         total_ms, e2e_s, bad = float(tt[0]), float(tt[1]), float(tt[2])
         ok = bad == 0.0
-    value = n * world * args.steps / (total_ms * 1e-3)
-    e2e_value = n * world * e2e_steps / e2e_s
+    value = n_total * args.steps / (total_ms * 1e-3)
+    e2e_value = n_total * e2e_steps / e2e_s
 
-    line = None
+    rc = 0
     if rank == 0:
-        cfg = workload_config(args, world)
+        cfg = workload_config(args, world, n_total)
         cfg["model_states"] = bundle.n_states
-        cfg["teams_per_launch"] = None
+        big = D.smem_bytes > 48 * 1024
+        cfg["rows_on_rank_0"] = n
+        cfg["waves_per_gpu"] = round(n / (148 * 2), 2) if big else None
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "metric": metric_name(args), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": cfg, "clocks": clocks, "gpu_launches": args.steps,   # pbgpu_solve_kernel launches inside the timed region of `value`
             "all_integrations_succeeded": ok,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "steps": e2e_steps, "kernel_ms_last": e2e_kernel_ms,
                     "call": "BatchedIDASolver.solve(t_eval, inputs=[{...}]*n, t_interp) -> list[Solution]"},
+            "e2e_full_state": e2e_full,
             "full_state": full_state,
             "gpu_ida_counters_mean": dict(zip(("nsteps", "nrevals", "nlinsetups", "netfails", "nniters", "nncfails", "njevals", "nge"),
                                               stats_gpu.tolist())),
+            "reference_install": reference_install_probe(),
         }
-        # ---- roofline + CPU baseline (rank 0) -------------------------------------------------------------
+        # ---- roofline + CPU baseline + parity (rank 0) ----------------------------------------------------
         cores = os.cpu_count() or 1
         peak_tf = measure_fp64_peak(local_rank)
         n_cpu = min(args.cpu_sample, n) if world == 1 else min(4 * cores, n)
-        ref, cpu_s = run_cpu_oracle(bundle, p[:n_cpu], cores)
-        stats_ref = ref["stats"].astype(np.float64).mean(axis=0)
-        w, terms = work_model(D, stats_ref, float(np.mean(ref["n_out"])), bundle.n_states)
+        base, cpu_s = run_cpu(cpu_oracle(bundle, fast=True), p[:n_cpu], cores, "sparse")
+        stats_ref = base["stats"].astype(np.float64).mean(axis=0)
+        w, terms = work_model(D, stats_ref, float(np.mean(base["n_out"])), bundle.n_states)
         kernel_s = (total_ms / args.steps) * 1e-3
         achieved_tf = w * n / kernel_s / 1e12
         alg_bytes = 8.0 * (p.shape[1] + float(np.mean(n_t)) * (1 + D.n_vars)) + 8
@@ -410,7 +535,7 @@ def run_b200_arm(args):
         except Exception:
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-        traffic, traffic_src = ncu_dram_traffic(n)
+        traffic, traffic_src = ncu_dram_traffic(n) if args.model == "dfn" else (None, "no capture for this model")
         line["roofline"] = {
             "bound": "fp64", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
             "traffic": traffic, "traffic_source": traffic_src, "kernel": "pbgpu_solve_kernel", "flop_per_simulation": w,
@@ -421,32 +546,62 @@ def run_b200_arm(args):
                     "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)",
                     "bytes_per_simulation": alg_bytes},
         }
-        # parity of the GPU results against the oracle on the sampled systems
-        y_host, t_host = d_y[:n_cpu].cpu().numpy(), d_t[:n_cpu].cpu().numpy()
-        wv = wt = wk = 0.0
-        agree = True
-        for i in range(n_cpu):
-            k = int(n_t[i])
-            if k != len(ref["t"][i]) or int(flags[i]) != int(ref["flag"][i]):
-                agree = False
-                continue
-            m = k - 1 if flags[i] == 2 else k
-            dv = np.abs(y_host[i, :m, 0] - ref["y"][i][:m, 0])
-            wv = max(wv, float(np.max(dv)))
-            # the same without the last grid point before a voltage cut-off: on that knee |dV/dt| is ~100x larger and two
-            # integrations at rtol = atol = 1e-8 differ by more than 1e-6 V from EACH OTHER'S tighter-tolerance limit
-            wk = max(wk, float(np.max(dv[:m - 1]))) if flags[i] == 2 and m > 1 else max(wk, float(np.max(dv)))
-            wt = max(wt, abs(float(t_host[i, k - 1]) - float(ref["t"][i][-1])))
-        line["parity_vs_oracle"] = {"systems": n_cpu, "max_abs_dV": wv, "max_abs_dV_before_the_cutoff_knee": wk,
-                                    "max_abs_dt_end": wt, "same_termination": agree, "bars": {"dV": 1e-6, "dt": 1e-3}}
+        n_par = min(args.parity_sample, n) if world == 1 else min(2 * cores, n)
+        y_host, t_host = d_y[:n_par].cpu().numpy(), d_t[:n_par].cpu().numpy()
+        t_end = np.array([t_host[i, int(n_t[i]) - 1] for i in range(n_par)])
+        par, _ = parity_block(bundle, p, n_t, flags, y_host[:, :, 0], t_end, n_par, cores)
+        line["parity"] = par
+        line["parity_ok"] = bool(par["ok"] and ok)
         if world == 1:
             line["cpu_baseline"] = {"value": n_cpu / cpu_s, "unit": UNIT, "cores": cores, "kind": "port",
-                                    "sample": f"first {n_cpu} of the {n} input sets, one pass",
-                                    "note": "CPU oracle (IDA restatement + banded LU), OpenMP over systems; not IDAKLU"}
+                                    "sample": f"first {n_cpu} of the {n} input sets, one pass", "note": CPU_NOTE}
         print(json.dumps(line), flush=True)
+        if not line["parity_ok"]:
+            print("bench.py: PARITY BAR EXCEEDED (see `parity` in the line above)", file=sys.stderr, flush=True)
+            rc = 3
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+    return rc
+
+
+def run_inproc_arm(args):
+    """What north_star describes literally: ONE process, ONE BatchedIDASolver(devices=range(N)).solve(inputs=[...]) call; the
+    batch (args.n_sys sets in total) is sharded over the N GPUs by host threads, results gathered on the host."""
+    import torch
+
+    from pybamm_b200 import BatchedIDASolver, build
+
+    n_dev = args.inproc_devices
+    if torch.cuda.device_count() < n_dev:
+        raise SystemExit(f"bench.py: --inproc-devices {n_dev} but only {torch.cuda.device_count()} CUDA devices")
+    bundle = build.load_bundle(args.model)
+    p = sample_inputs(bundle, args.n_sys, np.random.default_rng(20260))
+    inputs_list = [dict(zip(bundle.input_names, (float(x) for x in row))) for row in p]
+    solver = BatchedIDASolver(bundle, rtol=RTOL, atol=ATOL, output_variables=["Voltage [V]"], devices=list(range(n_dev)),
+                              on_failure="ignore", reuse_buffers=True)
+    for _ in range(max(1, min(args.warmup, 2))):
+        sols = solver.solve(T_EVAL, inputs=inputs_list, t_interp=T_INTERP)
+    steps = max(1, min(args.steps, 5))
+    sampler = ClockSampler(0)
+    sampler.start()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        sols = solver.solve(T_EVAL, inputs=inputs_list, t_interp=T_INTERP)
+        _ = float(sols[-1]["Voltage [V]"][-1, 0])
+    dt = time.perf_counter() - t0
+    clocks = sampler.stop()
+    cfg = workload_config(args, n_dev, args.n_sys)
+    cfg["model_states"] = bundle.n_states
+    cfg["sharding"] = f"one process, {n_dev} device(s), one host thread per device (BatchedIDASolver(devices=...))"
+    value = args.n_sys * steps / dt
+    line = {"metric": metric_name(args), "value": value, "unit": UNIT, "n_gpus": n_dev, "steps": steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": cfg, "clocks": clocks, "gpu_launches": steps * n_dev, "impl": "b200-inproc",
+            "e2e": {"value": value, "unit": UNIT, "kernel_ms_last_max_over_devices": solver.last_kernel_ms,
+                    "call": f"BatchedIDASolver(devices=range({n_dev})).solve(t_eval, inputs=[{{...}}]*{args.n_sys}, t_interp)"},
+            "all_integrations_succeeded": bool(all(s.flag in (1, 2) for s in sols))}
+    print(json.dumps(line), flush=True)
     return 0
 
 
@@ -457,16 +612,19 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--model", default="dfn", choices=["spm", "spme", "dfn"])
-    ap.add_argument("--n-sys", type=int, default=10000, help="input sets per GPU")
+    ap.add_argument("--n-sys", type=int, default=10000, help="input sets per GPU (weak) or in total (strong, in-process)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--inproc-devices", type=int, default=0, help="run the one-process multi-device arm on this many GPUs")
     ap.add_argument("--cpu-sample", type=int, default=1024, help="systems of the cpu_baseline / work-model sample")
-    ap.add_argument("--cpu-sample-max", type=int, default=2048)
-    ap.add_argument("--no-full-state", action="store_true", help="skip the full-state (output_mode 0) secondary number")
+    ap.add_argument("--parity-sample", type=int, default=256, help="systems compared with the oracle at 1e-8 and 1e-11")
+    ap.add_argument("--cpu-budget-s", type=float, default=150.0, help="--impl reference: time budget of the timed steps")
+    ap.add_argument("--full-state-e2e", type=int, default=1000, help="rows of the full-state end-to-end number (0: skip)")
+    ap.add_argument("--no-full-state", action="store_true", help="skip the full-state (output_mode 0) secondary numbers")
     args = ap.parse_args()
-    global METRIC
-    if args.model != "dfn":
-        METRIC = f"{args.model.upper()} simulations/sec ({args.n_sys} input sets)"
     if args.impl == "reference":
         return run_reference_arm(args)
+    if args.inproc_devices > 0:
+        return run_inproc_arm(args)
     return run_b200_arm(args)
 
 

@@ -153,6 +153,98 @@ static void dense_solve(const double* a, int n, const int* ipiv, double* b) {
   }
 }
 
+/* ------------------------------------------------------------------ static-pattern sparse LU (CPU baseline leg)
+ * What SUNLinSol_KLU does in steady state (IDAKLUSolverOpenMP_solvers.hpp:29-33): the fill-reducing ordering and the
+ * pivot sequence are fixed once (klu_analyze + the first klu_factor), every later set-up is a klu_refactor -- a numeric
+ * factorisation on the frozen pattern with no pivot search.  Here the ordering (row / column permutations) comes from
+ * pybamm_b200.symbolic_lu, the same one the device uses; the symbolic fill is recomputed below and the numeric phase
+ * is the row-wise (IKJ) elimination on CSR.  lu_mode 1 of pbo_solve; the banded LU with partial pivoting above stays
+ * the checker's linear solver (lu_mode 0). */
+typedef struct {
+  int n, nnz;
+  int *rp, *ci, *dg;     /* CSR of L+U in permuted numbering, columns ascending; dg[i] = position of the diagonal */
+  double *v, *w;         /* values; dense work row */
+  int* a_pos;            /* position in v of every structural entry of J - cj M */
+  int *ipr, *ipc;        /* old row -> new row, old column -> new column */
+  const int *pr, *pc;    /* new -> old */
+} splu_t;
+
+static void splu_init(splu_t* L, int n, int nnz_a, const int* rows, const int* cols, const int* perm_r, const int* perm_c) {
+  L->n = n; L->pr = perm_r; L->pc = perm_c;
+  L->ipr = (int*)malloc(sizeof(int) * n); L->ipc = (int*)malloc(sizeof(int) * n);
+  for (int i = 0; i < n; i++) { L->ipr[perm_r[i]] = i; L->ipc[perm_c[i]] = i; }
+  /* pattern of the permuted matrix, row by row, then symbolic fill: row i gains the U pattern of every row k < i it holds */
+  char* in = (char*)calloc((size_t)n * n, 1);     /* n <= a few thousand: a dense bitmap is the simplest exact symbolic phase */
+  for (int k = 0; k < nnz_a; k++) in[(size_t)L->ipr[rows[k]] * n + L->ipc[cols[k]]] = 1;
+  for (int i = 0; i < n; i++) in[(size_t)i * n + i] = 1;
+  for (int i = 0; i < n; i++) {
+    char* ri = in + (size_t)i * n;
+    for (int k = 0; k < i; k++)
+      if (ri[k]) {
+        const char* rk = in + (size_t)k * n;
+        for (int j = k + 1; j < n; j++) ri[j] |= rk[j];
+      }
+  }
+  L->rp = (int*)malloc(sizeof(int) * (n + 1)); L->dg = (int*)malloc(sizeof(int) * n);
+  int nnz = 0;
+  for (size_t q = 0; q < (size_t)n * n; q++) nnz += in[q];
+  L->nnz = nnz;
+  L->ci = (int*)malloc(sizeof(int) * nnz); L->v = (double*)calloc(nnz, sizeof(double)); L->w = (double*)calloc(n, sizeof(double));
+  int p = 0;
+  for (int i = 0; i < n; i++) {
+    L->rp[i] = p;
+    for (int j = 0; j < n; j++)
+      if (in[(size_t)i * n + j]) { if (j == i) L->dg[i] = p; L->ci[p++] = j; }
+  }
+  L->rp[n] = p;
+  L->a_pos = (int*)malloc(sizeof(int) * (nnz_a > 0 ? nnz_a : 1));
+  for (int k = 0; k < nnz_a; k++) {
+    const int i = L->ipr[rows[k]], j = L->ipc[cols[k]];
+    int lo = L->rp[i], hi = L->rp[i + 1] - 1;
+    while (lo < hi) { int mid = (lo + hi) >> 1; if (L->ci[mid] < j) lo = mid + 1; else hi = mid; }
+    L->a_pos[k] = lo;
+  }
+  free(in);
+}
+static void splu_free(splu_t* L) {
+  free(L->rp); free(L->ci); free(L->dg); free(L->v); free(L->w); free(L->a_pos); free(L->ipr); free(L->ipc);
+}
+/* numeric factorisation of the values scattered into L->v; the diagonal of U is stored inverted */
+static int splu_factor(splu_t* L) {
+  const int n = L->n;
+  double* w = L->w;
+  for (int i = 0; i < n; i++) {
+    const int p0 = L->rp[i], p1 = L->rp[i + 1], pd = L->dg[i];
+    for (int p = p0; p < p1; p++) w[L->ci[p]] = L->v[p];
+    for (int p = p0; p < pd; p++) {
+      const int k = L->ci[p];
+      const double l = w[k] * L->v[L->dg[k]];
+      w[k] = l;
+      if (l != 0.0)
+        for (int q = L->dg[k] + 1; q < L->rp[k + 1]; q++) w[L->ci[q]] -= l * L->v[q];
+    }
+    const double d = w[i];
+    if (d == 0.0 || !(d == d)) return i + 1;
+    for (int p = p0; p < p1; p++) L->v[p] = w[L->ci[p]];
+    L->v[pd] = 1.0 / d;
+  }
+  return 0;
+}
+static void splu_solve(const splu_t* L, const double* b, double* x, double* work) {
+  const int n = L->n;
+  for (int i = 0; i < n; i++) {
+    double s = b[L->pr[i]];
+    for (int p = L->rp[i]; p < L->dg[i]; p++) s -= L->v[p] * work[L->ci[p]];
+    work[i] = s;
+  }
+  for (int i = n - 1; i >= 0; i--) {
+    double s = work[i];
+    for (int p = L->dg[i] + 1; p < L->rp[i + 1]; p++) s -= L->v[p] * work[L->ci[p]];
+    work[i] = s * L->v[L->dg[i]];
+  }
+  for (int j = 0; j < n; j++) x[L->pc[j]] = work[j];
+}
+
 /* ------------------------------------------------------------------ solver state */
 typedef struct {
   const pbo_model* m;
@@ -164,7 +256,7 @@ typedef struct {
   /* IDA memory */
   double* phi[MXORDP1];
   double psi[MXORDP1], alpha[MXORDP1], beta[MXORDP1], sigma[MXORDP1], gamma[MXORDP1];
-  double *ewt, *ee, *delta, *yypredict, *yppredict, *yy, *yp, *tempv, *savres, *jacv, *tmp, *bw;
+  double *ewt, *ee, *delta, *yypredict, *yppredict, *yy, *yp, *tempv, *tempv2, *savres, *jacv, *tmp, *bw;
   double *p;
   double tn, hh, hused, cj, cjlast, cjold, cjratio, ss, rr, epsNewt, toldel, hmax_inv;
   int kk, kused, knew, phase, ns;
@@ -174,8 +266,9 @@ typedef struct {
   /* roots */
   double *glo, *ghi, *grout; int* gactive; int* iroots; double tlo, thi, trout, ttol;
   int irfnd;
-  /* linear solver */
+  /* linear solver: banded + partial pivoting (checker) or static-pattern sparse (baseline leg) */
   band_t B;
+  splu_t SP; int lu_mode;
   /* IC */
   double *Jaa; int* ipiv_a; double *xa, *xsave, *resa, *dela, *ewta;
   /* stats: nsteps nrevals nlinsetups netfails nniters nncfails njevals nge */
@@ -209,19 +302,29 @@ static int lsetup(ida_t* S, double t, const double* y) {
   const pbo_model* m = S->m;
   m->jac(y, S->p, t, S->cj, S->jacv, S->tmp);
   S->st[ST_NJE]++;
+  S->st[ST_NSETUPS]++;
+  if (S->lu_mode) {
+    memset(S->SP.v, 0, sizeof(double) * (size_t)S->SP.nnz);
+    for (int k = 0; k < m->nnz; k++) S->SP.v[S->SP.a_pos[k]] += S->jacv[k];
+    return splu_factor(&S->SP);
+  }
   memset(S->B.a, 0, sizeof(double) * (size_t)S->n * S->B.W);
   for (int k = 0; k < m->nnz; k++) {
     int i = S->iperm[m->jac_rows[k]], j = S->iperm[m->jac_cols[k]];
     BA(&S->B, i, j) += S->jacv[k];
   }
-  S->st[ST_NSETUPS]++;
   return band_factor(&S->B);
 }
 static void lsolve(ida_t* S, double* b) {
-  /* permute, solve, un-permute */
-  for (int i = 0; i < S->n; i++) S->bw[S->iperm[i]] = b[i];
-  band_solve(&S->B, S->bw);
-  for (int i = 0; i < S->n; i++) b[i] = S->bw[S->iperm[i]];
+  if (S->lu_mode) {
+    splu_solve(&S->SP, b, S->tempv2, S->bw);
+    memcpy(b, S->tempv2, sizeof(double) * S->n);
+  } else {
+    /* permute, solve, un-permute */
+    for (int i = 0; i < S->n; i++) S->bw[S->iperm[i]] = b[i];
+    band_solve(&S->B, S->bw);
+    for (int i = 0; i < S->n; i++) b[i] = S->bw[S->iperm[i]];
+  }
   if (S->opt.scalesol && S->cjratio != 1.0) {
     double f = 2.0 / (1.0 + S->cjratio);
     for (int i = 0; i < S->n; i++) b[i] *= f;
@@ -842,7 +945,8 @@ static int solve_one(ida_t* S, const double* t_eval, int n_eval, const double* t
 }
 
 /* ------------------------------------------------------------------ allocation + batch entry point */
-static ida_t* ida_alloc(const pbo_model* m, const pbo_options* opt, const double* atol, const int* perm) {
+static ida_t* ida_alloc(const pbo_model* m, const pbo_options* opt, const double* atol, const int* perm, const int* perm_c,
+                        int lu_mode) {
   ida_t* S = (ida_t*)calloc(1, sizeof(ida_t));
   const int n = m->n;
   S->m = m; S->opt = *opt; S->atol = atol; S->perm = perm; S->n = n;
@@ -850,7 +954,7 @@ static ida_t* ida_alloc(const pbo_model* m, const pbo_options* opt, const double
   S->iperm = (int*)malloc(sizeof(int) * n);
   for (int i = 0; i < n; i++) S->iperm[perm ? perm[i] : i] = i;
   for (int j = 0; j < MXORDP1; j++) S->phi[j] = (double*)calloc(n, sizeof(double));
-  double** vecs[] = {&S->ewt, &S->ee, &S->delta, &S->yypredict, &S->yppredict, &S->yy, &S->yp, &S->tempv, &S->savres, &S->bw};
+  double** vecs[] = {&S->ewt, &S->ee, &S->delta, &S->yypredict, &S->yppredict, &S->yy, &S->yp, &S->tempv, &S->tempv2, &S->savres, &S->bw};
   for (unsigned k = 0; k < sizeof(vecs) / sizeof(vecs[0]); k++) *vecs[k] = (double*)calloc(n, sizeof(double));
   S->jacv = (double*)calloc(m->nnz > 0 ? m->nnz : 1, sizeof(double));
   S->tmp = (double*)calloc(m->n_tmp > 0 ? m->n_tmp : 1, sizeof(double));
@@ -858,6 +962,8 @@ static ida_t* ida_alloc(const pbo_model* m, const pbo_options* opt, const double
   int ne = m->n_ev > 0 ? m->n_ev : 1;
   S->glo = (double*)calloc(ne, sizeof(double)); S->ghi = (double*)calloc(ne, sizeof(double)); S->grout = (double*)calloc(ne, sizeof(double));
   S->gactive = (int*)calloc(ne, sizeof(int)); S->iroots = (int*)calloc(ne, sizeof(int));
+  S->lu_mode = (lu_mode && perm && perm_c) ? 1 : 0;
+  if (S->lu_mode) splu_init(&S->SP, n, m->nnz, m->jac_rows, m->jac_cols, perm, perm_c);
   /* band widths of the permuted pattern */
   int kl = 0, ku = 0;
   for (int k = 0; k < m->nnz; k++) {
@@ -865,6 +971,7 @@ static ida_t* ida_alloc(const pbo_model* m, const pbo_options* opt, const double
     if (i - j > kl) kl = i - j;
     if (j - i > ku) ku = j - i;
   }
+  if (S->lu_mode) kl = ku = 0;   /* the band store is not used */
   S->B.n = n; S->B.kl = kl; S->B.ku = ku; S->B.W = 2 * kl + ku + 1;
   S->B.a = (double*)calloc((size_t)n * S->B.W, sizeof(double));
   S->B.ipiv = (int*)calloc(n, sizeof(int));
@@ -881,7 +988,8 @@ static void ida_free(ida_t* S) {
   free(S->ewt); free(S->ee); free(S->delta); free(S->yypredict); free(S->yppredict); free(S->yy); free(S->yp);
   free(S->tempv); free(S->savres); free(S->bw); free(S->jacv); free(S->tmp); free(S->p);
   free(S->glo); free(S->ghi); free(S->grout); free(S->gactive); free(S->iroots);
-  free(S->B.a); free(S->B.ipiv); free(S->iperm);
+  free(S->B.a); free(S->B.ipiv); free(S->iperm); free(S->tempv2);
+  if (S->lu_mode) splu_free(&S->SP);
   free(S->Jaa); free(S->ipiv_a); free(S->xa); free(S->xsave); free(S->resa); free(S->dela); free(S->ewta);
   free(S);
 }
@@ -896,7 +1004,7 @@ static void ida_free(ida_t* S) {
 int pbo_solve(int n_sys, const double* t_eval, int n_eval, const double* t_interp, int n_interp,
               const double* inputs, const double* y0, const double* atol, const pbo_options* opt, const int* perm,
               int save_vars, int n_max, double* t_out, double* y_out, int* n_out, int* flag, double* y_term,
-              long* stats, int n_threads) {
+              long* stats, int n_threads, const int* perm_c, int lu_mode) {
   const pbo_model* m = pbo_get_model();
   if (n_eval < 2) return -1;
   const int n_ret = save_vars ? m->n_var : m->n;
@@ -905,7 +1013,7 @@ int pbo_solve(int n_sys, const double* t_eval, int n_eval, const double* t_inter
 #endif
 #pragma omp parallel
   {
-    ida_t* S = ida_alloc(m, opt, atol, perm);
+    ida_t* S = ida_alloc(m, opt, atol, perm, perm_c, lu_mode);
 #pragma omp for schedule(dynamic, 1)
     for (int s = 0; s < n_sys; s++) {
       for (int k = 0; k < m->n_p; k++) S->p[k] = inputs[(size_t)s * m->n_p + k];

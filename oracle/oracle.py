@@ -36,6 +36,7 @@ class Oracle:
         self.lib.pbo_default_options.argtypes = [C.POINTER(Options)]
         self.lib.pbo_solve.restype = C.c_int
         self.perm = None
+        self.perm_r = self.perm_c = None
 
     def set_rcm(self, rows, cols):
         """Bandwidth-reducing symmetric permutation for the banded LU."""
@@ -45,6 +46,11 @@ class Oracle:
         A = sp.csr_matrix((np.ones(len(rows)), (rows, cols)), shape=(self.n, self.n))
         A = (A + A.T).tocsr()
         self.perm = np.ascontiguousarray(reverse_cuthill_mckee(A, symmetric_mode=True), dtype=np.int32)
+
+    def set_sparse(self, perm_r, perm_c):
+        """Row / column order of the static-pattern sparse LU (lu="sparse": the CPU-baseline leg; pybamm_b200.symbolic_lu)."""
+        self.perm_r = np.ascontiguousarray(perm_r, dtype=np.int32)
+        self.perm_c = np.ascontiguousarray(perm_c, dtype=np.int32)
 
     def eval(self, which, y, p, t=0.0, cj=0.0):
         idx = {"res": 0, "jac": 1, "events": 2, "ic": 3, "vars": 4}[which]
@@ -56,7 +62,7 @@ class Oracle:
         return out
 
     def solve(self, t_eval, inputs, t_interp=None, rtol=1e-4, atol=1e-6, y0=None, save_vars=False, n_threads=1,
-              n_max=None, options=None):
+              n_max=None, options=None, lu="band"):
         """Returns dict(t [list of arrays], y [list of (n_t, n_ret)], flag, y_term, stats)."""
         t_eval = np.unique(np.asarray(t_eval, dtype=np.float64))
         t_interp = np.zeros(0) if t_interp is None else np.unique(np.asarray(t_interp, dtype=np.float64))
@@ -82,15 +88,20 @@ class Oracle:
         stats = np.zeros((n_sys, 8), np.int64)
         vp = C.c_void_p
         self.lib.pbo_solve.argtypes = [C.c_int, _dp, C.c_int, vp, C.c_int, _dp, vp, _dp, C.POINTER(Options), vp,
-                                       C.c_int, C.c_int, _dp, _dp, _ip, _ip, _dp, _lp, C.c_int]
+                                       C.c_int, C.c_int, _dp, _dp, _ip, _ip, _dp, _lp, C.c_int, vp, C.c_int]
+        sparse = lu == "sparse"
+        if sparse and self.perm_r is None:
+            raise ValueError("set_sparse(perm_r, perm_c) first")
+        perm = self.perm_r if sparse else self.perm
         y0p = None
         if y0 is not None:
             y0 = np.ascontiguousarray(np.atleast_2d(np.asarray(y0, dtype=np.float64)))
             y0p = y0.ctypes.data_as(vp)
         rc = self.lib.pbo_solve(n_sys, t_eval, len(t_eval), t_interp.ctypes.data_as(vp) if len(t_interp) else None,
                                 len(t_interp), inputs, y0p, atol_v, C.byref(opt),
-                                self.perm.ctypes.data_as(vp) if self.perm is not None else None,
-                                int(save_vars), n_max, t_out, y_out, n_out, flag, y_term, stats, n_threads)
+                                perm.ctypes.data_as(vp) if perm is not None else None,
+                                int(save_vars), n_max, t_out, y_out, n_out, flag, y_term, stats, n_threads,
+                                self.perm_c.ctypes.data_as(vp) if sparse else None, int(sparse))
         if rc != 0:
             raise ValueError("t_eval must have at least 2 entries")
         return dict(t=[t_out[i, :n_out[i]] for i in range(n_sys)], y=[y_out[i, :n_out[i]] for i in range(n_sys)],

@@ -64,22 +64,47 @@ def generate(bundle: ModelBundle, dialect: str, outdir=BUILD, tag=""):
     return path, info
 
 
-def build_oracle(bundle: ModelBundle, force=False):
-    """Compile the CPU oracle for a bundle (tests / bench cpu_baseline only)."""
+def build_oracle(bundle: ModelBundle, force=False, fast=False):
+    """Compile the CPU oracle for a bundle (tests / bench cpu_baseline only).
+    fast: the CPU-baseline build (-O3 -march=native: compiled on the machine that runs it, never shipped)."""
     outdir = os.path.join(ORACLE, "_build")
     os.makedirs(outdir, exist_ok=True)
     header, _ = generate(bundle, "c", outdir)
-    out = os.path.join(outdir, f"oracle_{bundle.name}.so")
-    srcs = [os.path.join(ORACLE, f) for f in ("ida_oracle.c", "model_shim.c", "pbo_model.h")] + [header]
+    out = os.path.join(outdir, f"oracle_{bundle.name}{'_fast' if fast else ''}.so")
+    srcs = [os.path.join(ORACLE, f) for f in ("ida_oracle.c", "model_shim.c", "pbo_model.h", "Makefile")] + [header]
     stamp = out + ".stamp"
     dig = _src_digest(srcs)
+    if fast:
+        import platform
+
+        cpu = ""
+        try:
+            cpu = next(ln for ln in open("/proc/cpuinfo") if ln.startswith("model name")).strip()
+        except Exception:
+            pass
+        dig += hashlib.sha256((platform.machine() + cpu).encode()).hexdigest()[:8]
     if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:
         return out
-    cmd = ["make", "-s", "-C", ORACLE, "-B", f"MODEL={bundle.name}", f"HEADER={header}", f"OUT={out}"]
+    cmd = ["make", "-s", "-C", ORACLE, "-B", f"MODEL={bundle.name}", f"HEADER={header}", f"OUT={out}"] + (["FAST=1"] if fast else [])
     subprocess.run(cmd, check=True)
     with open(stamp, "w") as f:
         f.write(dig)
     return out
+
+
+def lu_order(bundle: ModelBundle):
+    """(perm_r, perm_c) of the static sparse LU of a bundle: read from the code generator's record of the last build of
+    the model image (<name>_cuda.json), recomputed when there is none."""
+    path = os.path.join(BUILD, f"{bundle.name}_cuda.json")
+    try:
+        lu = json.load(open(path))["lu"]
+        return lu["perm_r"], lu["perm_c"]
+    except Exception:
+        from . import symbolic_lu as slu
+
+        sym = slu.analyse(bundle.n_states, bundle.jac_rows, bundle.jac_cols, codegen.sample_matrices(bundle),
+                          team=codegen.default_team(bundle.n_states))
+        return [int(x) for x in sym.perm_r], [int(x) for x in sym.perm_c]
 
 
 def build_model(bundle: ModelBundle, force=False, team=None, verbose=False, profile=False, tag="", defines=(), extra_flags=(),

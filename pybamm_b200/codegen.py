@@ -534,7 +534,8 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
                           est_cycles_solve=sym.est_cycles_solve, est_cycles_factor=sym.est_cycles_factor,
                           flops_factor=sym.flops_factor, flops_solve=sym.flops_solve,
                           seq_clusters=sym.seq_info["clusters"], seq_fwd_heights=sym.seq_info["fwd_heights"],
-                          seq_bwd_heights=sym.seq_info["bwd_heights"], seq_team_min=sym.seq_info["team_min"])
+                          seq_bwd_heights=sym.seq_info["bwd_heights"], seq_team_min=sym.seq_info["team_min"],
+                          perm_r=[int(x) for x in sym.perm_r], perm_c=[int(x) for x in sym.perm_c])
     else:
         rows = ", ".join(str(int(r)) for r in bundle.jac_rows)
         cols = ", ".join(str(int(c)) for c in bundle.jac_cols)
