@@ -294,9 +294,14 @@ def parity_block(bundle, p, n_t, flags, v_gpu, t_end_gpu, n_par, cores):
     o = cpu_oracle(bundle, fast=False)
     ref, _ = run_cpu(o, p[:n_par], cores, "band")
     tru, _ = run_cpu(o, p[:n_par], cores, "sparse", tol=1e-11)
-    redo = np.nonzero(tru["flag"] < 0)[0]          # 1e-11 is at the edge of what the first step's error test accepts
-    if len(redo):
-        again, _ = run_cpu(o, np.ascontiguousarray(p[:n_par][redo]), cores, "band", tol=1e-10)
+    # 1e-11 is beyond what the first step's error test accepts for a few input sets (the algebraic states move at O(1) V/s
+    # right after the current step; IDA's first-order predictor for them costs h <= rtol |y| / |dy/dt|): those fall back to
+    # 1e-10, then 1e-9
+    for tol in (1e-10, 1e-9):
+        redo = np.nonzero(tru["flag"] < 0)[0]
+        if not len(redo):
+            break
+        again, _ = run_cpu(o, np.ascontiguousarray(p[:n_par][redo]), cores, "sparse", tol=tol)
         for k, i in enumerate(redo):
             for key in ("t", "y"):
                 tru[key][i] = again[key][k]
