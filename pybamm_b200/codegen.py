@@ -414,7 +414,10 @@ def emit_solve_program(sym: slu.SymbolicLU) -> str:
 
 
 def default_team(n_states: int) -> int:
-    """Threads per system: one warp for small models, a CTA of several warps for large ones."""
+    """Threads per system: one warp for small models, a CTA of several warps for large ones.  PBGPU_TEAM overrides (A/B runs)."""
+    env = __import__("os").environ.get("PBGPU_TEAM")
+    if env:
+        return int(env)
     if n_states <= 128:
         return 32
     if n_states <= 512:

@@ -88,11 +88,13 @@
 #else
 #define PB_OFF_END0 PB_OFF_FAC
 #endif
-// Large models: the correction ee, read and written by every Newton iteration, stays in shared memory as well; the
-// history, the predictors, the error weights and the Jacobian temporaries are the ones streamed from L2.
+// Large models: the correction ee and the error weights ewt, read by every Newton iteration and every norm, stay in
+// shared memory as well; the history, the predictors and the Jacobian temporaries are the ones streamed from L2.
+// (DFN: 113.9 KB per team; two teams and their 1 KB reservations still fit the 228 KB of an SM.)
 #if PB_GLOBAL_VEC
 #define PB_OFF_EE PB_OFF_END0
-#define PB_SMEM_DOUBLES (PB_OFF_EE + PBM_N)
+#define PB_OFF_EWT_S (PB_OFF_EE + PBM_N)
+#define PB_SMEM_DOUBLES (PB_OFF_EWT_S + PBM_N)
 #else
 #define PB_SMEM_DOUBLES PB_OFF_END0
 #endif
@@ -102,7 +104,11 @@
 // compile-time constant (elements per thread), the body is fully unrolled and guarded.  The streamed vectors of the
 // large models live in L2 (PB_GLOBAL_VEC): a pass then costs about one L2 round trip instead of one per element.
 #define PB_VPT ((PBM_N + PB_TEAM - 1) / PB_TEAM)
+#ifdef PB_VEC_ROLLED   /* A/B switch: rolled loops (a quarter of the code, one L2 round trip per trip) */
+#define PB_VEC_FOR(k, i) _Pragma("unroll 1") for (int k = 0, i = PB_TID; k < PB_VPT; k++, i += PB_TEAM)
+#else
 #define PB_VEC_FOR(k, i) _Pragma("unroll") for (int k = 0, i = PB_TID; k < PB_VPT; k++, i += PB_TEAM)
+#endif
 
 enum { PB_ST_NST, PB_ST_NRE, PB_ST_NSETUPS, PB_ST_NETF, PB_ST_NNI, PB_ST_NCFN, PB_ST_NJE, PB_ST_NGE };
 
@@ -129,11 +135,12 @@ struct pb_sys {
 };
 
 #define S_PHI(S, j) ((S).gv + PB_GOFF_PHI + (j) * PBM_N)
-#define S_EWT(S) ((S).gv + PB_GOFF_EWT)
 #if PB_GLOBAL_VEC
 #define S_EE(S) ((S).sm + PB_OFF_EE)
+#define S_EWT(S) ((S).sm + PB_OFF_EWT_S)
 #else
 #define S_EE(S) ((S).gv + PB_GOFF_EE)
+#define S_EWT(S) ((S).gv + PB_GOFF_EWT)
 #endif
 #define S_YYPRED(S) ((S).gv + PB_GOFF_YYPRED)
 #define S_YPPRED(S) ((S).gv + PB_GOFF_YPPRED)
@@ -937,6 +944,28 @@ static PB_DEV int pb_ewt_set(pb_sys& S, const double* y) {
   return pb_team_max(S.team, bad) != 0.0;
 }
 
+// ewt_set(y) and wrms(y) in one pass (IDASolve computes both from phi[0] before every step): returns the norm, NaN when
+// a weight is not positive.  Ends with a barrier.
+static PB_DEV double pb_ewt_set_norm(pb_sys& S, const double* y) {
+  double* PB_RESTRICT ewt = S_EWT(S);
+  double yv[PB_VPT], av[PB_VPT];
+  PB_VEC_FOR(k, i) {
+    yv[k] = (i < PBM_N) ? y[i] : 0.0;
+    av[k] = (i < PBM_N) ? PB_LD(S.atol[i]) : 1.0;
+  }
+  double acc = 0.0;
+  PB_VEC_FOR(k, i) {
+    const double w = S.rtol * fabs(yv[k]) + av[k];
+    if (!(w > 0.0)) acc = PB_NAN;
+    const double e = 1.0 / w;
+    if (i < PBM_N) ewt[i] = e;
+    const double v = yv[k] * e;
+    acc += v * v;
+  }
+  PB_SYNC();
+  return sqrt(pb_team_sum(S.team, acc) / PBM_N);
+}
+
 // ---- interpolation (IDAGetSolution / IDAGetDky k=0,1) ------------------------------------------
 struct pb_interp {
   double c[PB_MXORDP1], d[PB_MXORDP1];
@@ -1154,9 +1183,17 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
   double* ee = S_EE(S);
   double* delta = S_DELTA(S);
   double* yypred = S_YYPRED(S);
-  double* yppred = S_YPPRED(S);
   double* yy = S_YY(S);
   const double* ewt = S_EWT(S);
+  // What a thread needs of the streamed vectors inside the Newton loop stays in its registers: the predicted
+  // derivative of its rows and their places in the solve's permuted vector.  An iteration then touches global memory
+  // only inside the generated residual (tables): every L2 round trip here used to sit on the critical path.
+  double ypp[PB_VPT];
+  int ipr[PB_VPT], ipc[PB_VPT];
+  PB_VEC_FOR(k, i) {
+    ipr[k] = (i < PBM_N) ? (int)PB_LD(pbm_iperm_r[i]) : 0;
+    ipc[k] = (i < PBM_N) ? (int)PB_LD(pbm_iperm_c[i]) : 0;
+  }
   {  // phi -> phi* and predictor
     const double* beta = S_BETA(S);
     const double* gamma = S_GAMMA(S);
@@ -1190,9 +1227,11 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
           }
         }
         yypred[i] = a;
-        yppred[i] = b;
         ee[i] = 0.0;
         yy[i] = a;
+        ypp[k] = b;
+      } else {
+        ypp[k] = 0.0;
       }
     }
     PB_SYNC();
@@ -1228,17 +1267,12 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
         PB_STAT(S, PB_ST_NNI);
         // rhs = -F = -(f - M y'),  y' = yppred + cj * ee on the differential rows
         {
-          double yp[PB_VPT], ev[PB_VPT];
-          PB_VEC_FOR(k, i) {
-            yp[k] = (i < PBM_NDIFF) ? yppred[i] : 0.0;
-            ev[k] = (i < PBM_NDIFF) ? ee[i] : 0.0;
-          }
           double* PB_RESTRICT w = S_W(S);
           PB_VEC_FOR(k, i) {
             if (i < PBM_N) {
               double r = delta[i];
-              if (i < PBM_NDIFF) r -= yp[k] + S.cj * ev[k];
-              w[(int)PB_LD(pbm_iperm_r[i])] = -r;     // straight into the solve's permuted vector
+              if (i < PBM_NDIFF) r -= ypp[k] + S.cj * ee[i];
+              w[ipr[k]] = -r;     // straight into the solve's permuted vector
             }
           }
         }
@@ -1251,6 +1285,19 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
         const double scale = (S.scalesol && S.cjratio != 1.0) ? 2.0 / (1.0 + S.cjratio) : 1.0;
         double acc = 0.0;
         {
+#if PB_GLOBAL_VEC
+          // everything in shared memory: yy = yypred + ee is advanced by the same increment as ee
+          const double* PB_RESTRICT w = S_W(S);
+          PB_VEC_FOR(k, i) {
+            if (i < PBM_N) {
+              const double d = w[ipc[k]] * scale;
+              ee[i] += d;
+              yy[i] += d;
+              const double v = d * ewt[i];
+              acc += v * v;
+            }
+          }
+#else
           double ev[PB_VPT], pv[PB_VPT], wv[PB_VPT];
           PB_VEC_FOR(k, i) {
             ev[k] = (i < PBM_N) ? ee[i] : 0.0;
@@ -1260,7 +1307,7 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
           const double* PB_RESTRICT w = S_W(S);
           PB_VEC_FOR(k, i) {
             if (i < PBM_N) {
-              const double d = w[(int)PB_LD(pbm_iperm_c[i])] * scale;
+              const double d = w[ipc[k]] * scale;
               const double e = ev[k] + d;
               ee[i] = e;
               yy[i] = pv[k] + e;
@@ -1268,6 +1315,7 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
               acc += v * v;
             }
           }
+#endif
         }
         PB_SYNC();
         const double delnrm = sqrt(pb_team_sum(S.team, acc) / PBM_N);
@@ -1757,9 +1805,9 @@ static PB_DEV int pb_ida_solve_one_step(pb_sys& S, double tout, double* tret) {
       if ((S.tn + S.hh - S.tstop) * S.hh > 0.0) S.hh = (S.tstop - S.tn) * (1.0 - 4.0 * PB_UROUND);
     }
   }
-  if (S.nst > 0 && pb_ewt_set(S, S_PHI(S, 0))) return PB_IDA_ILL_INPUT;
   {
-    const double nrm = pb_wrms(S, S_PHI(S, 0));
+    const double nrm = (S.nst > 0) ? pb_ewt_set_norm(S, S_PHI(S, 0)) : pb_wrms(S, S_PHI(S, 0));
+    if (!(nrm == nrm)) return PB_IDA_ILL_INPUT;
     if (PB_UROUND * nrm > 1.0) return PB_IDA_TOO_MUCH_ACC;
   }
   const int sflag = pb_ida_step(S);

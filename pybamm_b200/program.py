@@ -30,7 +30,7 @@ from . import ir
 
 MERGE_INPUTS = bool(int(__import__("os").environ.get("PBGPU_MERGE_INPUTS", "1")))   # see extract(): input leaves are slots
 MATERIALISE_COST = 6      # DFMA-equivalents: shared sub-expressions at least this costly get a tmp slot
-SPLIT_COST = 40           # for functions with few roots: split big trees at nodes at least this costly
+SPLIT_COST = int(__import__("os").environ.get("PBGPU_SPLIT_COST", "120"))   # for functions with few roots: split big trees at nodes at least this costly
 FEW_ROOTS = 64
 
 

@@ -16,9 +16,8 @@ import numpy as np
 
 VARIANTS = [
     # tag, env of the code generator, -D defines, build_model keyword arguments
-    ("_x0nomerge", {"PBGPU_MERGE_INPUTS": "0"}, (), {}),
-    ("_x2redfn", {}, ("PB_TEAM_INLINE_RED=0",), {}),
     ("", {}, (), {}),
+    ("_rolled", {}, ("PB_VEC_ROLLED",), {}),
 ]
 
 
