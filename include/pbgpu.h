@@ -37,7 +37,7 @@ extern "C" {
 #endif
 
 #define PBGPU_QUEUE_WORDS (32 + 8 * 256)
-#define PBGPU_ABI_VERSION 4
+#define PBGPU_ABI_VERSION 5
 
 typedef struct pbgpu_model_s* pbgpu_model_t;
 typedef struct pbgpu_solver_s* pbgpu_solver_t;
@@ -155,6 +155,26 @@ int pbgpu_solve_device(pbgpu_solver_t solver, int n_sys, const double* t_eval, i
 int pbgpu_model_eval(pbgpu_solver_t solver, int which, int n_sys, const double* y, const double* p, double t,
                      double cj, const double* y2, double* out, int out_len);
 
+/*
+ * Observe the compiled output variables of a batch of solutions on the device: the batched counterpart of
+ * idaklu.observe / idaklu.observe_hermite_interp (idaklu_source/observe.cpp:319-354), which the reference calls once per
+ * variable and per solution from ProcessedVariable (processed_variable.py:90-297) through CasADi.
+ *   t [n_sys][n_max], y [n_sys][n_max][n_states], n_t [n_sys]: a result block of pbgpu_solve (output_mode 0)
+ *   yp [n_sys][n_max][n_states] or NULL, t_obs [n_obs] or NULL:
+ *     t_obs == NULL: out[s][i][:] = vars(t[s][i], y[s][i], p[s]) at the stored points i < n_t[s]   (observe; out rows: n_max)
+ *     t_obs != NULL: cubic Hermite interpolation of y between the stored points from (y, yp), then vars(t_obs[k], y(t_obs[k]), p[s])
+ *                    (observe_hermite_interp: interval j with t[j] <= t_obs[k] <= t[j+1], the last interval extrapolates; out
+ *                    rows: n_obs); yp is required
+ *   out [n_sys][n_rows][n_vars]
+ * pbgpu_observe takes host pointers, pbgpu_observe_device device pointers on the solver's device (no copies; stream as in
+ * pbgpu_solve_device).
+ */
+int pbgpu_observe(pbgpu_solver_t solver, int n_sys, int n_max, const int* n_t, const double* t, const double* y,
+                  const double* yp, const double* inputs, const double* t_obs, int n_obs, double* out);
+int pbgpu_observe_device(pbgpu_solver_t solver, int n_sys, int n_max, const int* n_t, const double* t, const double* y,
+                         const double* yp, const double* inputs, const double* t_obs, int n_obs, double* out, void* stream,
+                         int sync);
+
 const char* pbgpu_last_error(void);
 
 /* ---- interface between libpbgpu and a compiled model image (not for end users) ---- */
@@ -182,6 +202,18 @@ typedef struct {
   const int* order;     /* [n_sys] or NULL: the k-th system handed out by the queue is order[k] */
   pbgpu_options opt;
 } pbgpu_launch;
+
+typedef struct {
+  int n_sys, n_max, n_obs;   /* n_obs == 0: at the stored points */
+  const int* n_t;
+  const double* t;
+  const double* y;
+  const double* yp;
+  const double* inputs;
+  const double* t_obs;
+  double* out;
+  double* scratch;      /* as in pbgpu_launch */
+} pbgpu_observe_launch;
 
 typedef struct {
   int which, n_sys, out_len;

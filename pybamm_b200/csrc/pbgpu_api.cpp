@@ -34,6 +34,7 @@ typedef int (*describe_fn)(pbgpu_model_desc*);
 typedef int (*launch_fn)(const pbgpu_launch*, void*, int, char*, size_t);
 typedef int (*eval_fn)(const pbgpu_eval_launch*, void*, int, char*, size_t);
 typedef int (*plan_fn)(int, int*, char*, size_t);
+typedef int (*observe_fn)(const pbgpu_observe_launch*, void*, int, char*, size_t);
 
 struct DevBuf {
   void* p = nullptr;
@@ -62,6 +63,7 @@ struct pbgpu_model_s {
   launch_fn launch = nullptr;
   eval_fn eval = nullptr;
   plan_fn plan = nullptr;
+  observe_fn observe = nullptr;
   pbgpu_model_desc desc;
   std::string path;
 };
@@ -73,7 +75,7 @@ struct pbgpu_solver_s {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   DevBuf atol, t_eval, t_interp, inputs, y0, yp0, t_out, y_out, yp_out, n_out, flag, y_term, stats, event_idx, t_event, queue,
-      scratch_a, scratch_b, team_scratch, order;
+      scratch_a, scratch_b, team_scratch, order, ob_nt, ob_t, ob_y, ob_yp, ob_tobs, ob_out;
   int last_grid = 0;
   int order_n = 0;
 };
@@ -118,7 +120,8 @@ int pbgpu_model_load(const char* path, pbgpu_model_t* model) {
   m->launch = (launch_fn)dlsym(h, "pbgpu_image_launch");
   m->eval = (eval_fn)dlsym(h, "pbgpu_image_eval");
   m->plan = (plan_fn)dlsym(h, "pbgpu_image_plan");
-  if (!m->describe || !m->launch || !m->eval || !m->plan) {
+  m->observe = (observe_fn)dlsym(h, "pbgpu_image_observe");
+  if (!m->describe || !m->launch || !m->eval || !m->plan || !m->observe) {
     dlclose(h);
     delete m;
     return fail(std::string("pbgpu_model_load: '") + path + "' is not a pbgpu model image");
@@ -203,7 +206,7 @@ int pbgpu_solver_destroy(pbgpu_solver_t s) {
   if (s->stream) cudaStreamSynchronize(s->stream);
   DevBuf* bufs[] = {&s->atol, &s->t_eval, &s->t_interp, &s->inputs, &s->y0, &s->yp0, &s->t_out, &s->y_out, &s->yp_out,
                     &s->n_out, &s->flag, &s->y_term, &s->stats, &s->event_idx, &s->t_event, &s->queue, &s->scratch_a,
-                    &s->scratch_b, &s->team_scratch, &s->order};
+                    &s->scratch_b, &s->team_scratch, &s->order, &s->ob_nt, &s->ob_t, &s->ob_y, &s->ob_yp, &s->ob_tobs, &s->ob_out};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 4; i++)
     if (s->ev[i]) cudaEventDestroy(s->ev[i]);
@@ -381,6 +384,80 @@ int pbgpu_solve(pbgpu_solver_t s, int n_sys, const double* t_eval, int n_teval, 
   if (e != cudaSuccess) return cuda_fail("integration kernel", e);
   CK(cudaEventElapsedTime(&out->kernel_ms, s->ev[1], s->ev[2]));
   CK(cudaEventElapsedTime(&out->total_ms, s->ev[0], s->ev[3]));
+  return 0;
+}
+
+int pbgpu_observe_device(pbgpu_solver_t s, int n_sys, int n_max, const int* n_t, const double* t, const double* y,
+                         const double* yp, const double* inputs, const double* t_obs, int n_obs, double* out, void* stream,
+                         int sync) {
+  if (!s || !n_t || !t || !y || !out) return fail("pbgpu_observe: null argument");
+  if (n_sys < 1 || n_max < 1) return fail("pbgpu_observe: n_sys and n_max must be positive");
+  const pbgpu_model_desc& D = s->model->desc;
+  if (D.n_vars < 1) return fail("the model image has no compiled output variables");
+  if (D.n_inputs > 0 && !inputs) return fail("inputs has wrong number of dimensions. Expected 2 but got 0");
+  if (t_obs && n_obs < 1) return fail("pbgpu_observe: t_obs given but n_obs < 1");
+  if (t_obs && !yp) return fail("pbgpu_observe: Hermite interpolation needs yp (solve with the full state and adaptive steps)");
+  CK(cudaSetDevice(s->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  pbgpu_observe_launch O;
+  memset(&O, 0, sizeof(O));
+  O.n_sys = n_sys;
+  O.n_max = n_max;
+  O.n_obs = t_obs ? n_obs : 0;
+  O.n_t = n_t;
+  O.t = t;
+  O.y = y;
+  O.yp = yp;
+  O.inputs = inputs;
+  O.t_obs = t_obs;
+  O.out = out;
+  int teams = 0;
+  if (plan_launch(s, n_sys, &teams)) return 1;
+  O.scratch = (double*)s->team_scratch.p;
+  char err[512];
+  err[0] = 0;
+  if (s->model->observe(&O, (void*)st, teams, err, sizeof(err))) return fail(err);
+  if (sync) {
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return cuda_fail("observation kernel", e);
+  }
+  return 0;
+}
+
+int pbgpu_observe(pbgpu_solver_t s, int n_sys, int n_max, const int* n_t, const double* t, const double* y, const double* yp,
+                  const double* inputs, const double* t_obs, int n_obs, double* out) {
+  if (!s || !n_t || !t || !y || !out) return fail("pbgpu_observe: null argument");
+  if (n_sys < 1 || n_max < 1) return fail("pbgpu_observe: n_sys and n_max must be positive");
+  const pbgpu_model_desc& D = s->model->desc;
+  if (D.n_vars < 1) return fail("the model image has no compiled output variables");
+  if (t_obs && !yp) return fail("pbgpu_observe: Hermite interpolation needs yp (solve with the full state and adaptive steps)");
+  for (int i = 1; t_obs && i < n_obs; i++)
+    if (!(t_obs[i] >= t_obs[i - 1])) return fail("pbgpu_observe: t_obs must be sorted");
+  CK(cudaSetDevice(s->device));
+  const size_t N = D.n_states, rows = t_obs ? (size_t)n_obs : (size_t)n_max;
+  const size_t np = D.n_inputs > 0 ? D.n_inputs : 1;
+  if (s->ob_nt.ensure(sizeof(int) * n_sys)) return 1;
+  if (s->ob_t.ensure(sizeof(double) * (size_t)n_sys * n_max)) return 1;
+  if (s->ob_y.ensure(sizeof(double) * (size_t)n_sys * n_max * N)) return 1;
+  if (yp && s->ob_yp.ensure(sizeof(double) * (size_t)n_sys * n_max * N)) return 1;
+  if (t_obs && s->ob_tobs.ensure(sizeof(double) * n_obs)) return 1;
+  if (s->inputs.ensure(sizeof(double) * (size_t)n_sys * np)) return 1;
+  if (s->ob_out.ensure(sizeof(double) * (size_t)n_sys * rows * D.n_vars)) return 1;
+  cudaStream_t st = s->stream;
+  CK(cudaMemcpyAsync(s->ob_nt.p, n_t, sizeof(int) * n_sys, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(s->ob_t.p, t, sizeof(double) * (size_t)n_sys * n_max, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(s->ob_y.p, y, sizeof(double) * (size_t)n_sys * n_max * N, cudaMemcpyHostToDevice, st));
+  if (yp) CK(cudaMemcpyAsync(s->ob_yp.p, yp, sizeof(double) * (size_t)n_sys * n_max * N, cudaMemcpyHostToDevice, st));
+  if (t_obs) CK(cudaMemcpyAsync(s->ob_tobs.p, t_obs, sizeof(double) * n_obs, cudaMemcpyHostToDevice, st));
+  if (D.n_inputs > 0) CK(cudaMemcpyAsync(s->inputs.p, inputs, sizeof(double) * (size_t)n_sys * D.n_inputs, cudaMemcpyHostToDevice, st));
+  CK(cudaMemsetAsync(s->ob_out.p, 0, sizeof(double) * (size_t)n_sys * rows * D.n_vars, st));
+  if (pbgpu_observe_device(s, n_sys, n_max, (const int*)s->ob_nt.p, (const double*)s->ob_t.p, (const double*)s->ob_y.p,
+                           yp ? (const double*)s->ob_yp.p : nullptr, (const double*)s->inputs.p,
+                           t_obs ? (const double*)s->ob_tobs.p : nullptr, n_obs, (double*)s->ob_out.p, (void*)st, 0))
+    return 1;
+  CK(cudaMemcpyAsync(out, s->ob_out.p, sizeof(double) * (size_t)n_sys * rows * D.n_vars, cudaMemcpyDeviceToHost, st));
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) return cuda_fail("observation kernel", e);
   return 0;
 }
 

@@ -2204,6 +2204,57 @@ static PB_DEV void pb_solve_system(pb_sys& S, const pbgpu_launch& L, int sys) {
   }
 }
 
+// ---- variable observation (observe.cpp:18-354) -------------------------------------------------------------------------
+// One team per solution: for every requested time, the state (stored, or cubic-Hermite interpolated from y and y' of the
+// enclosing stored interval exactly as HermiteInterpolator::compute_knots / interpolate do) goes to shared memory and the
+// generated output-variable function writes the row.  S.sm and S_P(S) must be set; uses S_YY and S_TMP.
+#if PBM_NVAR > 0
+static PB_DEV void pb_observe_system(pb_sys& S, const pbgpu_observe_launch& O, int sys) {
+  const int nt = O.n_t[sys];
+  const double* t = O.t + (size_t)sys * O.n_max;
+  const double* y = O.y + (size_t)sys * O.n_max * PBM_N;
+  double* yy = S_YY(S);
+  PB_SYNC();
+  for (int k = PB_TID; k < PBM_NP_REAL; k += PB_TEAM) S_P(S)[k] = O.inputs[(size_t)sys * PBM_NP_REAL + k];
+  PB_SYNC();
+  if (O.n_obs == 0) {
+    for (int i = 0; i < nt; i++) {
+      for (int q = PB_TID; q < PBM_N; q += PB_TEAM) yy[q] = y[(size_t)i * PBM_N + q];
+      PB_SYNC();
+      pbm_vars(yy, S_P(S), PB_LDU(t[i]), 0.0, O.out + ((size_t)sys * O.n_max + i) * PBM_NVAR, S_TMP(S));
+      PB_SYNC();
+    }
+    return;
+  }
+  const double* yp = O.yp + (size_t)sys * O.n_max * PBM_N;
+  int j = 0;
+  for (int k = 0; k < O.n_obs; k++) {
+    double* row = O.out + ((size_t)sys * O.n_obs + k) * PBM_NVAR;
+    const double ti = PB_LDU(O.t_obs[k]);
+    if (nt < 2) {   // a single stored point: nothing to interpolate between
+      for (int q = PB_TID; q < PBM_N; q += PB_TEAM) yy[q] = (nt == 1) ? y[q] : PB_NAN;
+    } else {
+      // interval search as in TimeSeriesInterpolator::process_within_bounds (t_obs ascending; the last interval also serves
+      // every time beyond the final stored point: extrapolate_remaining)
+      while (j < nt - 2 && !(PB_LDU(t[j]) <= ti && ti <= PB_LDU(t[j + 1]))) j++;
+      const double t0 = PB_LDU(t[j]), hf = PB_LDU(t[j + 1]) - t0;
+      const double inv_h = 1.0 / hf, inv_h2 = inv_h * inv_h, inv_h3 = inv_h2 * inv_h;
+      const double h = ti - t0, h2 = h * h, h3 = h2 * h;
+      for (int q = PB_TID; q < PBM_N; q += PB_TEAM) {
+        const double y0 = y[(size_t)j * PBM_N + q], y1 = y[(size_t)(j + 1) * PBM_N + q];
+        const double p0 = yp[(size_t)j * PBM_N + q], p1 = yp[(size_t)(j + 1) * PBM_N + q];
+        const double c = 3.0 * (y1 - y0) * inv_h2 - (2.0 * p0 + p1) * inv_h;
+        const double d = 2.0 * (y0 - y1) * inv_h3 + (p0 + p1) * inv_h2;
+        yy[q] = y0 + p0 * h + c * h2 + d * h3;
+      }
+    }
+    PB_SYNC();
+    pbm_vars(yy, S_P(S), ti, 0.0, row, S_TMP(S));
+    PB_SYNC();
+  }
+}
+#endif
+
 // Constant slots of the LU value array and the packed streams (copied to shared memory once per team). S.sm must be set.
 static PB_DEV void pb_sys_tables(pb_sys& S) {
   if (PB_TID == 0) {

@@ -183,6 +183,21 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_e
   }
 }
 
+// Batched observation of the compiled output variables (pbgpu_observe): one team per solution, grid-stride.
+extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_observe_kernel(const pbgpu_observe_launch O) {
+#if PBM_NVAR > 0
+  extern __shared__ double pb_smem[];
+  pb_sys S;
+  S.sm = pb_smem;
+#if PB_GLOBAL_VEC
+  S.gv = O.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES;
+#else
+  S.gv = pb_smem;
+#endif
+  for (int sys = blockIdx.x; sys < O.n_sys; sys += gridDim.x) pb_observe_system(S, O, sys);
+#endif
+}
+
 // Launch configuration per device ordinal: the multi-device path runs one host thread per device through the same
 // image, so nothing here may be a single file-scope value.
 #include <mutex>
@@ -207,6 +222,8 @@ static int pb_configure(pb_dev_cfg* out, char* err, size_t errlen) {
   e = cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(pbgpu_observe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
   if (e != cudaSuccess) {
     snprintf(err, errlen, "model '%s' needs %d bytes of shared memory per team: %s", PBM_NAME, (int)PB_SMEM_BYTES,
              cudaGetErrorString(e));
@@ -246,6 +263,7 @@ static int pb_configure(pb_dev_cfg* out, char* err, size_t errlen) {
   if (pct > 100) pct = 100;
   cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+  cudaFuncSetAttribute(pbgpu_observe_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   c.ready = 1;
   g_cfg[dev] = c;
   *out = c;
@@ -320,6 +338,26 @@ extern "C" int pbgpu_image_eval(const pbgpu_eval_launch* E, void* stream, int gr
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     snprintf(err, errlen, "pbgpu_eval_kernel launch: %s", cudaGetErrorString(e));
+    return 1;
+  }
+  return 0;
+}
+
+extern "C" int pbgpu_image_observe(const pbgpu_observe_launch* O, void* stream, int grid, char* err, size_t errlen) {
+  pb_dev_cfg c;
+  if (pb_configure(&c, err, errlen)) return 1;
+  if (PBM_NVAR < 1) {
+    snprintf(err, errlen, "the model image has no compiled output variables");
+    return 1;
+  }
+  if (grid < 1 || grid > c.blocks_per_sm * c.num_sms) {
+    snprintf(err, errlen, "pbgpu_image_observe: grid %d was not planned for this device", grid);
+    return 1;
+  }
+  pbgpu_observe_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*O);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    snprintf(err, errlen, "pbgpu_observe_kernel launch: %s", cudaGetErrorString(e));
     return 1;
   }
   return 0;

@@ -50,6 +50,13 @@ class Result(C.Structure):
     ]
 
 
+class ObserveArgs(C.Structure):
+    _fields_ = [
+        ("n_sys", C.c_int), ("n_max", C.c_int), ("n_obs", C.c_int), ("n_t", C.c_void_p), ("t", C.c_void_p), ("y", C.c_void_p),
+        ("yp", C.c_void_p), ("inputs", C.c_void_p), ("t_obs", C.c_void_p), ("out", C.c_void_p), ("scratch", C.c_void_p),
+    ]
+
+
 class LaunchArgs(C.Structure):
     _fields_ = [
         ("n_sys", C.c_int), ("n_eval", C.c_int), ("n_interp", C.c_int), ("n_max", C.c_int), ("save_vars", C.c_int),

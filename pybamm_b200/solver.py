@@ -143,6 +143,8 @@ class _Lib:
             lib.pbgpu_solve_device.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int, vp, vp, vp, C.c_int,
                                                C.POINTER(Result), vp, C.c_int]
             lib.pbgpu_model_eval.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_double, C.c_double, vp, vp, C.c_int]
+            lib.pbgpu_observe.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, vp]
+            lib.pbgpu_observe_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int]
             cls._inst = lib
         return cls._inst
 
@@ -471,6 +473,42 @@ class BatchedIDASolver:
                 sol._yp_rows = yp_all[i, :n]
             sols.append(sol)
         return sols[0] if single else sols
+
+    # -- batched variable observation (idaklu.observe / observe_hermite_interp, observe.cpp:319-354) ----------------------
+    def observe(self, result, inputs, t_obs=None):
+        """Evaluate the bundle's compiled variables for every system of a full-state result of ``solve_arrays``.
+
+        ``t_obs=None``: at the stored points, returns ``(n_sys, n_max, n_vars)`` (rows beyond ``n_t`` are zero);
+        otherwise at the sorted times ``t_obs`` by cubic Hermite interpolation of ``y`` from ``(y, yp)`` (needs the ``yp``
+        block: adaptive steps with ``hermite_interpolation``), returns ``(n_sys, len(t_obs), n_vars)``.
+        The columns follow ``bundle.variables`` in order."""
+        self._ensure()
+        D = self.desc
+        if D.n_vars < 1:
+            raise SolverError(f"model bundle '{self.bundle.name}' has no compiled variables to observe")
+        t = np.ascontiguousarray(result["t"], dtype=np.float64)
+        y = np.ascontiguousarray(result["y"], dtype=np.float64)
+        if y.ndim != 3 or y.shape[2] != D.n_states:
+            raise SolverError("observe needs the full state (solve without output_variables)")
+        n_sys, n_max = t.shape
+        n_t = np.ascontiguousarray(np.minimum(result["n_t"], n_max), dtype=np.int32)
+        p = np.ascontiguousarray(np.asarray(inputs, dtype=np.float64).reshape(n_sys, -1))
+        if p.shape[1] != D.n_inputs:
+            raise SolverError(f"inputs has wrong number of cols. Expected {D.n_inputs} but got {p.shape[1]}")
+        yp = None
+        if t_obs is not None:
+            if result.get("yp") is None:
+                raise SolverError("Hermite observation needs yp: solve with adaptive steps and hermite_interpolation")
+            yp = np.ascontiguousarray(result["yp"], dtype=np.float64)
+            t_obs = np.ascontiguousarray(np.asarray(t_obs, dtype=np.float64).reshape(-1))
+            if np.any(np.diff(t_obs) < 0):
+                raise SolverError("t_obs must be sorted")
+        rows = len(t_obs) if t_obs is not None else n_max
+        out = np.zeros((n_sys, rows, D.n_vars))
+        if self._lib.pbgpu_observe(self._solver, n_sys, n_max, _ptr(n_t), _ptr(t), _ptr(y), _ptr(yp), _ptr(p), _ptr(t_obs),
+                                   0 if t_obs is None else len(t_obs), _ptr(out)):
+            raise SolverError(_err(self._lib))
+        return out
 
     # -- device evaluation of the generated functions (parity tests, event identification) ---------
     def eval(self, which, y, p, t=0.0, cj=0.0, y2=None):

@@ -8,7 +8,7 @@ import subprocess
 import numpy as np
 
 from pybamm_b200 import build
-from pybamm_b200.host import Options, LaunchArgs, default_options, canonical_time_grids
+from pybamm_b200.host import Options, LaunchArgs, ObserveArgs, default_options, canonical_time_grids
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 
@@ -94,3 +94,26 @@ class Emu:
         return dict(t=[t_out[i, :ns[i]] for i in range(n_sys)], y=[y_out[i, :ns[i]] for i in range(n_sys)],
                     yp=None if yp_out is None else [yp_out[i, :ns[i]] for i in range(n_sys)],
                     flag=flag, y_term=y_term, stats=stats, n_out=n_out, event_idx=event_idx, t_event=t_event)
+
+    def observe(self, t, y, n_t, inputs, yp=None, t_obs=None):
+        """The device observation routine (pb_observe_system) on the host. Padded arrays as BatchedIDASolver.observe."""
+        t = np.ascontiguousarray(t, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        n_sys, n_max = t.shape
+        n_t = np.ascontiguousarray(n_t, dtype=np.int32)
+        p = np.ascontiguousarray(np.asarray(inputs, dtype=np.float64).reshape(n_sys, -1))
+        if p.shape[1] == 0:
+            p = np.zeros((n_sys, 1))
+        rows = n_max if t_obs is None else len(t_obs)
+        out = np.zeros((n_sys, rows, self.n_var))
+        O = ObserveArgs()
+        vp = C.c_void_p
+        O.n_sys, O.n_max, O.n_obs = n_sys, n_max, 0 if t_obs is None else len(t_obs)
+        O.n_t, O.t, O.y, O.inputs, O.out = (a.ctypes.data_as(vp) for a in (n_t, t, y, p, out))
+        keep = []
+        if yp is not None:
+            yp = np.ascontiguousarray(yp, dtype=np.float64); keep.append(yp); O.yp = yp.ctypes.data_as(vp)
+        if t_obs is not None:
+            t_obs = np.ascontiguousarray(t_obs, dtype=np.float64); keep.append(t_obs); O.t_obs = t_obs.ctypes.data_as(vp)
+        if self.lib.emu_observe(C.byref(O)):
+            raise RuntimeError("the model has no compiled output variables")
+        return out

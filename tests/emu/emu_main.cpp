@@ -68,3 +68,17 @@ extern "C" int emu_eval(int which, const double* y, const double* p, double t, d
   free(sm);
   return rc;
 }
+
+extern "C" int emu_observe(const pbgpu_observe_launch* O) {
+#if PBM_NVAR > 0
+  double* sm = (double*)calloc(PB_SMEM_DOUBLES + PB_SCRATCH_DOUBLES + 1, sizeof(double));
+  pb_sys S;
+  S.sm = sm;
+  S.gv = PB_GLOBAL_VEC ? sm + PB_SMEM_DOUBLES : sm;
+  for (int sys = 0; sys < O->n_sys; sys++) pb_observe_system(S, *O, sys);
+  free(sm);
+  return 0;
+#else
+  return 1;
+#endif
+}

@@ -426,3 +426,26 @@ def test_cuda_path_matches_scipy_radau_anchor(name):
     r = gpu(name).solve_arrays(util.T_EVAL, anchor_inputs(b), t_interp=util.T_INTERP)
     n = int(r["n_t"][0])
     check_against_anchor(name, r["t"][0, n - 1], r["flag"][0], r["t"][0, :n], r["y"][0, :n, 0])
+
+
+def test_batched_observation_on_the_device():
+    # idaklu.observe / observe_hermite_interp (observe.cpp:319-354) for a whole batch in one launch, against the host
+    # emulation of the same routine and the numpy evaluation of the bundle
+    b = util.bundle("spme")
+    s = BatchedIDASolver(b, rtol=1e-6, atol=1e-8)
+    p = util.sample_inputs(b, 64, np.random.default_rng(21))
+    r = s.solve_arrays([0.0, 900.0], p)                       # adaptive steps: y and yp
+    assert r["yp"] is not None
+    obs = s.observe(r, p)
+    for i in (0, 31, 63):
+        k = int(r["n_t"][i]) - 1
+        ref = b.eval_variable("Voltage [V]", r["t"][i, k], r["y"][i, k], p[i])[0]
+        assert abs(obs[i, k, 0] - ref) < 1e-11
+    t_obs = np.array([0.0, 10.0, 450.0, 899.9, 900.0, 901.0])
+    got = s.observe(r, p, t_obs=t_obs)
+    ref = util.emu("spme").observe(r["t"], r["y"], np.minimum(r["n_t"], r["n_max"]), p, yp=r["yp"], t_obs=t_obs)
+    np.testing.assert_allclose(got, ref, rtol=0, atol=1e-11)
+    fixed = BatchedIDASolver(b, rtol=1e-6, atol=1e-8, output_variables=["Voltage [V]"]).solve_arrays([0.0, 900.0], p, t_interp=t_obs[1:4])
+    np.testing.assert_allclose(got[:, 1:4, 0], fixed["y"][:, 1:4, 0], rtol=0, atol=1e-4)
+    with pytest.raises(SolverError, match="yp"):
+        s.observe(s.solve_arrays([0.0, 900.0], p, t_interp=np.linspace(0, 900, 10)), p, t_obs=t_obs)

@@ -156,3 +156,44 @@ def test_yp0_is_used_only_without_calc_ic():
     np.testing.assert_allclose(good["y"][0][-1, 0], 2.0 * np.exp(-0.3), rtol=1e-6)
     bad = e.solve([0.0, 1.0], p, rtol=1e-8, atol=1e-10, yp0=np.array([[123.0]]), options={"calc_ic": False})
     assert not np.array_equal(bad["t"][0], base["t"][0])      # the wrong derivative changes the first step
+
+
+def _pad(r, key, n_max, width):
+    out = np.zeros((len(r["t"]), n_max) + ((width,) if width else ()))
+    for i, a in enumerate(r[key]):
+        out[i, :len(a)] = a
+    return out
+
+
+def test_device_observation_matches_the_reference_semantics():
+    # observe.cpp:25-64 (Hermite knots), :100-166 (interval search, extrapolation with the last interval), :319-354
+    b, e = util.bundle("spm"), util.emu("spm")
+    p = util.sample_inputs(b, 2, np.random.default_rng(8))
+    r = e.solve([0.0, 900.0], p, rtol=1e-6, atol=1e-8, want_yp=True)          # adaptive steps, y and y' stored
+    n_t = np.array([len(t) for t in r["t"]], np.int32)
+    n_max = int(n_t.max())
+    t, y, yp = _pad(r, "t", n_max, 0), _pad(r, "y", n_max, b.n_states), _pad(r, "yp", n_max, b.n_states)
+    # (1) at the stored points: var(t_i, y_i, p)
+    obs = e.observe(t, y, n_t, p)
+    for i in range(2):
+        ref = np.array([b.eval_variable("Voltage [V]", t[i, k], y[i, k], p[i])[0] for k in range(n_t[i])])
+        np.testing.assert_allclose(obs[i, :n_t[i], 0], ref, rtol=0, atol=1e-12)
+    # (2) Hermite interpolation at new times, including one beyond the last stored point
+    t_obs = np.array([0.0, 1.0, 123.4, 450.0, 899.0, 900.0, 905.0])
+    got = e.observe(t, y, n_t, p, yp=yp, t_obs=t_obs)
+    for i in range(2):
+        ti, yi, ypi = t[i, :n_t[i]], y[i, :n_t[i]], yp[i, :n_t[i]]
+        for k, to in enumerate(t_obs):
+            j = min(max(int(np.searchsorted(ti, to, side="left")) - 1, 0), len(ti) - 2)
+            if ti[j + 1] < to:
+                j = len(ti) - 2
+            H, h = ti[j + 1] - ti[j], to - ti[j]
+            c = 3 * (yi[j + 1] - yi[j]) / H ** 2 - (2 * ypi[j] + ypi[j + 1]) / H
+            d = 2 * (yi[j] - yi[j + 1]) / H ** 3 + (ypi[j] + ypi[j + 1]) / H ** 2
+            yh = yi[j] + ypi[j] * h + c * h * h + d * h ** 3
+            ref = b.eval_variable("Voltage [V]", to, yh, p[i])[0]
+            assert abs(got[i, k, 0] - ref) < 1e-10, (i, k, got[i, k, 0], ref)
+    # the interpolant is as accurate as the integration: against a fixed-grid solve at the same times
+    fixed = e.solve([0.0, 900.0], p, t_interp=t_obs[1:5], rtol=1e-6, atol=1e-8, save_vars=True)
+    for i in range(2):
+        np.testing.assert_allclose(got[i, 1:5, 0], fixed["y"][i][1:5, 0], rtol=0, atol=5e-5)
