@@ -37,7 +37,7 @@ extern "C" {
 #endif
 
 #define PBGPU_QUEUE_WORDS (32 + 8 * 256)
-#define PBGPU_ABI_VERSION 5
+#define PBGPU_ABI_VERSION 6
 
 typedef struct pbgpu_model_s* pbgpu_model_t;
 typedef struct pbgpu_solver_s* pbgpu_solver_t;
@@ -156,6 +156,50 @@ int pbgpu_model_eval(pbgpu_solver_t solver, int which, int n_sys, const double* 
                      double cj, const double* y2, double* out, int out_len);
 
 /*
+ * Experiment schedule (BASELINE config 5): the per-step loop of Simulation.solve
+ * (packages/pybamm/src/pybamm/simulation/simulation.py:991-1167) for the *unified* experiment model (:269-416), whose
+ * control law and step termination are selected by input parameters ("Experiment step index", "Experiment step value",
+ * "Ambient temperature [K]").  The reference runs it as one Python solver.step() per step and per input set and refuses a
+ * list of input sets (:832-835); here the whole schedule runs inside the kernel for every system of the batch.
+ * Per step k (base_solver.py:1334-1588, BaseStep.setup_timestepping base_step.py:355-421):
+ *   the over_slot inputs take over_val[k][:]; t_start = end of the previous step (moved to the next floating-point value when
+ *   non-zero); consistent initialisation; termination events at t_start: the experiment event <= 0 skips the step
+ *   ("Event exceeded in initial conditions" -> EmptySolution, simulation.py:1062-1070), any other one ends the run; integrate to
+ *   t_start + duration[k] storing t_start, t_start + j * duration[k] / (n_pts[k] - 1) (j = 1 .. n_pts[k] - 2) and the end point;
+ *   a root of the experiment event ends the step, a root of any other termination event ends the run (infeasible experiment),
+ *   reaching the duration of a step with stop_on_final_time[k] set ends the run as well (default durations, :1140-1147).
+ * All pointers are host memory for pbgpu_solve_experiment.
+ */
+typedef struct {
+  int n_steps;
+  int n_over;                            /* inputs overridden by the schedule */
+  const int* over_slot;                  /* [n_over] columns of `inputs` */
+  const double* over_val;                /* [n_steps][n_over] */
+  const double* duration;                /* [n_steps] seconds */
+  const int* n_pts;                      /* [n_steps] output points of the step's linspace(0, duration, n_pts), >= 2 */
+  const unsigned char* stop_on_final_time; /* [n_steps] or NULL */
+  int experiment_event;                  /* index of the termination event that ends a step normally, -1: none */
+} pbgpu_schedule;
+
+/* step_term codes */
+#define PBGPU_STEP_NOT_RUN 0
+#define PBGPU_STEP_FINAL_TIME 1
+#define PBGPU_STEP_EXPERIMENT_EVENT 2
+#define PBGPU_STEP_SKIPPED 3
+#define PBGPU_STEP_OTHER_EVENT 4
+
+/* Points a result block must hold per system for a schedule: sum over steps of n_pts[k] + 1. */
+int pbgpu_schedule_capacity(const pbgpu_schedule* sched);
+
+/*
+ * Run the schedule for n_sys input sets starting at time t0.  out as in pbgpu_solve (t / y concatenated over the steps; flag:
+ * 1 all steps done, 2 ended on a termination event other than the experiment's, < 0 IDA failure); step_end [n_sys][n_steps]:
+ * number of stored points up to and including step k; step_term [n_sys][n_steps]: PBGPU_STEP_* or a negative IDA flag.
+ */
+int pbgpu_solve_experiment(pbgpu_solver_t solver, int n_sys, double t0, const pbgpu_schedule* sched, const double* y0,
+                           const double* inputs, int output_mode, pbgpu_result* out, int* step_end, int* step_term);
+
+/*
  * Observe the compiled output variables of a batch of solutions on the device: the batched counterpart of
  * idaklu.observe / idaklu.observe_hermite_interp (idaklu_source/observe.cpp:319-354), which the reference calls once per
  * variable and per solution from ProcessedVariable (processed_variable.py:90-297) through CasADi.
@@ -201,6 +245,11 @@ typedef struct {
   double* scratch;      /* [teams][scratch_doubles_per_team] device memory owned by the solver handle, may be NULL if 0 */
   const int* order;     /* [n_sys] or NULL: the k-th system handed out by the queue is order[k] */
   pbgpu_options opt;
+  /* experiment schedule (device pointers), sched.n_steps == 0: plain solve */
+  pbgpu_schedule sched;
+  double t_start;       /* start time of the schedule */
+  int* step_end;
+  int* step_term;
 } pbgpu_launch;
 
 typedef struct {

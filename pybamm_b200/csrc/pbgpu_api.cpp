@@ -75,7 +75,7 @@ struct pbgpu_solver_s {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   DevBuf atol, t_eval, t_interp, inputs, y0, yp0, t_out, y_out, yp_out, n_out, flag, y_term, stats, event_idx, t_event, queue,
-      scratch_a, scratch_b, team_scratch, order, ob_nt, ob_t, ob_y, ob_yp, ob_tobs, ob_out;
+      scratch_a, scratch_b, team_scratch, order, sc_slot, sc_val, sc_dur, sc_npts, sc_stop, sc_end, sc_term, ob_nt, ob_t, ob_y, ob_yp, ob_tobs, ob_out;
   int last_grid = 0;
   int order_n = 0;
 };
@@ -206,7 +206,8 @@ int pbgpu_solver_destroy(pbgpu_solver_t s) {
   if (s->stream) cudaStreamSynchronize(s->stream);
   DevBuf* bufs[] = {&s->atol, &s->t_eval, &s->t_interp, &s->inputs, &s->y0, &s->yp0, &s->t_out, &s->y_out, &s->yp_out,
                     &s->n_out, &s->flag, &s->y_term, &s->stats, &s->event_idx, &s->t_event, &s->queue, &s->scratch_a,
-                    &s->scratch_b, &s->team_scratch, &s->order, &s->ob_nt, &s->ob_t, &s->ob_y, &s->ob_yp, &s->ob_tobs, &s->ob_out};
+                    &s->scratch_b, &s->team_scratch, &s->order, &s->sc_slot, &s->sc_val, &s->sc_dur, &s->sc_npts, &s->sc_stop,
+                    &s->sc_end, &s->sc_term, &s->ob_nt, &s->ob_t, &s->ob_y, &s->ob_yp, &s->ob_tobs, &s->ob_out};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 4; i++)
     if (s->ev[i]) cudaEventDestroy(s->ev[i]);
@@ -257,7 +258,8 @@ struct DevResult {
 
 static int launch_common(pbgpu_solver_s* s, int n_sys, const double* d_t_eval, int n_teval, const double* d_t_interp,
                          int n_tinterp, const double* d_y0, const double* d_yp0, const double* d_inputs, int output_mode,
-                         int n_max, const DevResult& R, cudaStream_t stream) {
+                         int n_max, const DevResult& R, cudaStream_t stream, const pbgpu_schedule* d_sched = nullptr,
+                         double t_start = 0.0, int* d_step_end = nullptr, int* d_step_term = nullptr) {
   const pbgpu_model_desc& D = s->model->desc;
   pbgpu_launch L;
   memset(&L, 0, sizeof(L));
@@ -288,6 +290,12 @@ static int launch_common(pbgpu_solver_s* s, int n_sys, const double* d_t_eval, i
   L.scratch = (double*)s->team_scratch.p;
   L.order = (s->order_n == n_sys && n_sys > 0) ? (const int*)s->order.p : nullptr;
   L.opt = s->opt;
+  if (d_sched) {
+    L.sched = *d_sched;
+    L.t_start = t_start;
+    L.step_end = d_step_end;
+    L.step_term = d_step_term;
+  }
   CK(cudaMemsetAsync(s->queue.p, 0, sizeof(unsigned int) * PBGPU_QUEUE_WORDS, stream));
   char err[512];
   err[0] = 0;
@@ -382,6 +390,100 @@ int pbgpu_solve(pbgpu_solver_t s, int n_sys, const double* t_eval, int n_teval, 
   CK(cudaEventRecord(s->ev[3], st));
   cudaError_t e = cudaStreamSynchronize(st);
   if (e != cudaSuccess) return cuda_fail("integration kernel", e);
+  CK(cudaEventElapsedTime(&out->kernel_ms, s->ev[1], s->ev[2]));
+  CK(cudaEventElapsedTime(&out->total_ms, s->ev[0], s->ev[3]));
+  return 0;
+}
+
+int pbgpu_schedule_capacity(const pbgpu_schedule* q) {
+  if (!q || q->n_steps < 1 || !q->n_pts) return 0;
+  long long n = 0;
+  for (int k = 0; k < q->n_steps; k++) n += (q->n_pts[k] < 2 ? 2 : q->n_pts[k]) + 1;
+  return n > 2000000000LL ? 0 : (int)n;
+}
+
+int pbgpu_solve_experiment(pbgpu_solver_t s, int n_sys, double t0, const pbgpu_schedule* q, const double* y0,
+                           const double* inputs, int output_mode, pbgpu_result* out, int* step_end, int* step_term) {
+  if (!s || !out || !q || !step_end || !step_term) return fail("pbgpu_solve_experiment: null argument");
+  if (n_sys < 1) return fail("pbgpu_solve_experiment: n_sys must be positive");
+  const pbgpu_model_desc& D = s->model->desc;
+  if (q->n_steps < 1 || !q->duration || !q->n_pts) return fail("pbgpu_solve_experiment: the schedule has no steps");
+  if (q->n_over < 0 || (q->n_over > 0 && (!q->over_slot || !q->over_val))) return fail("pbgpu_solve_experiment: incomplete input overrides");
+  for (int j = 0; j < q->n_over; j++)
+    if (q->over_slot[j] < 0 || q->over_slot[j] >= D.n_inputs) return fail("pbgpu_solve_experiment: override slot out of range");
+  for (int k = 0; k < q->n_steps; k++)
+    if (!(q->duration[k] > 0.0)) return fail("pbgpu_solve_experiment: step durations must be positive");
+  if (q->experiment_event >= D.n_events) return fail("pbgpu_solve_experiment: experiment_event out of range");
+  if (output_mode != PBGPU_OUTPUT_STATES && output_mode != PBGPU_OUTPUT_VARS) return fail("invalid output_mode");
+  if (output_mode == PBGPU_OUTPUT_VARS && D.n_vars < 1) return fail("the model image has no compiled output variables");
+  const int n_ret = output_mode == PBGPU_OUTPUT_VARS ? D.n_vars : D.n_states;
+  if (out->n_ret != n_ret)
+    return fail("result block has wrong row length. Expected " + std::to_string(n_ret) + " but got " + std::to_string(out->n_ret));
+  if (out->n_max < pbgpu_schedule_capacity(q) || !out->t || !out->y || !out->n_t || !out->flag)
+    return fail("result block is too small for the schedule (pbgpu_schedule_capacity) or incomplete");
+  if (D.n_inputs > 0 && !inputs) return fail("inputs has wrong number of dimensions. Expected 2 but got 0");
+  CK(cudaSetDevice(s->device));
+  const size_t N = D.n_states, nm = out->n_max, ns = q->n_steps;
+  if (s->inputs.ensure(sizeof(double) * (size_t)n_sys * (D.n_inputs > 0 ? D.n_inputs : 1))) return 1;
+  if (y0 && s->y0.ensure(sizeof(double) * n_sys * N)) return 1;
+  if (s->t_out.ensure(sizeof(double) * n_sys * nm)) return 1;
+  if (s->y_out.ensure(sizeof(double) * n_sys * nm * n_ret)) return 1;
+  if (out->yp && s->yp_out.ensure(sizeof(double) * n_sys * nm * N)) return 1;
+  if (s->n_out.ensure(sizeof(int) * n_sys)) return 1;
+  if (s->flag.ensure(sizeof(int) * n_sys)) return 1;
+  if (out->y_term && s->y_term.ensure(sizeof(double) * n_sys * N)) return 1;
+  if (out->stats && s->stats.ensure(sizeof(long long) * n_sys * 8)) return 1;
+  if (out->event_idx && s->event_idx.ensure(sizeof(int) * n_sys)) return 1;
+  if (out->t_event && s->t_event.ensure(sizeof(double) * n_sys)) return 1;
+  if (s->sc_slot.ensure(sizeof(int) * (q->n_over > 0 ? q->n_over : 1))) return 1;
+  if (s->sc_val.ensure(sizeof(double) * (ns * (q->n_over > 0 ? q->n_over : 1)))) return 1;
+  if (s->sc_dur.ensure(sizeof(double) * ns)) return 1;
+  if (s->sc_npts.ensure(sizeof(int) * ns)) return 1;
+  if (s->sc_stop.ensure(ns)) return 1;
+  if (s->sc_end.ensure(sizeof(int) * n_sys * ns)) return 1;
+  if (s->sc_term.ensure(sizeof(int) * n_sys * ns)) return 1;
+  cudaStream_t st = s->stream;
+  CK(cudaEventRecord(s->ev[0], st));
+  if (D.n_inputs > 0)
+    CK(cudaMemcpyAsync(s->inputs.p, inputs, sizeof(double) * (size_t)n_sys * D.n_inputs, cudaMemcpyHostToDevice, st));
+  if (y0) CK(cudaMemcpyAsync(s->y0.p, y0, sizeof(double) * n_sys * N, cudaMemcpyHostToDevice, st));
+  if (q->n_over > 0) {
+    CK(cudaMemcpyAsync(s->sc_slot.p, q->over_slot, sizeof(int) * q->n_over, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(s->sc_val.p, q->over_val, sizeof(double) * ns * q->n_over, cudaMemcpyHostToDevice, st));
+  }
+  CK(cudaMemcpyAsync(s->sc_dur.p, q->duration, sizeof(double) * ns, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(s->sc_npts.p, q->n_pts, sizeof(int) * ns, cudaMemcpyHostToDevice, st));
+  if (q->stop_on_final_time) CK(cudaMemcpyAsync(s->sc_stop.p, q->stop_on_final_time, ns, cudaMemcpyHostToDevice, st));
+  else CK(cudaMemsetAsync(s->sc_stop.p, 0, ns, st));
+  pbgpu_schedule dq = *q;
+  dq.over_slot = (const int*)s->sc_slot.p;
+  dq.over_val = (const double*)s->sc_val.p;
+  dq.duration = (const double*)s->sc_dur.p;
+  dq.n_pts = (const int*)s->sc_npts.p;
+  dq.stop_on_final_time = (const unsigned char*)s->sc_stop.p;
+  CK(cudaEventRecord(s->ev[1], st));
+  const DevResult R = {(double*)s->t_out.p, (double*)s->y_out.p, out->yp ? (double*)s->yp_out.p : nullptr, (int*)s->n_out.p,
+                       (int*)s->flag.p, out->y_term ? (double*)s->y_term.p : nullptr,
+                       out->stats ? (long long*)s->stats.p : nullptr, out->event_idx ? (int*)s->event_idx.p : nullptr,
+                       out->t_event ? (double*)s->t_event.p : nullptr};
+  if (launch_common(s, n_sys, nullptr, 2, nullptr, 0, y0 ? (const double*)s->y0.p : nullptr, nullptr, (const double*)s->inputs.p,
+                    output_mode, out->n_max, R, st, &dq, t0, (int*)s->sc_end.p, (int*)s->sc_term.p))
+    return 1;
+  CK(cudaEventRecord(s->ev[2], st));
+  CK(cudaMemcpyAsync(out->t, s->t_out.p, sizeof(double) * n_sys * nm, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out->y, s->y_out.p, sizeof(double) * n_sys * nm * n_ret, cudaMemcpyDeviceToHost, st));
+  if (out->yp) CK(cudaMemcpyAsync(out->yp, s->yp_out.p, sizeof(double) * n_sys * nm * N, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out->n_t, s->n_out.p, sizeof(int) * n_sys, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out->flag, s->flag.p, sizeof(int) * n_sys, cudaMemcpyDeviceToHost, st));
+  if (out->y_term) CK(cudaMemcpyAsync(out->y_term, s->y_term.p, sizeof(double) * n_sys * N, cudaMemcpyDeviceToHost, st));
+  if (out->stats) CK(cudaMemcpyAsync(out->stats, s->stats.p, sizeof(long long) * n_sys * 8, cudaMemcpyDeviceToHost, st));
+  if (out->event_idx) CK(cudaMemcpyAsync(out->event_idx, s->event_idx.p, sizeof(int) * n_sys, cudaMemcpyDeviceToHost, st));
+  if (out->t_event) CK(cudaMemcpyAsync(out->t_event, s->t_event.p, sizeof(double) * n_sys, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(step_end, s->sc_end.p, sizeof(int) * n_sys * ns, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(step_term, s->sc_term.p, sizeof(int) * n_sys * ns, cudaMemcpyDeviceToHost, st));
+  CK(cudaEventRecord(s->ev[3], st));
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) return cuda_fail("experiment kernel", e);
   CK(cudaEventElapsedTime(&out->kernel_ms, s->ev[1], s->ev[2]));
   CK(cudaEventElapsedTime(&out->total_ms, s->ev[0], s->ev[3]));
   return 0;

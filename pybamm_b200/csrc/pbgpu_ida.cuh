@@ -2204,6 +2204,181 @@ static PB_DEV void pb_solve_system(pb_sys& S, const pbgpu_launch& L, int sys) {
   }
 }
 
+// ---- experiment schedule on the device (Simulation.solve's step loop, simulation.py:991-1167) ----------------------------
+// One call integrates every step of the schedule for one system: the step's inputs are switched, the state is carried over,
+// the algebraic states are re-initialised, and the step runs to its duration or to a root of the experiment's termination
+// event.  See pbgpu_schedule in include/pbgpu.h for the per-step rules and the citations.
+static PB_DEV double pb_next_after(double t) {
+  if (t == 0.0) return t;   // base_solver.py:1380-1390: the first step starts at 0 exactly
+#ifndef PB_EMU
+  return __longlong_as_double(__double_as_longlong(t) + (t > 0.0 ? 1LL : -1LL));
+#else
+  return std::nextafter(t, INFINITY);
+#endif
+}
+
+static PB_DEV void pb_solve_experiment(pb_sys& S, const pbgpu_launch& L, int sys) {
+  const pbgpu_schedule& Q = L.sched;
+  PB_SYNC();
+  for (int k = PB_TID; k < PBM_NP_REAL; k += PB_TEAM) S_P(S)[k] = L.inputs[(size_t)sys * PBM_NP_REAL + k];
+  for (int k = PB_TID; k < 8; k += PB_TEAM) S_STATS(S)[k] = 0.0;
+  for (int k = PB_TID; k < Q.n_steps; k += PB_TEAM) {
+    L.step_end[(size_t)sys * Q.n_steps + k] = 0;
+    L.step_term[(size_t)sys * Q.n_steps + k] = PBGPU_STEP_NOT_RUN;
+  }
+  PB_SYNC();
+  for (int j = PB_TID; j < Q.n_over; j += PB_TEAM) S_P(S)[Q.over_slot[j]] = Q.over_val[j];   // step 0: y0(p) may depend on them
+  PB_SYNC();
+  double t_cur = L.t_start;
+  if (L.y0) {
+    double* phi0 = S_PHI(S, 0);
+    for (int i = PB_TID; i < PBM_N; i += PB_TEAM) phi0[i] = L.y0[(size_t)sys * PBM_N + i];
+  } else {
+    pbm_ic(S_YY(S), S_P(S), t_cur, 0.0, S_PHI(S, 0), S_TMP(S));
+  }
+  PB_SYNC();
+  int i_save = 0, overall = PB_IDA_TSTOP_RETURN, ev_idx = -1;
+  double t_last = t_cur;
+  int have_history = 0;   // phi holds a stepped history of the previous step (so y(t_cur) comes from the interpolant)
+  for (int k = 0; k < Q.n_steps; k++) {
+    PB_SYNC();
+    for (int j = PB_TID; j < Q.n_over; j += PB_TEAM) S_P(S)[Q.over_slot[j]] = Q.over_val[(size_t)k * Q.n_over + j];
+    PB_SYNC();
+    if (have_history) {   // carry the state over: y(t_cur) of the finished step becomes the new start state
+      pb_get_solution(S, t_cur, S_YY(S));
+      PB_SYNC();
+      double* phi0 = S_PHI(S, 0);
+      const double* yy = S_YY(S);
+      for (int i = PB_TID; i < PBM_N; i += PB_TEAM) phi0[i] = yy[i];
+      PB_SYNC();
+      have_history = 0;
+    }
+    const double t0 = pb_next_after(t_cur);   // base_solver.py:1380-1390 (0 stays 0)
+    const double dur = PB_LDU(Q.duration[k]);
+    const double tf = t_cur + dur;
+    const int npts = Q.n_pts[k] < 2 ? 2 : Q.n_pts[k];
+    const double dt_out = dur / (npts - 1);
+    pb_consistent_init(S, t0, 1);
+    int term = PBGPU_STEP_NOT_RUN;
+#if PBM_NEV > 0
+    {   // termination events at the start of the step (IDAKLUSolverOpenMP.inl:365-378, simulation.py:1062-1070)
+      double* g = S_GHI(S);
+      pb_gfun(S, t0, S_PHI(S, 0), g);
+      int trig_exp = 0, trig_other = 0;
+      double best = PB_INF;
+      for (int i = 0; i < PBM_NEV; i++) {
+        if (g[i] <= 0.0) {
+          if (i == Q.experiment_event) trig_exp = 1;
+          else trig_other = 1;
+          if (fabs(g[i]) < best) {
+            best = fabs(g[i]);
+            ev_idx = i;
+          }
+        }
+      }
+      PB_SYNC();
+      if (trig_exp && !trig_other) term = PBGPU_STEP_SKIPPED;
+      else if (trig_other) term = PBGPU_STEP_OTHER_EVENT;
+    }
+#endif
+    if (term == PBGPU_STEP_SKIPPED) {
+      if (PB_TID == 0) {
+        L.step_end[(size_t)sys * Q.n_steps + k] = i_save;
+        L.step_term[(size_t)sys * Q.n_steps + k] = term;
+      }
+      continue;   // t_cur and the state stay; the next step re-initialises from phi[0]
+    }
+    if (term == PBGPU_STEP_OTHER_EVENT) {
+      overall = PB_IDA_ROOT_RETURN;
+      if (PB_TID == 0) {
+        L.step_end[(size_t)sys * Q.n_steps + k] = i_save;
+        L.step_term[(size_t)sys * Q.n_steps + k] = term;
+      }
+      break;
+    }
+    S.tstop = tf;
+    S.tstopset = 1;
+    double t_val = t0, t_prev = t0;
+    int retval = pb_ida_solve_one_step(S, pb_perturb_time(tf), &t_val);
+    if (retval >= 0) {
+      pb_store_point(S, L, sys, t0, &i_save, &t_last);
+      have_history = 1;
+    }
+    int j_out = 1;
+    long long guard = 0;
+    for (;;) {
+      if (retval < 0) break;
+      if (t_prev == t_val) {
+        retval = PB_IDA_ERR_FAIL;
+        break;
+      }
+      while (j_out < npts - 1) {
+        const double ti = t_cur + j_out * dt_out;
+        if (!(ti <= t_val)) break;
+        if (ti > t0) pb_store_point(S, L, sys, ti, &i_save, &t_last);
+        j_out++;
+      }
+      const int hit_final = retval == PB_IDA_TSTOP_RETURN || t_val >= tf;
+      const int hit_event = retval == PB_IDA_ROOT_RETURN;
+      if (hit_final || hit_event) {
+        if (t_val != t_last) pb_store_point(S, L, sys, t_val, &i_save, &t_last);
+        break;
+      }
+      t_prev = t_val;
+      if (++guard > S.max_num_steps) {
+        retval = PB_IDA_TOO_MUCH_WORK;
+        break;
+      }
+      retval = pb_ida_solve_one_step(S, pb_perturb_time(tf), &t_val);
+    }
+    if (retval < 0) {
+      term = retval;
+      overall = retval;
+    } else if (retval == PB_IDA_ROOT_RETURN) {
+#if PBM_NEV > 0
+      const double* gr = S_GROUT(S);
+      double best = PB_INF;
+      for (int i = 0; i < PBM_NEV; i++) {
+        const double a = fabs(gr[i]);
+        if (a < best) {
+          best = a;
+          ev_idx = i;
+        }
+      }
+#endif
+      term = (ev_idx == Q.experiment_event) ? PBGPU_STEP_EXPERIMENT_EVENT : PBGPU_STEP_OTHER_EVENT;
+      if (term == PBGPU_STEP_OTHER_EVENT) overall = PB_IDA_ROOT_RETURN;
+    } else {
+      term = PBGPU_STEP_FINAL_TIME;
+      if (Q.stop_on_final_time && Q.stop_on_final_time[k]) overall = PB_IDA_SUCCESS;   // infeasible: the default duration ran out
+    }
+    PB_SYNC();
+    if (PB_TID == 0) {
+      L.step_end[(size_t)sys * Q.n_steps + k] = i_save;
+      L.step_term[(size_t)sys * Q.n_steps + k] = term;
+    }
+    t_cur = t_val;
+    if (term != PBGPU_STEP_EXPERIMENT_EVENT && !(term == PBGPU_STEP_FINAL_TIME && overall == PB_IDA_TSTOP_RETURN)) break;
+  }
+  if (L.y_term) {
+    PB_SYNC();
+    if (have_history) pb_get_solution(S, t_cur, L.y_term + (size_t)sys * PBM_N);
+    else {
+      const double* phi0 = S_PHI(S, 0);
+      for (int i = PB_TID; i < PBM_N; i += PB_TEAM) L.y_term[(size_t)sys * PBM_N + i] = phi0[i];
+    }
+  }
+  PB_SYNC();
+  if (PB_TID == 0) {
+    L.n_out[sys] = i_save;
+    L.flag[sys] = overall;
+    if (L.event_idx) L.event_idx[sys] = (overall == PB_IDA_ROOT_RETURN) ? ev_idx : -1;
+    if (L.t_event) L.t_event[sys] = t_last;
+    if (L.stats)
+      for (int q = 0; q < 8; q++) L.stats[(size_t)sys * 8 + q] = (long long)S_STATS(S)[q];
+  }
+}
+
 // ---- variable observation (observe.cpp:18-354) -------------------------------------------------------------------------
 // One team per solution: for every requested time, the state (stored, or cubic-Hermite interpolated from y and y' of the
 // enclosing stored interval exactly as HermiteInterpolator::compute_knots / interpolate do) goes to shared memory and the

@@ -183,6 +183,27 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_e
   }
 }
 
+// The experiment schedule (pbgpu_solve_experiment): its own kernel, so that the driver of the plain solve stays as small as
+// it is (the integration is bound by instruction fetch).
+extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_experiment_kernel(const pbgpu_launch L) {
+  extern __shared__ double pb_smem[];
+  __shared__ unsigned int next_sys;
+  pb_sys S;
+#if PB_GLOBAL_VEC
+  pb_sys_init(S, pb_smem, L.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES, L);
+#else
+  pb_sys_init(S, pb_smem, pb_smem, L);
+#endif
+  for (;;) {
+    if (threadIdx.x == 0) next_sys = atomicAdd(L.queue, 1u);
+    __syncthreads();
+    const unsigned int slot = next_sys;
+    __syncthreads();
+    if (slot >= (unsigned int)L.n_sys) break;
+    pb_solve_experiment(S, L, L.order ? L.order[slot] : (int)slot);
+  }
+}
+
 // Batched observation of the compiled output variables (pbgpu_observe): one team per solution, grid-stride.
 extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_observe_kernel(const pbgpu_observe_launch O) {
 #if PBM_NVAR > 0
@@ -224,6 +245,8 @@ static int pb_configure(pb_dev_cfg* out, char* err, size_t errlen) {
     e = cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(pbgpu_observe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(pbgpu_experiment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
   if (e != cudaSuccess) {
     snprintf(err, errlen, "model '%s' needs %d bytes of shared memory per team: %s", PBM_NAME, (int)PB_SMEM_BYTES,
              cudaGetErrorString(e));
@@ -264,6 +287,7 @@ static int pb_configure(pb_dev_cfg* out, char* err, size_t errlen) {
   cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   cudaFuncSetAttribute(pbgpu_observe_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+  cudaFuncSetAttribute(pbgpu_experiment_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   c.ready = 1;
   g_cfg[dev] = c;
   *out = c;
@@ -318,7 +342,10 @@ extern "C" int pbgpu_image_launch(const pbgpu_launch* L, void* stream, int grid,
     snprintf(err, errlen, "pbgpu_image_launch: grid %d was not planned for this device", grid);
     return 1;
   }
-  pbgpu_solve_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*L);
+  if (L->sched.n_steps > 0)
+    pbgpu_experiment_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*L);
+  else
+    pbgpu_solve_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*L);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     snprintf(err, errlen, "pbgpu_solve_kernel launch: %s", cudaGetErrorString(e));

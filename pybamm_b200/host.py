@@ -57,6 +57,13 @@ class ObserveArgs(C.Structure):
     ]
 
 
+class Schedule(C.Structure):
+    _fields_ = [
+        ("n_steps", C.c_int), ("n_over", C.c_int), ("over_slot", C.c_void_p), ("over_val", C.c_void_p),
+        ("duration", C.c_void_p), ("n_pts", C.c_void_p), ("stop_on_final_time", C.c_void_p), ("experiment_event", C.c_int),
+    ]
+
+
 class LaunchArgs(C.Structure):
     _fields_ = [
         ("n_sys", C.c_int), ("n_eval", C.c_int), ("n_interp", C.c_int), ("n_max", C.c_int), ("save_vars", C.c_int),
@@ -65,6 +72,7 @@ class LaunchArgs(C.Structure):
         ("n_out", C.c_void_p), ("flag", C.c_void_p), ("y_term", C.c_void_p), ("stats", C.c_void_p),
         ("yp_out", C.c_void_p), ("event_idx", C.c_void_p), ("t_event", C.c_void_p),
         ("queue", C.c_void_p), ("scratch", C.c_void_p), ("order", C.c_void_p), ("opt", Options),
+        ("sched", Schedule), ("t_start", C.c_double), ("step_end", C.c_void_p), ("step_term", C.c_void_p),
     ]
 
 

@@ -143,6 +143,7 @@ class _Lib:
             lib.pbgpu_solve_device.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int, vp, vp, vp, C.c_int,
                                                C.POINTER(Result), vp, C.c_int]
             lib.pbgpu_model_eval.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_double, C.c_double, vp, vp, C.c_int]
+            lib.pbgpu_solve_experiment.argtypes = [vp, C.c_int, C.c_double, vp, vp, vp, C.c_int, C.POINTER(Result), vp, vp]
             lib.pbgpu_observe.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, vp]
             lib.pbgpu_observe_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int]
             cls._inst = lib
@@ -473,6 +474,54 @@ class BatchedIDASolver:
                 sol._yp_rows = yp_all[i, :n]
             sols.append(sol)
         return sols[0] if single else sols
+
+    # -- experiment schedules on the device (pybamm_b200.experiment; simulation.py:991-1167) -------------------------------
+    def solve_experiment(self, schedule, inputs, t0=0.0, y0=None, output_mode=None, want_stats=True):
+        """Run an ``ExperimentSchedule`` for every row of ``inputs`` (n_sys, n_inputs; the columns the schedule overrides are
+        ignored).  Returns the dict of ``solve_arrays`` plus ``step_end`` / ``step_term`` (n_sys, n_steps): stored points up
+        to and including each step, and how each step ended (experiment.STEP_* or a negative IDA flag).
+        flag: 1 every step ran, 0 a default step duration ran out, 2 a termination event other than the experiment's, < 0 failure."""
+        from .host import Schedule
+
+        self._ensure()
+        lib, D = self._lib, self.desc
+        inputs = np.ascontiguousarray(np.asarray(inputs, dtype=np.float64))
+        if inputs.ndim != 2 or inputs.shape[1] != D.n_inputs:
+            raise SolverError(f"inputs has wrong shape. Expected (n_sys, {D.n_inputs}) but got {inputs.shape}")
+        n_sys = inputs.shape[0]
+        try:
+            slots, ev = schedule.slots(self.bundle), schedule.event_index(self.bundle)
+        except ValueError as e:
+            raise SolverError(str(e)) from None
+        if output_mode is None:
+            output_mode = 1 if self.output_variables else 0
+        n_ret = D.n_vars if output_mode == 1 else D.n_states
+        n_max = schedule.capacity
+        q = Schedule()
+        q.n_steps, q.n_over, q.experiment_event = schedule.n_steps, len(slots), ev
+        q.over_slot, q.over_val, q.duration = _ptr(slots), _ptr(schedule.over_val), _ptr(schedule.duration)
+        q.n_pts, q.stop_on_final_time = _ptr(schedule.n_pts), _ptr(schedule.stop_on_final_time)
+        if y0 is not None:
+            y0 = np.ascontiguousarray(np.asarray(y0, dtype=np.float64).reshape(n_sys, D.n_states))
+        (t_out, k1), (y_out, k2) = _pinned_empty((n_sys, n_max), np.float64), _pinned_empty((n_sys, n_max, n_ret), np.float64)
+        n_t, flag = np.zeros(n_sys, np.int32), np.zeros(n_sys, np.int32)
+        event_idx, t_event = np.zeros(n_sys, np.int32), np.zeros(n_sys)
+        y_term = np.zeros((n_sys, D.n_states))
+        stats = np.zeros((n_sys, 8), np.int64) if want_stats else None
+        step_end = np.zeros((n_sys, schedule.n_steps), np.int32)
+        step_term = np.zeros((n_sys, schedule.n_steps), np.int32)
+        res = Result()
+        res.n_max, res.n_ret = n_max, n_ret
+        res.t, res.y, res.n_t, res.flag = _ptr(t_out), _ptr(y_out), _ptr(n_t), _ptr(flag)
+        res.y_term, res.stats, res.event_idx, res.t_event = _ptr(y_term), _ptr(stats), _ptr(event_idx), _ptr(t_event)
+        if lib.pbgpu_solver_set_launch_order(self._solver, None, 0):
+            raise SolverError(_err(lib))
+        if lib.pbgpu_solve_experiment(self._solver, n_sys, float(t0), C.byref(q), _ptr(y0), _ptr(inputs), output_mode, C.byref(res),
+                                      _ptr(step_end), _ptr(step_term)):
+            raise SolverError(_err(lib))
+        self.last_kernel_ms, self.last_total_ms = float(res.kernel_ms), float(res.total_ms)
+        return dict(t=t_out, y=y_out, yp=None, n_t=n_t, flag=flag, y_term=y_term, stats=stats, event_idx=event_idx,
+                    t_event=t_event, n_max=n_max, step_end=step_end, step_term=step_term, _keep=(k1, k2))
 
     # -- batched variable observation (idaklu.observe / observe_hermite_interp, observe.cpp:319-354) ----------------------
     def observe(self, result, inputs, t_obs=None):

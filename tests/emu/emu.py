@@ -8,7 +8,7 @@ import subprocess
 import numpy as np
 
 from pybamm_b200 import build
-from pybamm_b200.host import Options, LaunchArgs, ObserveArgs, default_options, canonical_time_grids
+from pybamm_b200.host import Options, LaunchArgs, ObserveArgs, Schedule, default_options, canonical_time_grids
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 
@@ -117,3 +117,42 @@ class Emu:
         if self.lib.emu_observe(C.byref(O)):
             raise RuntimeError("the model has no compiled output variables")
         return out
+
+    def solve_experiment(self, bundle, schedule, inputs, t0=0.0, rtol=1e-4, atol=1e-6, y0=None, save_vars=False, options=None):
+        """pb_solve_experiment (the device experiment loop) on the host."""
+        inputs = np.ascontiguousarray(np.atleast_2d(np.asarray(inputs, dtype=np.float64)))
+        n_sys = inputs.shape[0]
+        atol_v = np.ascontiguousarray(np.broadcast_to(np.asarray(atol, dtype=np.float64), (self.n,)).copy())
+        n_ret = self.n_var if save_vars else self.n
+        n_max = schedule.capacity
+        ns = schedule.n_steps
+        t_out = np.zeros((n_sys, n_max)); y_out = np.zeros((n_sys, n_max, n_ret))
+        n_out = np.zeros(n_sys, np.int32); flag = np.zeros(n_sys, np.int32)
+        y_term = np.zeros((n_sys, self.n)); stats = np.zeros((n_sys, 8), np.int64)
+        event_idx = np.full(n_sys, -7, np.int32); t_event = np.zeros(n_sys)
+        step_end = np.zeros((n_sys, ns), np.int32); step_term = np.zeros((n_sys, ns), np.int32)
+        queue = np.zeros(1, np.uint32)
+        slots = schedule.slots(bundle)
+        vp = C.c_void_p
+        L = LaunchArgs()
+        L.n_sys, L.n_eval, L.n_interp, L.n_max, L.save_vars, L.n_ret = n_sys, 2, 0, n_max, int(save_vars), n_ret
+        L.inputs = inputs.ctypes.data_as(vp)
+        if y0 is not None:
+            y0 = np.ascontiguousarray(np.atleast_2d(np.asarray(y0, dtype=np.float64)))
+            L.y0 = y0.ctypes.data_as(vp)
+        L.atol = atol_v.ctypes.data_as(vp)
+        L.t_out = t_out.ctypes.data_as(vp); L.y_out = y_out.ctypes.data_as(vp); L.n_out = n_out.ctypes.data_as(vp)
+        L.flag = flag.ctypes.data_as(vp); L.y_term = y_term.ctypes.data_as(vp); L.stats = stats.ctypes.data_as(vp)
+        L.event_idx = event_idx.ctypes.data_as(vp); L.t_event = t_event.ctypes.data_as(vp)
+        L.queue = queue.ctypes.data_as(vp); L.opt = default_options(rtol=rtol, **(options or {}))
+        q = Schedule()
+        q.n_steps, q.n_over, q.experiment_event = ns, len(slots), schedule.event_index(bundle)
+        q.over_slot = slots.ctypes.data_as(vp); q.over_val = schedule.over_val.ctypes.data_as(vp)
+        q.duration = schedule.duration.ctypes.data_as(vp); q.n_pts = schedule.n_pts.ctypes.data_as(vp)
+        q.stop_on_final_time = schedule.stop_on_final_time.ctypes.data_as(vp)
+        L.sched = q; L.t_start = float(t0)
+        L.step_end = step_end.ctypes.data_as(vp); L.step_term = step_term.ctypes.data_as(vp)
+        self.lib.emu_solve(C.byref(L))
+        return dict(t=[t_out[i, :n_out[i]] for i in range(n_sys)], y=[y_out[i, :n_out[i]] for i in range(n_sys)], flag=flag,
+                    y_term=y_term, stats=stats, n_out=n_out, event_idx=event_idx, t_event=t_event, step_end=step_end,
+                    step_term=step_term)

@@ -19,7 +19,10 @@ extern "C" int emu_solve(const pbgpu_launch* L) {
   double* sm = (double*)calloc(PB_SMEM_DOUBLES + PB_SCRATCH_DOUBLES + 1, sizeof(double));
   pb_sys S;
   pb_sys_init(S, sm, PB_GLOBAL_VEC ? sm + PB_SMEM_DOUBLES : sm, *L);
-  for (int sys = 0; sys < L->n_sys; sys++) pb_solve_system(S, *L, sys);
+  for (int sys = 0; sys < L->n_sys; sys++) {
+    if (L->sched.n_steps > 0) pb_solve_experiment(S, *L, sys);
+    else pb_solve_system(S, *L, sys);
+  }
   free(sm);
   return 0;
 }

@@ -96,7 +96,27 @@ def input_params():
                    input_names=["a", "b"], input_sizes=[1, 2], nominal=[0.1, 0.2, 0.3])
 
 
+def cccv_toy():
+    """A constant-current / constant-voltage toy with the structure of the unified experiment model
+    (simulation.py:269-416): one differential state q, one algebraic "current variable" i whose constraint is selected by the
+    input ``mode`` (1: i = value, 2: v = value with v = q - R i), and a combined experiment event selected the same way
+    (mode 1: sgn (v - thr), mode 2: |i| - thr).  q' = -i, q(0) = 1.  Every step has a closed form (tests/test_experiment.py)."""
+    b = ModelBundle()
+    g = b.graph
+    q, i = g.state(0), g.state(1)
+    R, mode, sgn, thr, value = (g.input(k) for k in range(5))     # sorted names: R, mode, sgn, thr, value
+    v = g.sub(q, g.mul(R, i))
+    is_cc = g.binary(ir.LE, mode, g.const(1.5))
+    rhs = [g.neg(i), g.select(is_cc, g.sub(i, value), g.sub(v, value))]
+    ic = [g.const(1.0), g.const(0.0)]
+    ev_exp = g.select(is_cc, g.mul(sgn, g.sub(v, thr)), g.sub(g.unary(ir.ABS, i), thr))
+    ev = [g.sub(g.const(10.0), q), ev_exp]
+    return _finish(b, "kat_cccv", rhs, ic, 1, ev, ["q max", "Combined termination [experiment]"], {"v": [v], "i": [i]},
+                   input_names=["R", "mode", "sgn", "thr", "value"], input_sizes=[1] * 5, nominal=[0.1, 1.0, 1.0, 0.5, 1.0])
+
+
 ALL = {
+    "kat_cccv": cccv_toy,
     "kat_roberts": roberts,
     "kat_decay": decay,
     "kat_growth": lambda: growth(None),

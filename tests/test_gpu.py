@@ -449,3 +449,62 @@ def test_batched_observation_on_the_device():
     np.testing.assert_allclose(got[:, 1:4, 0], fixed["y"][:, 1:4, 0], rtol=0, atol=1e-4)
     with pytest.raises(SolverError, match="yp"):
         s.observe(s.solve_arrays([0.0, 900.0], p, t_interp=np.linspace(0, 900, 10)), p, t_obs=t_obs)
+
+
+# ---- experiment schedules on the device (8f-2, BASELINE config 5) ---------------------------------------------------------
+def test_experiment_toy_closed_forms_on_the_device():
+    from tests.test_experiment import closed_form, cccv_schedule
+    from pybamm_b200.experiment import STEP_EXPERIMENT_EVENT, STEP_FINAL_TIME
+
+    b = util.bundle("kat_cccv")
+    s = BatchedIDASolver(b, rtol=1e-9, atol=1e-11)
+    Rs = np.linspace(0.05, 0.25, 33)
+    p = np.zeros((len(Rs), 5))
+    p[:, b.input_names.index("R")] = Rs
+    r = s.solve_experiment(cccv_schedule(2), p)
+    assert np.all(r["flag"] == 1)
+    for i, R in enumerate(Rs):
+        dts, qs = closed_form(R)
+        np.testing.assert_array_equal(r["step_term"][i][:4], [STEP_EXPERIMENT_EVENT, STEP_FINAL_TIME, STEP_EXPERIMENT_EVENT, STEP_EXPERIMENT_EVENT])
+        t_end = 0.0
+        for k in range(4):
+            j = r["step_end"][i, k] - 1
+            t_end += dts[k]
+            assert abs(r["t"][i, j] - t_end) < 1e-6 and abs(r["y"][i, j, 0] - qs[k]) < 1e-7
+
+
+def test_dfn_cccv_three_cycles_batch_against_the_reference_loop():
+    """BASELINE config 5 at test size: DFN unified-experiment model, 3 x (discharge 1C to 2.5 V / rest 1 h / charge 0.3C to
+    4.2 V / hold 4.2 V to C/50) for a batch of input sets in ONE launch; two of them against the reference's step loop restated
+    around the CPU oracle (tests/util.oracle_experiment)."""
+    from pybamm_b200.experiment import STEP_EXPERIMENT_EVENT, STEP_FINAL_TIME, ExperimentSchedule
+    from tests.util import oracle_experiment
+
+    b = util.bundle("dfn_cccv")
+    sched = ExperimentSchedule.from_meta(b.meta["experiment"])
+    rng = np.random.default_rng(20265)
+    n = 64
+    p = np.tile(np.array(b.meta["nominal_inputs"]), (n, 1))
+    for nm, lo, hi in (("Negative particle diffusivity [m2.s-1]", -14, -13), ("Positive particle diffusivity [m2.s-1]", -15, -14)):
+        p[:, b.input_names.index(nm)] = 10 ** rng.uniform(lo, hi, n)
+    p[:, b.input_names.index("Initial concentration in electrolyte [mol.m-3]")] = rng.uniform(900, 1100, n)
+    s = BatchedIDASolver(b, rtol=1e-8, atol=1e-8, output_variables=["Voltage [V]", "Current [A]"])
+    r = s.solve_experiment(sched, p)
+    assert np.all(r["flag"] == 1), np.unique(r["flag"], return_counts=True)
+    expect = [STEP_EXPERIMENT_EVENT, STEP_FINAL_TIME, STEP_EXPERIMENT_EVENT, STEP_EXPERIMENT_EVENT] * 3
+    for i in range(n):
+        np.testing.assert_array_equal(r["step_term"][i], expect)
+        ends = r["step_end"][i] - 1
+        np.testing.assert_allclose(r["y"][i, ends[0::4], 0], 2.5, atol=1e-6)         # every discharge ends at the cut-off
+        np.testing.assert_allclose(r["y"][i, ends[2::4], 0], 4.2, atol=1e-6)         # every charge at 4.2 V
+        np.testing.assert_allclose(r["y"][i, ends[3::4], 1], -0.1, atol=1e-6)        # every hold at C/50
+    ref = oracle_experiment("dfn_cccv", sched, p[:2], rtol=1e-8, atol=1e-8)
+    for i in range(2):
+        np.testing.assert_array_equal(r["step_end"][i], ref[i]["step_end"])
+        k = int(r["n_t"][i])
+        # the hold steps end where |dI/dt| ~ 1e-6 A/s: at rtol = atol = 1e-8 their event times are defined to ~1e-2 s only,
+        # and every later step inherits the shift
+        np.testing.assert_allclose(r["t"][i, :k], ref[i]["t"], rtol=0, atol=5e-2)
+        ends = set(ref[i]["step_end"] - 1)
+        inner = np.array([j for j in range(k) if j not in ends])
+        assert np.max(np.abs(r["y"][i, inner, 0] - ref[i]["v"][inner, 0])) < 5e-6      # voltage over 3 cycles (errors of event times add up)

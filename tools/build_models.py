@@ -25,8 +25,33 @@ CONFIGS = {
 }
 
 
+INPUTS_C5 = INPUTS_C3[1:]          # config 5: the inputs of config 3 minus the current (the experiment sets it)
+CCCV_CYCLE = ("Discharge at 1C until 2.5 V", "Rest for 1 hour", "Charge at 0.3C until 4.2 V", "Hold at 4.2 V until C/50")
+EXPERIMENTS = {"dfn_cccv": ("DFN", [CCCV_CYCLE] * 3, INPUTS_C5)}
+
+
+def build_experiment(config: str):
+    """BASELINE config 5: (pybamm, discretised *unified* experiment model, input names, ExperimentSchedule).
+    Simulation(..., experiment_model_mode="unified").build_for_experiment() (simulation.py:269-416)."""
+    pybamm = env.load()
+    from pybamm.input.parameters.lithium_ion.Chen2020 import get_parameter_values
+
+    from pybamm_b200.experiment import schedule_from_simulation
+
+    cls, cycles, input_names = EXPERIMENTS[config]
+    model = getattr(pybamm.lithium_ion, cls)()
+    pv = pybamm.ParameterValues(get_parameter_values())
+    pv.update({n: "[input]" for n in input_names})
+    sim = pybamm.Simulation(model, parameter_values=pv, experiment=pybamm.Experiment(cycles), experiment_model_mode="unified")
+    sim.build_for_experiment()
+    built = sim._built_experiment_model
+    return pybamm, built, sorted(ip.name for ip in built.input_parameters), schedule_from_simulation(sim)
+
+
 def build(config: str):
     """Return (pybamm, discretised model, input names) for a named config."""
+    if config in EXPERIMENTS:
+        return build_experiment(config)[:3]
     pybamm = env.load()
     from pybamm.input.parameters.lithium_ion.Chen2020 import get_parameter_values
 
@@ -54,4 +79,7 @@ def nominal_inputs(config: str) -> dict:
         "Positive particle diffusivity [m2.s-1]": 4e-15,
         "Initial concentration in electrolyte [mol.m-3]": 1000.0,
     }
+    vals.update({"Ambient temperature [K]": 298.15, "Experiment step index": 1.0, "Experiment step value": 5.0})
+    if config in EXPERIMENTS:
+        return {n: vals[n] for n in list(EXPERIMENTS[config][2]) + ["Ambient temperature [K]", "Experiment step index", "Experiment step value"]}
     return {n: vals[n] for n in CONFIGS[config][3]}

@@ -20,15 +20,21 @@ import sys
 import numpy as np
 import scipy.sparse as sp
 
-from tools.build_models import CONFIGS, build, nominal_inputs
+from tools.build_models import CONFIGS, EXPERIMENTS, build, build_experiment, nominal_inputs
 from pybamm_b200.bundle import bundle_from_pybamm
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def freeze(config: str, n_points=6, seed=20260):
-    pybamm, model, names = build(config)
-    b = bundle_from_pybamm(model, inputs=names, name=config)
+    schedule = None
+    if config in EXPERIMENTS:
+        pybamm, model, names, schedule = build_experiment(config)
+        b = bundle_from_pybamm(model, inputs=names, variables=("Voltage [V]", "Current [A]"), name=config)
+        b.meta["experiment"] = schedule.to_meta()
+    else:
+        pybamm, model, names = build(config)
+        b = bundle_from_pybamm(model, inputs=names, name=config)
     nom = nominal_inputs(config)
     b.meta["nominal_inputs"] = [float(nom[n]) for n in b.input_names]
     b.meta["config"] = config
@@ -47,9 +53,13 @@ def freeze(config: str, n_points=6, seed=20260):
     p_nom = np.array(b.meta["nominal_inputs"])
     for k in range(n_points):
         p = p_nom * (1.0 + (0.2 * rng.uniform(-1, 1, len(p_nom)) if k else 0.0))
+        if schedule is not None:      # the schedule's own inputs are selectors: take them from its rows, never perturbed
+            row = schedule.over_val[k % schedule.n_steps]
+            for nm, v in zip(schedule.over_names, row):
+                p[b.input_names.index(nm)] = v
         inputs = {n: float(v) for n, v in zip(b.input_names, p)}
         y0 = model.concatenated_initial_conditions.evaluate(0.0, None, None, inputs).reshape(-1)
-        y = y0 * (1.0 + (0.03 * rng.standard_normal(len(y0)) if k else 0.0))
+        y = y0 * (1.0 + ((0.003 if schedule is not None else 0.03) * rng.standard_normal(len(y0)) if k else 0.0))
         t = float(100.0 * k)
         f = rhs_alg.evaluate(t, y, None, inputs).reshape(-1)
         g = np.array([float(np.asarray(e.evaluate(t, y, None, inputs)).reshape(-1)[0]) for e in events])
