@@ -610,13 +610,102 @@ def run_inproc_arm(args):
     return 0
 
 
+def sample_inputs_c5(bundle, n, rng):
+    """Config 5: the inputs of config 3 minus the current; the schedule's own inputs are set by the schedule."""
+    p = np.tile(np.asarray(bundle.meta["nominal_inputs"], dtype=np.float64), (n, 1))
+    for nm, fn in (("Negative particle diffusivity [m2.s-1]", lambda: 10 ** rng.uniform(-14, -13, n)),
+                   ("Positive particle diffusivity [m2.s-1]", lambda: 10 ** rng.uniform(-15, -14, n)),
+                   ("Initial concentration in electrolyte [mol.m-3]", lambda: rng.uniform(900, 1100, n))):
+        p[:, bundle.input_names.index(nm)] = fn()
+    return np.ascontiguousarray(p)
+
+
+def run_experiment_arm(args):
+    """BASELINE config 5: DFN unified-experiment model, 3 x (discharge 1C to 2.5 V / rest 1 h / charge 0.3C to 4.2 V / hold 4.2 V
+    to C/50), n_sys input sets, the whole schedule inside one kernel launch per step of the bench.  The reference has no
+    batched path for this (Simulation.solve refuses a list of inputs with an experiment, simulation.py:832-835): its baseline is
+    a loop over the input sets of the per-step solver.step loop -- here that loop around the CPU oracle, one thread per set."""
+    import torch
+    from concurrent.futures import ThreadPoolExecutor
+
+    from oracle.experiment_loop import oracle_experiment
+    from pybamm_b200 import BatchedIDASolver, build
+    from pybamm_b200.experiment import ExperimentSchedule
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this solver has no CPU fallback")
+    bundle = build.load_bundle(args.model)
+    sched = ExperimentSchedule.from_meta(bundle.meta["experiment"])
+    n = args.n_sys
+    p = sample_inputs_c5(bundle, n, np.random.default_rng(20260))
+    solver = BatchedIDASolver(bundle, rtol=RTOL, atol=ATOL, output_variables=["Voltage [V]", "Current [A]"], on_failure="ignore")
+    for _ in range(max(1, min(args.warmup, 2))):
+        r = solver.solve_experiment(sched, p)
+    steps = max(1, min(args.steps, 5))
+    sampler = ClockSampler(0)
+    sampler.start()
+    t0 = time.perf_counter()
+    kernel_ms = []
+    for _ in range(steps):
+        r = solver.solve_experiment(sched, p)
+        kernel_ms.append(solver.last_kernel_ms)
+    dt = time.perf_counter() - t0
+    clocks = sampler.stop()
+    ok = bool(np.all(r["flag"] == 1))
+    cores = os.cpu_count() or 1
+    o = cpu_oracle(bundle, fast=True)
+    n_cpu = min(2 * cores, n)
+
+    def one(i):
+        return oracle_experiment(bundle, o, sched, p[i:i + 1], rtol=RTOL, atol=ATOL, save_vars=False, lu="sparse")[0]
+
+    tc = time.perf_counter()
+    with ThreadPoolExecutor(max_workers=cores) as pool:
+        refs = list(pool.map(one, range(n_cpu)))
+    cpu_s = time.perf_counter() - tc
+    # parity on the CPU sample: same step terminations and point counts, end voltages of every step, voltage over the grid
+    worst_v, worst_t, same = 0.0, 0.0, True
+    for i, ref in enumerate(refs):
+        if not (np.array_equal(ref["step_end"], r["step_end"][i]) and np.array_equal(ref["step_term"], r["step_term"][i])):
+            same = False
+            continue
+        k = int(r["n_t"][i])
+        ends = set(ref["step_end"] - 1)
+        inner = np.array([j for j in range(k) if j not in ends])
+        v_ref = np.array([bundle.eval_variable("Voltage [V]", ref["t"][j], ref["y"][j], np.r_[p[i]])[0] for j in inner[::7]])
+        worst_v = max(worst_v, float(np.max(np.abs(r["y"][i, inner[::7], 0] - v_ref))))
+        worst_t = max(worst_t, float(np.max(np.abs(r["t"][i, :k] - ref["t"]))))
+    cfg = {"workload": f"DFN Chen2020 unified experiment model, CCCV x 3 cycles (12 steps), {n} input sets varying 3 parameters",
+           "model_states": bundle.n_states, "n_sys_total": n, "rtol": RTOL, "atol": ATOL, "steps_of_the_schedule": sched.n_steps,
+           "output": "Voltage [V], Current [A] at every step's period grid", "l2": "inputs larger than L2 are not needed: state is on chip"}
+    value = n * steps / dt
+    line = {"metric": f"DFN CCCV experiments/sec ({n} input sets, 3 cycles)", "value": n / (float(np.mean(kernel_ms)) * 1e-3), "unit": "experiments/s",
+            "n_gpus": 1, "steps": steps, "warmup": args.warmup, "ms_per_step": float(np.mean(kernel_ms)), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg, "clocks": clocks,
+            "gpu_launches": steps, "all_integrations_succeeded": ok,
+            "e2e": {"value": value, "unit": "experiments/s", "call": "BatchedIDASolver.solve_experiment(schedule, inputs) with host buffers",
+                    "d2h_bytes_per_step": int(n * sched.capacity * 8 * 3)},
+            "gpu_ida_counters_mean": dict(zip(("nsteps", "nrevals", "nlinsetups", "netfails", "nniters", "nncfails", "njevals", "nge"),
+                                              r["stats"].astype(float).mean(axis=0).tolist())),
+            "cpu_baseline": {"value": n_cpu / cpu_s, "unit": "experiments/s", "cores": cores, "kind": "port",
+                             "sample": f"first {n_cpu} input sets, one thread each",
+                             "note": "the reference's per-step solver.step loop restated around the CPU oracle (oracle/experiment_loop.py), "
+                                     "static sparse LU, -O3 -march=native; the reference itself has no batched experiment path"},
+            "parity": {"systems": n_cpu, "same_step_terminations_and_counts": same, "max_abs_dV": worst_v, "max_abs_dt": worst_t,
+                       "bars": {"dV": 5e-6, "dt": 5e-2, "why": "hold steps end where |dI/dt| ~ 1e-6 A/s: event times are defined to ~1e-2 s at 1e-8"}},
+            }
+    line["parity_ok"] = bool(same and ok and worst_v <= 5e-6 and worst_t <= 5e-2)
+    print(json.dumps(line), flush=True)
+    return 0 if line["parity_ok"] else 3
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--model", default="dfn", choices=["spm", "spme", "dfn"])
+    ap.add_argument("--model", default="dfn", choices=["spm", "spme", "dfn", "dfn_cccv"])
     ap.add_argument("--n-sys", type=int, default=10000, help="input sets per GPU (weak) or in total (strong, in-process)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--inproc-devices", type=int, default=0, help="run the one-process multi-device arm on this many GPUs")
@@ -626,6 +715,10 @@ def main():
     ap.add_argument("--full-state-e2e", type=int, default=1000, help="rows of the full-state end-to-end number (0: skip)")
     ap.add_argument("--no-full-state", action="store_true", help="skip the full-state (output_mode 0) secondary numbers")
     args = ap.parse_args()
+    if args.model == "dfn_cccv":
+        if args.n_sys == 10000:
+            args.n_sys = 4000          # BASELINE config 5
+        return run_experiment_arm(args)
     if args.impl == "reference":
         return run_reference_arm(args)
     if args.inproc_devices > 0:
