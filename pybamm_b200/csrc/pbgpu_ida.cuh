@@ -1874,7 +1874,8 @@ static PB_DEV double pb_alg_res_norm(pb_sys& S, double t, const double* y) {
 // NonlinearSolver::RunNewtonLoop (NonlinearSolver.inl:100-177) on the algebraic sub-block; the
 // sub-block system J_aa d = g is solved through the full static LU with identity differential rows.
 // y (= S_YY) is updated in place.  Returns 1 on success.
-static PB_DEV int pb_newton_ic(pb_sys& S, double t, double* init_norm, double* final_norm) {
+static PB_DEV int pb_newton_ic(pb_sys& S, double t, double* init_norm, double* final_norm, const int max_iter,
+                               const int max_backtracks) {
   double* y = S_YY(S);
   double* xsave = S_EE(S);
   double* res = S_DELTA(S);
@@ -1887,7 +1888,7 @@ static PB_DEV int pb_newton_ic(pb_sys& S, double t, double* init_norm, double* f
     xsave[i] = y[i];
   }
   PB_SYNC();
-  for (int iter = 0; iter < S.max_iter_ic; iter++) {
+  for (int iter = 0; iter < max_iter; iter++) {
     const double res_norm = pb_alg_res_norm(S, t, y);
     if (iter == 0) *init_norm = res_norm;
     *final_norm = res_norm;
@@ -1922,7 +1923,7 @@ static PB_DEV int pb_newton_ic(pb_sys& S, double t, double* init_norm, double* f
     for (int i = PBM_NDIFF + PB_TID; i < PBM_N; i += PB_TEAM) xsave[i] = y[i];
     PB_SYNC();
     double alpha = 1.0;
-    for (int ls = 0; ls < S.max_backtracks_ic; ls++) {
+    for (int ls = 0; ls < max_backtracks; ls++) {
       for (int i = PBM_NDIFF + PB_TID; i < PBM_N; i += PB_TEAM) y[i] = xsave[i] - alpha * del[i];
       PB_SYNC();
       const double trial = pb_alg_res_norm(S, t, y);
@@ -1947,10 +1948,19 @@ static PB_DEV void pb_consistent_init(pb_sys& S, double t, int calc_ic) {
       backup[i] = phi0[i];
     }
     PB_SYNC();
-    double in = 0.0, fn = 0.0;
-    const int ok = pb_newton_ic(S, t, &in, &fn);
-    if (ok || fn <= in) {
-      for (int i = PB_TID; i < PBM_N; i += PB_TEAM) phi0[i] = y[i];
+    // First the Newton loop of NonlinearSolver (five halvings per iteration); when it fails AND leaves a larger residual
+    // than it started from, the reference restores the state and hands over to IDACalcIC (IDAKLUSolverOpenMP.inl:838-850),
+    // whose Newton carries a proper backtracking line search.  The second pass below plays that role: the same iteration
+    // from the restored state with up to thirty halvings per iteration (a step is always found unless the Jacobian is singular).
+    for (int attempt = 0; attempt < 2; attempt++) {
+      double in = 0.0, fn = 0.0;
+      const int ok = pb_newton_ic(S, t, &in, &fn, S.max_iter_ic, attempt ? 30 : S.max_backtracks_ic);
+      if (ok || fn <= in) {
+        for (int i = PB_TID; i < PBM_N; i += PB_TEAM) phi0[i] = y[i];
+        PB_SYNC();
+        break;
+      }
+      for (int i = PB_TID; i < PBM_N; i += PB_TEAM) y[i] = backup[i];
       PB_SYNC();
     }
   }

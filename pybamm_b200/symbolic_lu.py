@@ -332,7 +332,11 @@ def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01, tea
             print(f"[symbolic_lu] ordering {name} failed: {e}")
     best = None
     for name, perm_r, perm_c in candidates:
-        s = _build(n, rows, cols, perm_r, perm_c, name, team=team)
+        try:
+            s = _build(n, rows, cols, perm_r, perm_c, name, team=team)
+        except AssertionError as e:      # an ordering the cluster schedule cannot express (unsymmetric fill): next candidate
+            print(f"[symbolic_lu] ordering {name} rejected: {e}")
+            continue
         # cost proxy (cycles per factorisation interval): ~30 triangular solves per factorisation (measured on the
         # battery models); the L+U values and the solve stream must stay in shared memory (8 + ~6 bytes per entry)
         score = 30.0 * s.est_cycles_solve + s.est_cycles_factor + 30.0 * s.nnz_lu

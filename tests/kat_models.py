@@ -115,7 +115,19 @@ def cccv_toy():
                    input_names=["R", "mode", "sgn", "thr", "value"], input_sizes=[1] * 5, nominal=[0.1, 1.0, 1.0, 0.5, 1.0])
 
 
+def hard_ic():
+    """An algebraic initial condition a plain Newton cannot reach: u' = -u, 0 = atan(10 (v - 1)), v(0) = 5.  From the flat
+    part of the arctangent the full step overshoots by two orders of magnitude; five halvings are not enough, the
+    IDACalcIC-like second pass (pb_consistent_init) is."""
+    b = ModelBundle()
+    g = b.graph
+    u, v = g.state(0), g.state(1)
+    rhs = [g.neg(u), g.unary(ir.ATAN, g.mul(g.const(10.0), g.sub(v, g.const(1.0))))]
+    return _finish(b, "kat_hard_ic", rhs, [g.const(1.0), g.const(5.0)], 1, variables={"v": [v]})
+
+
 ALL = {
+    "kat_hard_ic": hard_ic,
     "kat_cccv": cccv_toy,
     "kat_roberts": roberts,
     "kat_decay": decay,

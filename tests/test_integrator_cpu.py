@@ -197,3 +197,15 @@ def test_device_observation_matches_the_reference_semantics():
     fixed = e.solve([0.0, 900.0], p, t_interp=t_obs[1:5], rtol=1e-6, atol=1e-8, save_vars=True)
     for i in range(2):
         np.testing.assert_allclose(got[i, 1:5, 0], fixed["y"][i][1:5, 0], rtol=0, atol=5e-5)
+
+
+def test_failed_ic_newton_gets_a_second_pass_with_a_real_line_search():
+    # IDAKLUSolverOpenMP.inl:838-850: when the Newton of NonlinearSolver fails, IDACalcIC takes over
+    e = util.emu("kat_hard_ic")
+    r = e.solve([0.0, 1.0], np.zeros((1, 0)), t_interp=np.linspace(0, 1, 5), rtol=1e-8, atol=1e-10)
+    assert r["flag"][0] in (0, 1)
+    np.testing.assert_allclose(r["y"][0][:, 1], 1.0, atol=1e-8)          # the algebraic state found its root
+    np.testing.assert_allclose(r["y"][0][:, 0], np.exp(-r["t"][0]), rtol=1e-6)
+    one = e.solve([0.0, 1.0], np.zeros((1, 0)), t_interp=np.linspace(0, 1, 5), rtol=1e-8, atol=1e-10,
+                  options={"max_linesearch_backtracks_ic": 30})
+    np.testing.assert_allclose(one["y"][0], r["y"][0], atol=1e-9)

@@ -59,7 +59,11 @@ def freeze(config: str, n_points=6, seed=20260):
                 p[b.input_names.index(nm)] = v
         inputs = {n: float(v) for n, v in zip(b.input_names, p)}
         y0 = model.concatenated_initial_conditions.evaluate(0.0, None, None, inputs).reshape(-1)
-        y = y0 * (1.0 + ((0.003 if schedule is not None else 0.03) * rng.standard_normal(len(y0)) if k else 0.0))
+        noise = rng.standard_normal(len(y0))
+        for amp in ((0.003,) if schedule is not None else (0.03, 0.01, 0.003, 0.001)):      # an unphysical state overflows sinh
+            y = y0 * (1.0 + (amp * noise if k else 0.0))
+            if np.all(np.isfinite(rhs_alg.evaluate(float(100.0 * k), y, None, inputs))):
+                break
         t = float(100.0 * k)
         f = rhs_alg.evaluate(t, y, None, inputs).reshape(-1)
         g = np.array([float(np.asarray(e.evaluate(t, y, None, inputs)).reshape(-1)[0]) for e in events])
