@@ -213,6 +213,7 @@ def _emit_template(em: _Emitter, tp, dest, lines, ind):
         lines.append(f"{ind}const double v{k} = {e};")
     oe = _slot_expr(em, tp.out, "q", "o")
     lines.append(f"{ind}{dest}[{oe}] = {ref(tp.result)};")
+    lines.append(f"{ind}PB_PAD")        # empty; the code-size sensitivity experiment defines it as a run of NOPs
 
 
 def emit_program(prog: Program, fname: str, prefix: str):
@@ -334,6 +335,59 @@ PAR_GENERIC = bool(int(__import__("os").environ.get("PBGPU_PAR_GENERIC", "1")))
 PAR_RUN_MIN = int(__import__("os").environ.get("PBGPU_PAR_RUN_MIN", "99"))
 
 
+# Measured on the DFN (5 920 systems): the table-driven loop halves pb_solve_program (11.5 -> 5.8 KB) but adds ~250 cycles of
+# descriptor look-ups and dynamic dispatch to each of the 16 records (triangular solve 16.6k -> 20.7k cycles): 4 884 against
+# 4 939 sims/s.  Off; the straight-line call sequence stays the default.
+SOLVE_TABLE = bool(int(__import__("os").environ.get("PBGPU_SOLVE_TABLE", "0")))
+
+
+def emit_solve_table(sym: slu.SymbolicLU):
+    """The triangular solves as a TABLE walked by one small loop (pb_solve_program in pbgpu_ida.cuh) instead of forty
+    straight-line call sites (10.7 KB of code for the DFN, fetched by every Newton iteration: the integration is bound by
+    instruction fetch).  Per (record, warp) two words: offset | nt << 16 and G | mlg << 8 | mode << 16 | kind << 24 with
+    kind 1 PAR, 2 forward CHAIN, 3 backward CHAIN, 0 nothing to do; per record the synchronisation that follows it
+    (0 none, 1 warp, 2 team, 3: the record is the dense top block).  Returns None when the stream has a record kind the
+    table does not cover (the straight-line program is emitted then)."""
+    nw_max = 0
+    rows = []          # (sync, {warp: (d0, d1)}, dense_off)
+    for r in sym.solve_program:
+        if r["kind"] == 3:
+            rows.append((3, {}, r["offset"] + slu.SEQ_HDR + r["nblocks"]))
+            continue
+        if r["kind"] not in (1, 2):
+            return None
+        boff = r["offset"] + slu.SEQ_HDR + (1 if r.get("narrow") else r["nblocks"])
+        ent = {}
+        for v in range(r["nblocks"]):
+            nt = r["desc"][v] & 0xFFFF
+            wv = r["first_warp"] + v
+            if r["kind"] == 1:
+                G, mlg = r["param"] & 0xFF, r["param"] >> 8
+                if boff >= 65536 or nt >= 65536 or mlg >= 256 or G >= 256:
+                    return None
+                ent[wv] = (boff | nt << 16, G | mlg << 8 | r["mode"] << 16 | 1 << 24)
+                boff += (1 + mlg) * nt
+            else:
+                ent[wv] = (boff | nt << 16, (3 if (r["mode"] & 1) else 2) << 24)
+                boff += 3 * nt
+            nw_max = max(nw_max, wv + 1)
+        rows.append((r["sync"], ent, 0))
+    nw = max(nw_max, 1)
+    flat, sync = [], []
+    dense_off = 0
+    for sy, ent, doff in rows:
+        sync.append(sy)
+        if sy == 3:
+            dense_off = doff
+        for wv in range(nw):
+            d = ent.get(wv, (0, 0))
+            flat += [d[0], d[1]]
+    text = f"#define PBM_SOLVE_NREC {len(rows)}\n#define PBM_SOLVE_NW {nw}\n#define PBM_SOLVE_DENSE_OFF {dense_off}\n"
+    text += f"static PB_CTABLE const unsigned int pbm_solve_desc[{len(flat)}] = {{" + ", ".join(f"{x}u" for x in flat) + "};\n"
+    text += f"static PB_CTABLE const unsigned char pbm_solve_sync[{len(sync)}] = {{" + ", ".join(str(x) for x in sync) + "};\n"
+    return text
+
+
 def emit_solve_program(sym: slu.SymbolicLU) -> str:
     """The triangular solves as a call sequence: one call per record of the solve stream, expanded inside
     pb_solve_program (pbgpu_ida.cuh), which defines st, lu, w.  Runs of single-warp PAR records (the top of the
@@ -450,6 +504,9 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
     out.append("#define PB_POWM025(x) pow(x, -0.25)")
     out.append("#define PB_POWM125(x) pow(x, -1.25)")
     out.append("#endif")
+    out.append("#ifndef PB_PAD")
+    out.append("#define PB_PAD")
+    out.append("#endif")
     out.append("#ifndef PB_SQRT")
     out.append("#define PB_SQRT(x) sqrt(x)")
     out.append("#endif")
@@ -527,6 +584,9 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
                 lines.append(f"#define PBM_FAC_CHUNK_WORDS {max(b - a for (a, _), (b, _) in zip(chunks, chunks[1:] + [(len(sym.factor_stream), 0)]))}")
                 lines.append(f"static PB_CTABLE const unsigned int pbm_fac_chunk[{len(flat)}] = {{" + ", ".join(f"{x}u" for x in flat) + "};")
         lines.append(emit_solve_program(sym))
+        table = emit_solve_table(sym) if SOLVE_TABLE else None
+        if table is not None:
+            lines.append(table)
         out.append("\n".join(lines))
         out.append(f"#define PBM_FLOPS_FACTOR {sym.flops_factor}")
         out.append(f"#define PBM_FLOPS_SOLVE {sym.flops_solve}")

@@ -745,9 +745,33 @@ static_assert(PBM_DENSE_N * PBM_DENSE_G <= PB_TEAM, "dense block wider than the 
 static __device__ __noinline__ void pb_solve_program(const unsigned int* PB_RESTRICT st, const double* PB_RESTRICT lu,
                                                      double* PB_RESTRICT w, const double* PB_RESTRICT wd) {
   PB_DENSE_PROLOGUE(wd)
+#ifdef PBM_SOLVE_NREC
+  // table-driven: one loop over the records, this warp's descriptor from constant memory (codegen.emit_solve_table)
+  for (int r = 0; r < PBM_SOLVE_NREC; r++) {
+    const unsigned int sy = pbm_solve_sync[r];
+#if PBM_DENSE_N > 0
+    if (sy == 3u) {
+      PB_DENSE_REC(PBM_SOLVE_DENSE_OFF)
+      continue;
+    }
+#endif
+    if (PB_WARP < PBM_SOLVE_NW) {
+      const unsigned int d0 = pbm_solve_desc[(r * PBM_SOLVE_NW + PB_WARP) * 2], d1 = pbm_solve_desc[(r * PBM_SOLVE_NW + PB_WARP) * 2 + 1];
+      const unsigned int kind = d1 >> 24;
+      const unsigned int* blk = st + (d0 & 0xFFFFu);
+      const int nt = (int)(d0 >> 16);
+      if (kind == 1u) pb_par_generic(blk, nt, (int)(d1 & 0xFFu), (int)((d1 >> 8) & 0xFFu), (d1 >> 16) & 0xFFu, lu, w);
+      else if (kind == 2u) pb_chain_rec<0>(blk, nt, lu, w);
+      else if (kind == 3u) pb_chain_rec<1>(blk, nt, lu, w);
+    }
+    if (sy == 2u) PB_SYNC();
+    else if (sy == 1u) PB_SYNCWARP();
+  }
+#else
 #define PB_REC_MARK
   PBM_SOLVE_PROGRAM
 #undef PB_REC_MARK
+#endif
 }
 #endif
 

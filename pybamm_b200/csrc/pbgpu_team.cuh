@@ -95,6 +95,11 @@ static __device__ __noinline__ double pb_f_powm125(double x) { return rsqrt(sqrt
 #define PB_POWM125(x) pb_f_powm125(x)
 #endif
 // FP64 division is a 20-instruction sequence with a slow path: one shared copy (PB_INLINE_DIV=1 inlines it again).
+#ifdef PB_PAD_NOPS   /* experiment: how much does the integration slow down per KB of (executed) code?  16 NOPs = 256 B per template */
+#define PB_PAD1 (void)pad_[0];
+#define PB_PAD { volatile const double* pad_ = p; PB_PAD1 PB_PAD1 PB_PAD1 PB_PAD1 PB_PAD1 PB_PAD1 PB_PAD1 PB_PAD1 \
+                 PB_PAD1 PB_PAD1 PB_PAD1 PB_PAD1 PB_PAD1 PB_PAD1 PB_PAD1 PB_PAD1 }
+#endif
 #ifndef PB_INLINE_SQRT
 static __device__ __noinline__ double pb_f_sqrt(double x) { return sqrt(x); }
 #define PB_SQRT(x) pb_f_sqrt(x)

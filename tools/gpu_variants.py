@@ -16,8 +16,8 @@ import numpy as np
 
 VARIANTS = [
     # tag, env of the code generator, -D defines, build_model keyword arguments
+    ("_prog", {"PBGPU_SOLVE_TABLE": "0"}, (), {}),
     ("", {}, (), {}),
-    ("_rolled", {}, ("PB_VEC_ROLLED",), {}),
 ]
 
 
