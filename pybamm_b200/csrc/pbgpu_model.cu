@@ -159,9 +159,29 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_e
         t0 = clock64();
         for (int r = 0; r < reps; r++) acc += pb_wrms(S, S_PHI(S, r % 6));
         c[5] = clock64() - t0;
+        long long c_ev = 0, c_var = 0;
+#if PBM_NEV > 0
+        t0 = clock64();
+        for (int r = 0; r < reps; r++) {
+          pbm_events(y, S_P(S), E.t, 0.0, S_GHI(S), S_TMP(S));
+          PB_SYNC();
+        }
+        c_ev = clock64() - t0;
+#endif
+#if PBM_NVAR > 0
+        t0 = clock64();
+        for (int r = 0; r < reps; r++) {
+          pbm_vars(y, S_P(S), E.t, 0.0, out, S_TMP(S));
+          PB_SYNC();
+        }
+        c_var = clock64() - t0;
+#endif
         if (PB_TID == 0) {
           for (int k = 0; k < 6 && k < E.out_len; k++) gout[k] = (double)c[k] / reps;
-          if (E.out_len > 6) gout[6] = acc;
+          if (E.out_len > 7) {
+            gout[6] = (double)c_ev / reps + (acc == 12345.678 ? 1.0 : 0.0);
+            gout[7] = (double)c_var / reps;
+          }
         }
         if (E.out_len >= 8 + 3) {
           pb_lu_solve_t<1>(S, out, gout + 8);   // warm

@@ -20,5 +20,5 @@ y = np.array([o.eval("ic", None, p[i]) for i in range(n)]) * (1 + 0.01 * rng.sta
 s = BatchedIDASolver(bundle, rtol=1e-8, atol=1e-8, output_variables=["Voltage [V]"], image_path=img)
 c = s.eval("cycles", y, p, 10.0, 0.5, rng.standard_normal((n, bundle.n_states)))
 m = c.mean(axis=0)
-print(f"{name} x{n} team {s.desc.team_size}: cycles/call  res {m[0]:.0f}  lu_solve {m[1]:.0f}  jac {m[2]:.0f}  factor {m[3]:.0f}  ewt_set {m[4]:.0f}  wrms {m[5]:.0f}")
+print(f"{name} x{n} team {s.desc.team_size}: cycles/call  res {m[0]:.0f}  lu_solve {m[1]:.0f}  jac {m[2]:.0f}  factor {m[3]:.0f}  ewt_set {m[4]:.0f}  wrms {m[5]:.0f}  events {m[6]:.0f}  vars {m[7]:.0f}")
 print("  lu_solve trace (gather, records..., scatter):", " ".join(f"{v:.0f}" for v in m[8:] if v > 0))
