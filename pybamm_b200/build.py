@@ -121,7 +121,10 @@ def build_model(bundle: ModelBundle, force=False, team=None, verbose=False, prof
     if gvec is None:
         gvec = 1 if bundle.n_states > 256 else 0   # streamed vectors in global scratch for large models (pbgpu_ida.cuh)
     if min_teams is None:
-        min_teams = 2 if gvec else 1           # register cap: two large teams per SM (65536 / (2 * team) registers each)
+        # register cap.  Large models: two 256-thread teams per SM (128 registers).  Tiny one-warp models (SPM, 42 states):
+        # without a cap the kernel takes 255 registers and only 8 warps fit an SM; 16 warps at 128 registers measured +25 %
+        # (24 / 32 warps spill too much).  In between (SPMe, 102 states) shared memory binds first and the cap only costs.
+        min_teams = 2 if gvec else (16 if (team == 32 and bundle.n_states <= 64) else 1)
     dig = _src_digest(srcs) + f"-t{team}-g{gvec}-m{min_teams}-p{int(profile)}-{'-'.join(defines)}-{'-'.join(extra_flags)}-" + hashlib.sha256(" ".join(NVCC_FLAGS).encode()).hexdigest()[:8]
     stamp = out + ".stamp"
     if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:

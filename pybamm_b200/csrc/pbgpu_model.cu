@@ -281,7 +281,7 @@ static int pb_configure(pb_dev_cfg* out, char* err, size_t errlen) {
   // shared memory they can use; small ones (SPM / SPMe: one warp per system, the CTA-per-SM limit binds first) leave
   // at least 64 KB of L1 for the index tables of the generated functions.  PBGPU_SMEM_CARVEOUT_KB / PBGPU_TEAMS_PER_SM override.
   const int per_team = (int)PB_SMEM_BYTES + 1024;  // + the per-CTA reservation
-  int carve_kb = (per_team > 48 * 1024) ? 227 : 164;
+  int carve_kb = 227;   // measured on SPMe (22 KB per team): 9 resident teams at 227 KB against 7 at 164 KB, +3.5 %
   if (const char* env = getenv("PBGPU_SMEM_CARVEOUT_KB")) carve_kb = atoi(env);
   if (carve_kb * 1024 < per_team) carve_kb = (per_team + 1023) / 1024;
   if (carve_kb > 227) carve_kb = 227;

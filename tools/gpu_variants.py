@@ -16,8 +16,11 @@ import numpy as np
 
 VARIANTS = [
     # tag, env of the code generator, -D defines, build_model keyword arguments
-    ("_prog", {"PBGPU_SOLVE_TABLE": "0"}, (), {}),
     ("", {}, (), {}),
+    ("_m8", {}, (), {"min_teams": 8}),
+    ("_m16", {}, (), {"min_teams": 16}),
+    ("_m24", {}, (), {"min_teams": 24}),
+    ("_m32", {}, (), {"min_teams": 32}),
 ]
 
 
