@@ -277,9 +277,9 @@ static int pb_configure(pb_dev_cfg* out, char* err, size_t errlen) {
   pb_dev_cfg c;
   c.num_sms = prop.multiProcessorCount;
   // Shared-memory carve-out.  The integration is latency-bound (dependent shared-memory round trips in the
-  // triangular solves), so resident teams per SM is what buys throughput: large teams (> 48 KB: DFN) take all the
-  // shared memory they can use; small ones (SPM / SPMe: one warp per system, the CTA-per-SM limit binds first) leave
-  // at least 64 KB of L1 for the index tables of the generated functions.  PBGPU_SMEM_CARVEOUT_KB / PBGPU_TEAMS_PER_SM override.
+  // triangular solves), so resident teams per SM is what buys throughput: every model takes all the shared memory the
+  // SM has (the index tables of the generated functions live in L2 either way).  PBGPU_SMEM_CARVEOUT_KB /
+  // PBGPU_TEAMS_PER_SM override.
   const int per_team = (int)PB_SMEM_BYTES + 1024;  // + the per-CTA reservation
   int carve_kb = 227;   // measured on SPMe (22 KB per team): 9 resident teams at 227 KB against 7 at 164 KB, +3.5 %
   if (const char* env = getenv("PBGPU_SMEM_CARVEOUT_KB")) carve_kb = atoi(env);
