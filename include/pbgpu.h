@@ -147,6 +147,29 @@ int pbgpu_solve_device(pbgpu_solver_t solver, int n_sys, const double* t_eval, i
                        int n_tinterp, const double* y0, const double* yp0, const double* inputs, int output_mode,
                        pbgpu_result* out, void* stream, int sync);
 
+/* pbgpu_solve_device without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments and results as pbgpu_solve_device, but the work queue and the per-team scratch vectors of
+ * the solve kernel live in a file-scope `static __device__` array of the model image instead of the solver handle's
+ * cudaMalloc'ed blocks, and the call makes no cudaMalloc / cudaFree / allocating library call.
+ *   limits   n_sys <= PBGPU_STATIC_MAX_SYSTEMS per call; the array holds at most PBGPU_STATIC_MAX_TEAMS team slots and
+ *            PBGPU_STATIC_MAX_BYTES bytes, so a large model runs on fewer teams than pbgpu_solve_device would use (same
+ *            results, lower throughput).  A larger n_sys is rejected with an error, nothing is launched.
+ *   memory   every GPU that loads the model image holds the array (<= PBGPU_STATIC_MAX_BYTES) until the process exits.
+ *   sharing  every call on a device uses the same array: the queue words are cleared on `stream` before the launch, the
+ *            team slots keep the previous call's contents (never read before written).  Calls that overlap on the GPU
+ *            (different streams, different solver handles of the same image) race: serialise them.
+ *   set-up   n_sys == 0 launches nothing and only performs the one-time set-up for the solver's device (kernel attributes,
+ *            address of the array): call it once before a region that must not touch the runtime's module loader.
+ * The launch order of pbgpu_solver_set_launch_order (stored in the handle beforehand) is honoured; experiment schedules are
+ * not available here. */
+#define PBGPU_STATIC_MAX_SYSTEMS 1024
+#define PBGPU_STATIC_MAX_TEAMS 64
+#define PBGPU_STATIC_MAX_BYTES (8u << 20)
+int pbgpu_solve_device_noalloc(pbgpu_solver_t solver, int n_sys, const double* t_eval, int n_teval, const double* t_interp,
+                               int n_tinterp, const double* y0, const double* yp0, const double* inputs, int output_mode,
+                               pbgpu_result* out, void* stream, int sync);
+
 /* Evaluate generated model functions / the sparse LU on the device for n_sys (y, p) pairs (parity tests
  * of the code generator).  which: 0 res, 1 jac (bundle CSC order), 2 events, 3 ic, 4 vars,
  * 5 solve (J - cj*M) x = rhs with rhs = y2; 8 events at per-system times t_sys = y2[sys][0] (which event ended each

@@ -35,6 +35,7 @@ typedef int (*launch_fn)(const pbgpu_launch*, void*, int, char*, size_t);
 typedef int (*eval_fn)(const pbgpu_eval_launch*, void*, int, char*, size_t);
 typedef int (*plan_fn)(int, int*, char*, size_t);
 typedef int (*observe_fn)(const pbgpu_observe_launch*, void*, int, char*, size_t);
+typedef int (*launch_static_fn)(const pbgpu_launch*, void*, int*, char*, size_t);
 
 struct DevBuf {
   void* p = nullptr;
@@ -64,6 +65,7 @@ struct pbgpu_model_s {
   eval_fn eval = nullptr;
   plan_fn plan = nullptr;
   observe_fn observe = nullptr;
+  launch_static_fn launch_static = nullptr;   // optional: images built before the entry point existed lack it
   pbgpu_model_desc desc;
   std::string path;
 };
@@ -121,6 +123,7 @@ int pbgpu_model_load(const char* path, pbgpu_model_t* model) {
   m->eval = (eval_fn)dlsym(h, "pbgpu_image_eval");
   m->plan = (plan_fn)dlsym(h, "pbgpu_image_plan");
   m->observe = (observe_fn)dlsym(h, "pbgpu_image_observe");
+  m->launch_static = (launch_static_fn)dlsym(h, "pbgpu_image_launch_static");
   if (!m->describe || !m->launch || !m->eval || !m->plan || !m->observe) {
     dlclose(h);
     delete m;
@@ -319,6 +322,69 @@ int pbgpu_solve_device(pbgpu_solver_t s, int n_sys, const double* t_eval, int n_
   const DevResult R = {out->t, out->y, out->yp, out->n_t, out->flag, out->y_term, out->stats, out->event_idx, out->t_event};
   if (launch_common(s, n_sys, t_eval, n_teval, t_interp, n_tinterp, y0, yp0, inputs, output_mode, out->n_max, R, st))
     return 1;
+  if (sync) {
+    CK(cudaEventRecord(s->ev[1], st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaEventElapsedTime(&out->kernel_ms, s->ev[0], s->ev[1]));
+    out->total_ms = out->kernel_ms;
+  }
+  return 0;
+}
+
+// pbgpu_solve_device on the model image's static scratch array: nothing here (or below it) allocates.  Not routed through
+// launch_common, whose plan_launch sizes the handle's cudaMalloc'ed team scratch.
+int pbgpu_solve_device_noalloc(pbgpu_solver_t s, int n_sys, const double* t_eval, int n_teval, const double* t_interp,
+                               int n_tinterp, const double* y0, const double* yp0, const double* inputs, int output_mode,
+                               pbgpu_result* out, void* stream, int sync) {
+  if (!s) return fail("pbgpu_solve_device_noalloc: null argument");
+  if (!s->model->launch_static)
+    return fail("pbgpu_solve_device_noalloc: the model image has no static-scratch launch (rebuild it)");
+  if (n_sys < 0) return fail("pbgpu_solve_device_noalloc: n_sys must not be negative");
+  if (n_sys > PBGPU_STATIC_MAX_SYSTEMS)
+    return fail("pbgpu_solve_device_noalloc: n_sys = " + std::to_string(n_sys) + " is beyond the static limit of " +
+                std::to_string(PBGPU_STATIC_MAX_SYSTEMS) + " systems per call (use pbgpu_solve_device, or split the batch)");
+  const pbgpu_model_desc& D = s->model->desc;
+  CK(cudaSetDevice(s->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  pbgpu_launch L;
+  memset(&L, 0, sizeof(L));
+  char err[512];
+  err[0] = 0;
+  int teams = 0;
+  if (n_sys == 0) {   // set-up only
+    if (s->model->launch_static(&L, (void*)st, &teams, err, sizeof(err))) return fail(err);
+    return 0;
+  }
+  if (!out) return fail("pbgpu_solve_device_noalloc: null argument");
+  if (output_mode == PBGPU_OUTPUT_VARS && D.n_vars < 1) return fail("the model image has no compiled output variables");
+  if (n_teval < 2) return fail("t_eval must have at least 2 entries");
+  if (D.n_inputs > 0 && !inputs) return fail("inputs has wrong number of dimensions. Expected 2 but got 0");
+  L.n_sys = n_sys;
+  L.n_eval = n_teval;
+  L.n_interp = n_tinterp;
+  L.n_max = out->n_max;
+  L.save_vars = (output_mode == PBGPU_OUTPUT_VARS);
+  L.n_ret = L.save_vars ? D.n_vars : D.n_states;
+  L.t_eval = t_eval;
+  L.t_interp = t_interp;
+  L.inputs = inputs;
+  L.y0 = y0;
+  L.yp0 = yp0;
+  L.atol = (const double*)s->atol.p;   // uploaded by pbgpu_solver_create
+  L.t_out = out->t;
+  L.y_out = out->y;
+  L.yp_out = L.save_vars ? nullptr : out->yp;
+  L.n_out = out->n_t;
+  L.flag = out->flag;
+  L.y_term = out->y_term;
+  L.stats = out->stats;
+  L.event_idx = out->event_idx;
+  L.t_event = out->t_event;
+  L.order = (s->order_n == n_sys) ? (const int*)s->order.p : nullptr;
+  L.opt = s->opt;
+  if (sync) CK(cudaEventRecord(s->ev[0], st));
+  if (s->model->launch_static(&L, (void*)st, &teams, err, sizeof(err))) return fail(err);
+  s->last_grid = teams;
   if (sync) {
     CK(cudaEventRecord(s->ev[1], st));
     CK(cudaStreamSynchronize(st));

@@ -374,6 +374,91 @@ extern "C" int pbgpu_image_launch(const pbgpu_launch* L, void* stream, int grid,
   return 0;
 }
 
+// ---- launch without any allocation (pbgpu_solve_device_noalloc) -------------------------------------------------
+// The work queue and the per-team scratch of the solve kernel in a file-scope device array instead of the solver
+// handle's cudaMalloc'ed blocks: for callers that may not allocate (CUDA graph capture, serving loops).  Every device
+// that loads the image holds the array until the process exits; every call on a device shares it, so calls that overlap
+// on the GPU race.  Layout: [queue words, padded to 256 bytes][PB_STATIC_TEAMS team slots of PB_SCRATCH_DOUBLES].
+#define PB_STATIC_QUEUE_DOUBLES (((PBGPU_QUEUE_WORDS * 4 + 255) / 256) * 32)
+#if PB_SCRATCH_DOUBLES > 0
+#define PB_STATIC_FIT ((int)((PBGPU_STATIC_MAX_BYTES / 8 - PB_STATIC_QUEUE_DOUBLES) / PB_SCRATCH_DOUBLES))
+#define PB_STATIC_TEAMS (PB_STATIC_FIT < PBGPU_STATIC_MAX_TEAMS ? PB_STATIC_FIT : PBGPU_STATIC_MAX_TEAMS)
+#else
+#define PB_STATIC_TEAMS PBGPU_STATIC_MAX_TEAMS   /* no team scratch: only the queue lives in the array */
+#endif
+#define PB_STATIC_DOUBLES (PB_STATIC_QUEUE_DOUBLES + (size_t)(PB_STATIC_TEAMS > 0 ? PB_STATIC_TEAMS : 0) * PB_SCRATCH_DOUBLES)
+static_assert(PB_STATIC_DOUBLES * 8 <= PBGPU_STATIC_MAX_BYTES, "static scratch larger than its stated maximum");
+static __device__ __align__(256) double pb_static_scratch[PB_STATIC_DOUBLES];
+
+// In host code pb_static_scratch is only a handle for the runtime, not a device address: the address is asked for once
+// per device, with that device current, and cached.
+static double* g_static_ptr[64];
+static std::mutex g_static_mutex;
+
+static int pb_static_setup(double** ptr, char* err, size_t errlen) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 64) {
+    snprintf(err, errlen, "cudaGetDevice: %s", e != cudaSuccess ? cudaGetErrorString(e) : "ordinal out of range");
+    return 1;
+  }
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  if (!g_static_ptr[dev]) {
+    double* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, pb_static_scratch);
+    if (e != cudaSuccess || !p) {
+      snprintf(err, errlen, "cudaGetSymbolAddress(pb_static_scratch) on device %d: %s", dev, cudaGetErrorString(e));
+      return 1;
+    }
+    g_static_ptr[dev] = p;
+  }
+  *ptr = g_static_ptr[dev];
+  return 0;
+}
+
+// L: as for pbgpu_image_launch, its queue and scratch fields are ignored.  L->n_sys == 0: set-up only (kernel
+// attributes, the array's address on the current device).  *grid_out: teams launched.
+extern "C" int pbgpu_image_launch_static(const pbgpu_launch* L, void* stream, int* grid_out, char* err, size_t errlen) {
+  pb_dev_cfg c;
+  if (pb_configure(&c, err, errlen)) return 1;
+  double* base = nullptr;
+  if (pb_static_setup(&base, err, errlen)) return 1;
+  if (grid_out) *grid_out = 0;
+  if (L->n_sys == 0) return 0;
+  if (L->n_sys < 0 || L->n_sys > PBGPU_STATIC_MAX_SYSTEMS) {
+    snprintf(err, errlen, "pbgpu_solve_device_noalloc: n_sys = %d is beyond the static limit of %d systems per call", L->n_sys,
+             (int)PBGPU_STATIC_MAX_SYSTEMS);
+    return 1;
+  }
+  if (PB_STATIC_TEAMS < 1) {
+    snprintf(err, errlen, "model '%s' needs %lld bytes of scratch per team: more than the static array of %lld bytes holds",
+             PBM_NAME, (long long)PB_SCRATCH_DOUBLES * 8, (long long)PBGPU_STATIC_MAX_BYTES);
+    return 1;
+  }
+  if (L->sched.n_steps > 0) {
+    snprintf(err, errlen, "pbgpu_solve_device_noalloc: experiment schedules are not supported on this entry point");
+    return 1;
+  }
+  int grid = c.blocks_per_sm * c.num_sms;
+  if (grid > L->n_sys) grid = L->n_sys;
+  if (PB_SCRATCH_DOUBLES > 0 && grid > PB_STATIC_TEAMS) grid = PB_STATIC_TEAMS;
+  pbgpu_launch K = *L;
+  K.queue = (unsigned int*)base;
+  K.scratch = base + PB_STATIC_QUEUE_DOUBLES;
+  // the queue must start at zero; the team slots keep the last call's contents, which no team reads before writing
+  cudaError_t e = cudaMemsetAsync(base, 0, sizeof(double) * PB_STATIC_QUEUE_DOUBLES, (cudaStream_t)stream);
+  if (e == cudaSuccess) {
+    pbgpu_solve_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(K);
+    e = cudaGetLastError();
+  }
+  if (e != cudaSuccess) {
+    snprintf(err, errlen, "pbgpu_solve_kernel launch (static scratch): %s", cudaGetErrorString(e));
+    return 1;
+  }
+  if (grid_out) *grid_out = grid;
+  return 0;
+}
+
 extern "C" int pbgpu_image_eval(const pbgpu_eval_launch* E, void* stream, int grid, char* err, size_t errlen) {
   pb_dev_cfg c;
   if (pb_configure(&c, err, errlen)) return 1;

@@ -142,6 +142,8 @@ class _Lib:
             lib.pbgpu_solve.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int, vp, vp, vp, C.c_int, C.POINTER(Result)]
             lib.pbgpu_solve_device.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int, vp, vp, vp, C.c_int,
                                                C.POINTER(Result), vp, C.c_int]
+            lib.pbgpu_solve_device_noalloc.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int, vp, vp, vp, C.c_int,
+                                               C.POINTER(Result), vp, C.c_int]
             lib.pbgpu_model_eval.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_double, C.c_double, vp, vp, C.c_int]
             lib.pbgpu_solve_experiment.argtypes = [vp, C.c_int, C.c_double, vp, vp, vp, C.c_int, C.POINTER(Result), vp, vp]
             lib.pbgpu_observe.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, vp]
