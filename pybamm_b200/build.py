@@ -124,12 +124,15 @@ def build_model(bundle: ModelBundle, force=False, team=None, verbose=False, prof
         # register cap.  Large models: two 256-thread teams per SM (128 registers).  Tiny one-warp models (SPM, 42 states):
         # without a cap the kernel takes 255 registers and only 8 warps fit an SM; 16 warps at 128 registers measured +25 %
         # (24 / 32 warps spill too much).  In between (SPMe, 102 states) shared memory binds first and the cap only costs.
-        min_teams = 2 if gvec else (16 if (team == 32 and bundle.n_states <= 64) else 1)
-    dig = _src_digest(srcs) + f"-t{team}-g{gvec}-m{min_teams}-p{int(profile)}-{'-'.join(defines)}-{'-'.join(extra_flags)}-" + hashlib.sha256(" ".join(NVCC_FLAGS).encode()).hexdigest()[:8]
+        # Which of the two wins depends on the batch size, so such an image carries both kernels (PB_MIN_TEAMS_WIDE) and the
+        # launch picks: uncapped while every system of the batch is resident at once, capped beyond that.
+        min_teams = 2 if gvec else 1
+    wide = 16 if (not gvec and team == 32 and bundle.n_states <= 64 and min_teams == 1) else 0
+    dig = _src_digest(srcs) + f"-t{team}-g{gvec}-m{min_teams}-w{wide}-p{int(profile)}-{'-'.join(defines)}-{'-'.join(extra_flags)}-" + hashlib.sha256(" ".join(NVCC_FLAGS).encode()).hexdigest()[:8]
     stamp = out + ".stamp"
     if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:
         return out
-    cmd = [NVCC] + NVCC_FLAGS + [f"-DPBM_HEADER=\"{header}\"", f"-DPB_TEAM_SIZE={team}", f"-DPB_GLOBAL_VEC={gvec}", f"-DPB_MIN_TEAMS={min_teams}", f"-I{inc}", f"-I{CSRC}",
+    cmd = [NVCC] + NVCC_FLAGS + [f"-DPBM_HEADER=\"{header}\"", f"-DPB_TEAM_SIZE={team}", f"-DPB_GLOBAL_VEC={gvec}", f"-DPB_MIN_TEAMS={min_teams}"] + ([f"-DPB_MIN_TEAMS_WIDE={wide}"] if wide else []) + [f"-I{inc}", f"-I{CSRC}",
                                  kernel_srcs[0], "-o", out] + ([f"-DPB_PROFILE={int(profile)}"] if profile else []) + [f"-D{d}" for d in defines] + list(extra_flags)
     r = subprocess.run(cmd, capture_output=True, text=True)
     log = r.stdout + r.stderr

@@ -21,7 +21,7 @@ static_assert(PB_TEAM_SIZE >= PBM_LU_TEAM_MIN, "team smaller than the widest rec
 #ifndef PB_MIN_TEAMS
 #define PB_MIN_TEAMS 1
 #endif
-extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_solve_kernel(const pbgpu_launch L) {
+static __device__ __forceinline__ void pb_solve_body(const pbgpu_launch& L) {
   extern __shared__ double pb_smem[];
   __shared__ unsigned int next_sys;
   pb_sys S;
@@ -56,6 +56,18 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_s
     pb_align_state(S, 2u);
   }
 }
+
+extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_solve_kernel(const pbgpu_launch L) { pb_solve_body(L); }
+
+// The same integration under a tighter register cap (PB_MIN_TEAMS_WIDE teams per SM), for one-warp models whose uncapped
+// kernel takes 255 registers: more resident teams win once a batch has more systems than the uncapped kernel keeps
+// resident (SPM, 10 000 sets: +25 %), and lose below that (1 000 sets: -9 %, spills without anything to hide them).
+// pb_use_wide() picks per launch.
+#ifdef PB_MIN_TEAMS_WIDE
+extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS_WIDE) pbgpu_solve_kernel_wide(const pbgpu_launch L) {
+  pb_solve_body(L);
+}
+#endif
 
 // Evaluate generated functions / the LU for parity tests of the code generator (one team per system).
 extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_eval_kernel(const pbgpu_eval_launch E) {
@@ -244,7 +256,17 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_o
 #include <mutex>
 struct pb_dev_cfg {
   int ready, blocks_per_sm, num_sms;
+  int blocks_per_sm_wide;   // resident teams per SM of pbgpu_solve_kernel_wide, 0 when the image has none
 };
+
+static inline bool pb_use_wide(const pb_dev_cfg& c, int n_sys) {
+  return c.blocks_per_sm_wide > c.blocks_per_sm && n_sys > c.blocks_per_sm * c.num_sms;
+}
+static inline int pb_grid_for(const pb_dev_cfg& c, int n_sys) {
+  int grid = (pb_use_wide(c, n_sys) ? c.blocks_per_sm_wide : c.blocks_per_sm) * c.num_sms;
+  if (n_sys > 0 && grid > n_sys) grid = n_sys;
+  return grid < 1 ? 1 : grid;
+}
 static pb_dev_cfg g_cfg[64];
 static std::mutex g_cfg_mutex;
 
@@ -308,6 +330,24 @@ static int pb_configure(pb_dev_cfg* out, char* err, size_t errlen) {
   cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   cudaFuncSetAttribute(pbgpu_observe_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   cudaFuncSetAttribute(pbgpu_experiment_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+  c.blocks_per_sm_wide = 0;
+#ifdef PB_MIN_TEAMS_WIDE
+  if (!getenv("PBGPU_NO_WIDE")) {
+    e = cudaFuncSetAttribute(pbgpu_solve_kernel_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(pbgpu_solve_kernel_wide, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    int bw = 0;
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bw, pbgpu_solve_kernel_wide, PB_TEAM_SIZE, PB_SMEM_BYTES);
+    if (e == cudaSuccess && bw > by_carve) bw = by_carve;
+    if (e == cudaSuccess && bw > c.blocks_per_sm && !getenv("PBGPU_TEAMS_PER_SM")) {
+      c.blocks_per_sm_wide = bw;
+      int wkb = (bw * per_team + 1023) / 1024;
+      if (wkb > carve_kb) wkb = carve_kb;
+      int wpct = (wkb * 100 + total_kb - 1) / total_kb;
+      cudaFuncSetAttribute(pbgpu_solve_kernel_wide, cudaFuncAttributePreferredSharedMemoryCarveout, wpct > 100 ? 100 : wpct);
+    }
+    (void)cudaGetLastError();
+  }
+#endif
   c.ready = 1;
   g_cfg[dev] = c;
   *out = c;
@@ -346,10 +386,7 @@ extern "C" int pbgpu_image_describe(pbgpu_model_desc* d) {
 extern "C" int pbgpu_image_plan(int n_sys, int* teams, char* err, size_t errlen) {
   pb_dev_cfg c;
   if (pb_configure(&c, err, errlen)) return 1;
-  int grid = c.blocks_per_sm * c.num_sms;
-  if (n_sys > 0 && grid > n_sys) grid = n_sys;
-  if (grid < 1) grid = 1;
-  *teams = grid;
+  *teams = pb_grid_for(c, n_sys);
   return 0;
 }
 
@@ -358,14 +395,20 @@ extern "C" int pbgpu_image_plan(int n_sys, int* teams, char* err, size_t errlen)
 extern "C" int pbgpu_image_launch(const pbgpu_launch* L, void* stream, int grid, char* err, size_t errlen) {
   pb_dev_cfg c;
   if (pb_configure(&c, err, errlen)) return 1;
-  if (grid < 1 || grid > c.blocks_per_sm * c.num_sms) {
+  const bool wide = pb_use_wide(c, L->n_sys) && L->sched.n_steps == 0;
+  if (grid < 1 || grid > (wide ? c.blocks_per_sm_wide : c.blocks_per_sm) * c.num_sms) {
     snprintf(err, errlen, "pbgpu_image_launch: grid %d was not planned for this device", grid);
     return 1;
   }
-  if (L->sched.n_steps > 0)
+  if (L->sched.n_steps > 0) {
     pbgpu_experiment_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*L);
-  else
+  } else if (wide) {
+#ifdef PB_MIN_TEAMS_WIDE
+    pbgpu_solve_kernel_wide<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*L);
+#endif
+  } else {
     pbgpu_solve_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*L);
+  }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     snprintf(err, errlen, "pbgpu_solve_kernel launch: %s", cudaGetErrorString(e));
@@ -462,6 +505,8 @@ extern "C" int pbgpu_image_launch_static(const pbgpu_launch* L, void* stream, in
 extern "C" int pbgpu_image_eval(const pbgpu_eval_launch* E, void* stream, int grid, char* err, size_t errlen) {
   pb_dev_cfg c;
   if (pb_configure(&c, err, errlen)) return 1;
+  if (grid > c.blocks_per_sm * c.num_sms && grid <= c.blocks_per_sm_wide * c.num_sms)
+    grid = c.blocks_per_sm * c.num_sms;   // planned for the wide solve kernel: this kernel is grid-stride, fewer teams do
   if (grid < 1 || grid > c.blocks_per_sm * c.num_sms) {
     snprintf(err, errlen, "pbgpu_image_eval: grid %d was not planned for this device", grid);
     return 1;
@@ -482,6 +527,8 @@ extern "C" int pbgpu_image_observe(const pbgpu_observe_launch* O, void* stream, 
     snprintf(err, errlen, "the model image has no compiled output variables");
     return 1;
   }
+  if (grid > c.blocks_per_sm * c.num_sms && grid <= c.blocks_per_sm_wide * c.num_sms)
+    grid = c.blocks_per_sm * c.num_sms;   // planned for the wide solve kernel: this kernel is grid-stride, fewer teams do
   if (grid < 1 || grid > c.blocks_per_sm * c.num_sms) {
     snprintf(err, errlen, "pbgpu_image_observe: grid %d was not planned for this device", grid);
     return 1;
