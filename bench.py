@@ -517,7 +517,7 @@ def run_b200_arm(args):
             "all_integrations_succeeded": ok,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "steps": e2e_steps, "kernel_ms_last": e2e_kernel_ms,
-                    "call": "BatchedIDASolver.solve(t_eval, inputs=[{...}]*n, t_interp) -> list[Solution]"},
+                    "call": "BatchedIDASolver.solve(t_eval, inputs=[{...}]*n, t_interp) -> SolutionBatch (list-like; Solution views made on access)"},
             "e2e_full_state": e2e_full,
             "full_state": full_state,
             "gpu_ida_counters_mean": dict(zip(("nsteps", "nrevals", "nlinsetups", "netfails", "nniters", "nncfails", "njevals", "nge"),

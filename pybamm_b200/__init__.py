@@ -6,6 +6,6 @@ scalar DAG (``frontend``, ``ir``, ``bundle``), the re-rolling code generator (``
 stand-alone front end (``solver``) and the pybamm drop-in (``idaklu_solver``).
 """
 from .bundle import ModelBundle, bundle_from_pybamm  # noqa: F401
-from .solver import BatchedIDASolver, Solution, SolverError  # noqa: F401
+from .solver import BatchedIDASolver, Solution, SolutionBatch, SolverError  # noqa: F401
 
 __version__ = "0.1.0"
