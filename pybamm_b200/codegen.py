@@ -55,6 +55,14 @@ _BIN = {
 }
 
 
+# ops that compile to a call of an out-of-line libm copy (pbgpu_team.cuh) and can be issued 2 or 4 at a time (PB_B2 / PB_B4)
+_BATCH_UN = {ir.EXP: "exp", ir.LOG: "log", ir.TANH: "tanh", ir.SINH: "sinh", ir.COSH: "cosh", ir.ASINH: "asinh", ir.SQRT: "sqrt"}
+# Measured and left off (default 1): libdevice's exp / log / tanh branch on their argument ranges, so the copies inside a
+# 2- / 4-wide routine are NOT interleaved by the compiler and the latency stays (SPM events 8 735 against 8 610 cycles) while
+# the code grows: SPM 92.6k (4-wide) / 120.2k (2-wide) against 124.8k sims/s, SPMe 17.2k / 19.1k / 19.7k, DFN 4 892 / 4 831 / 5 134.
+BATCH_W = int(__import__("os").environ.get("PBGPU_BATCH_W", "1"))
+
+
 class _Emitter:
     def __init__(self, prefix):
         self.prefix = prefix
@@ -62,6 +70,7 @@ class _Emitter:
         self.code = []
         self.table_bytes = 0
         self._ntab = 0
+        self.batch = False
 
     def table(self, ctype, values, hint="t", qual="PB_TABLE"):
         name = f"{self.prefix}_{hint}{self._ntab}"
@@ -194,31 +203,72 @@ def _emit_template(em: _Emitter, tp, dest, lines, ind):
             return "cj"
         return refs[r]
 
-    for k, (o, args) in enumerate(tp.body):
+    def batch_name(o, args):
+        """Short name of the out-of-line libm routine an op compiles to, or None."""
+        if o == ir.POW and args[1][0] == "c" and np.all(c_val[:, args[1][1]] == -0.25):
+            return "powm025"
+        if o == ir.POW and args[1][0] == "c" and np.all(c_val[:, args[1][1]] == -1.25):
+            return "powm125"
+        return _BATCH_UN.get(o)
+
+    def expr_of(o, args):
         a = [ref(r) for r in args]
         if o == ir.SELECT:
-            e = f"(({a[0]} != 0.0) ? {a[1]} : {a[2]})"
-        elif o == ir.POW and args[1][0] == "c" and np.all(c_val[:, args[1][1]] == -0.25):
-            e = f"PB_POWM025({a[0]})"     # reg_power's x^-1/4 and its derivative x^-5/4: two square roots instead of pow()
-        elif o == ir.POW and args[1][0] == "c" and np.all(c_val[:, args[1][1]] == -1.25):
-            e = f"PB_POWM125({a[0]})"
-        elif o == ir.DIV:
-            e = f"PB_DIV({a[0]}, {a[1]})"
-        elif o == ir.RECIP:
-            e = f"PB_DIV(1.0, {a[0]})"
-        elif o in _UN:
-            e = _UN[o].format(a=a[0])
-        else:
-            e = _BIN[o].format(a=a[0], b=a[1])
-        lines.append(f"{ind}const double v{k} = {e};")
+            return f"(({a[0]} != 0.0) ? {a[1]} : {a[2]})"
+        if o == ir.POW and args[1][0] == "c" and np.all(c_val[:, args[1][1]] == -0.25):
+            return f"PB_POWM025({a[0]})"     # reg_power's x^-1/4 and its derivative x^-5/4: two square roots instead of pow()
+        if o == ir.POW and args[1][0] == "c" and np.all(c_val[:, args[1][1]] == -1.25):
+            return f"PB_POWM125({a[0]})"
+        if o == ir.DIV:
+            return f"PB_DIV({a[0]}, {a[1]})"
+        if o == ir.RECIP:
+            return f"PB_DIV(1.0, {a[0]})"
+        if o in _UN:
+            return _UN[o].format(a=a[0])
+        return _BIN[o].format(a=a[0], b=a[1])
+
+    if BATCH_W < 2 or not em.batch:
+        for k, (o, args) in enumerate(tp.body):
+            lines.append(f"{ind}const double v{k} = {expr_of(o, args)};")
+    else:
+        # Independent calls of the same libm routine are issued as ONE call of a 2- or 4-wide copy whose chains the compiler
+        # interleaves: a template is a serial FP64 dependency chain per lane (~8 cycles per instruction), and a terminal
+        # voltage or a Butler-Volmer row is fifteen such routines in a row.  Level = number of routine calls on the longest
+        # path to a node; equal level and name means independent.  Order: per level, the batched calls, then the rest.
+        body = tp.body
+        lvl = []
+        for k, (o, args) in enumerate(body):
+            base = max([lvl[r[1]] for r in args if r[0] == "v"], default=0)
+            lvl.append(base + (1 if batch_name(o, args) else 0))
+        for L in range(0, (max(lvl) if lvl else 0) + 1):
+            groups = {}
+            for k, (o, args) in enumerate(body):
+                nm = batch_name(o, args)
+                if nm and lvl[k] == L:
+                    groups.setdefault(nm, []).append(k)
+            for nm, ks in groups.items():
+                while ks:
+                    w = 4 if (len(ks) >= 4 and BATCH_W >= 4) else (2 if len(ks) >= 2 else 1)
+                    chunk, ks = ks[:w], ks[w:]
+                    if w == 1:
+                        o, args = body[chunk[0]]
+                        lines.append(f"{ind}const double v{chunk[0]} = {expr_of(o, args)};")
+                    else:
+                        outs = ", ".join(f"v{k}" for k in chunk)
+                        ins = ", ".join(ref(body[k][1][0]) for k in chunk)
+                        lines.append(f"{ind}PB_B{w}({nm}, {outs}, {ins})")
+            for k, (o, args) in enumerate(body):
+                if lvl[k] == L and not batch_name(o, args):
+                    lines.append(f"{ind}const double v{k} = {expr_of(o, args)};")
     oe = _slot_expr(em, tp.out, "q", "o")
     lines.append(f"{ind}{dest}[{oe}] = {ref(tp.result)};")
     lines.append(f"{ind}PB_PAD")        # empty; the code-size sensitivity experiment defines it as a run of NOPs
 
 
-def emit_program(prog: Program, fname: str, prefix: str):
-    """Return (tables_text, function_text)."""
+def emit_program(prog: Program, fname: str, prefix: str, batch=False):
+    """Return (tables_text, function_text).  batch: issue independent libm calls 2 / 4 at a time (PB_B2 / PB_B4)."""
     em = _Emitter(prefix)
+    em.batch = batch
     L = []
     L.append(f"PB_FN void {fname}(const double* PB_RESTRICT y, const double* PB_RESTRICT p, const double t, const double cj, "
              f"double* PB_RESTRICT out, double* PB_RESTRICT tmp) {{")
@@ -269,6 +319,10 @@ def _emit_u32(lines, name, words):
     lines.append(f"static PB_TABLE PB_ALIGN16 const unsigned int {name}[{max(len(words), 1)}] = {{{body}}};")
 
 
+# Events and output variables of the small models are one long scalar expression (terminal voltage: sixteen tanh / exp / log
+# calls in a row on ONE lane, 8.7k cycles for the SPM against 2.5k for its whole residual; events + output points were half of
+# the SPM / SPMe integration).  Splitting spreads the transcendental terms over lanes in earlier stages.
+SPLIT_EV = bool(int(__import__("os").environ.get("PBGPU_SPLIT_EV", "0")))   # measured: SPM +1 %, SPMe -2 % (templates of a stage run one after the other on a one-warp team); batched calls below do the job
 SPLIT_RES = bool(int(__import__("os").environ.get("PBGPU_SPLIT_RES", "0")))   # measured on the DFN: -6 % (two more stage barriers, 580 more tmp slots)
 
 # shared memory the team may spend on the factor stream (bytes); larger streams stay in global memory / L1
@@ -288,10 +342,10 @@ def model_functions(bundle, sym: slu.SymbolicLU | None, dialect: str):
         progs["jac"] = build_program(g, jroots, "jac", out_index=sym.a_slot, n_out=sym.nnz_lu)
     else:
         progs["jac"] = build_program(g, jroots, "jac")
-    progs["events"] = build_program(g, bundle.events, "events")
+    progs["events"] = build_program(g, bundle.events, "events", split=(dialect == "cuda" and SPLIT_EV))
     progs["ic"] = build_program(g, bundle.ic, "ic")
     vroots = [int(n) for name in bundle.variables for n in bundle.variables[name]]
-    progs["vars"] = build_program(g, vroots, "vars")
+    progs["vars"] = build_program(g, vroots, "vars", split=(dialect == "cuda" and SPLIT_EV))
     return progs
 
 
@@ -513,6 +567,15 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
     out.append("#ifndef PB_DIV")
     out.append("#define PB_DIV(a, b) ((a) / (b))")
     out.append("#endif")
+    # 2- / 4-wide issue of independent libm calls: the device build defines PB_B2 / PB_B4 (pbgpu_team.cuh), any other
+    # consumer of this header evaluates them one by one
+    out.append("#ifndef PB_B2")
+    for nm, mac in (("exp", "PB_EXP"), ("log", "PB_LOG"), ("tanh", "PB_TANH"), ("sinh", "PB_SINH"), ("cosh", "PB_COSH"),
+                    ("asinh", "PB_ASINH"), ("sqrt", "PB_SQRT"), ("powm025", "PB_POWM025"), ("powm125", "PB_POWM125")):
+        out.append(f"#define PB_B1_{nm}(x) {mac}(x)")
+    out.append("#define PB_B2(f, r0, r1, x0, x1) const double r0 = PB_B1_##f(x0), r1 = PB_B1_##f(x1);")
+    out.append("#define PB_B4(f, r0, r1, r2, r3, x0, x1, x2, x3) const double r0 = PB_B1_##f(x0), r1 = PB_B1_##f(x1), r2 = PB_B1_##f(x2), r3 = PB_B1_##f(x3);")
+    out.append("#endif")
     out.append(f'#define PBM_NAME "{bundle.name}"')
     out.append(f"#define PBM_N {bundle.n_states}")
     out.append(f"#define PBM_NDIFF {bundle.n_diff}")
@@ -526,7 +589,7 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
     out.append(f"#define PBM_NVAR {n_var}")
     info = dict(n_tmp=n_tmp, n_var=n_var, table_bytes=0, programs={})
     for key in ("res", "jac", "events", "ic", "vars"):
-        tabs, fn, tb = emit_program(progs[key], f"pbm_{key}", f"pbm_{key}")
+        tabs, fn, tb = emit_program(progs[key], f"pbm_{key}", f"pbm_{key}", batch=(dialect == "cuda"))
         out.append(tabs)
         out.append(fn)
         info["table_bytes"] += tb

@@ -109,6 +109,42 @@ static __device__ __noinline__ double pb_f_div(double a, double b) { return a / 
 #define PB_DIV(a, b) pb_f_div(a, b)
 #endif
 
+// 2- and 4-wide copies of the out-of-line libm routines (PB_B2 / PB_B4 in the generated code): one call evaluates
+// independent arguments, and the compiler interleaves their dependency chains.  A lane's template body is a serial FP64
+// chain at ~8 cycles per instruction; a terminal-voltage expression is sixteen such routines in a row.
+#ifndef PB_NO_BATCH
+#define PB_BATCH_FN(name, expr)                                                                       \
+  static __device__ __noinline__ double2 pb_f2_##name(double x0, double x1) {                         \
+    double2 r;                                                                                        \
+    { const double x = x0; r.x = expr; }                                                              \
+    { const double x = x1; r.y = expr; }                                                              \
+    return r;                                                                                         \
+  }                                                                                                   \
+  static __device__ __noinline__ double4 pb_f4_##name(double x0, double x1, double x2, double x3) {   \
+    double4 r;                                                                                        \
+    { const double x = x0; r.x = expr; }                                                              \
+    { const double x = x1; r.y = expr; }                                                              \
+    { const double x = x2; r.z = expr; }                                                              \
+    { const double x = x3; r.w = expr; }                                                              \
+    return r;                                                                                         \
+  }
+PB_BATCH_FN(exp, exp(x))
+PB_BATCH_FN(log, log(x))
+PB_BATCH_FN(tanh, tanh(x))
+PB_BATCH_FN(sinh, sinh(x))
+PB_BATCH_FN(cosh, cosh(x))
+PB_BATCH_FN(asinh, asinh(x))
+PB_BATCH_FN(sqrt, sqrt(x))
+PB_BATCH_FN(powm025, rsqrt(sqrt(x)))
+PB_BATCH_FN(powm125, rsqrt(sqrt(x)) / x)
+#define PB_B2(f, r0, r1, x0, x1)          \
+  const double2 r0##_b = pb_f2_##f(x0, x1); \
+  const double r0 = r0##_b.x, r1 = r0##_b.y;
+#define PB_B4(f, r0, r1, r2, r3, x0, x1, x2, x3)    \
+  const double4 r0##_b = pb_f4_##f(x0, x1, x2, x3);   \
+  const double r0 = r0##_b.x, r1 = r0##_b.y, r2 = r0##_b.z, r3 = r0##_b.w;
+#endif
+
 struct pb_team_ctx {
   double* red;   // 2 * 32 doubles of shared memory for cross-warp reductions (double buffered)
   int red_phase;
