@@ -30,6 +30,11 @@ def sass_lines(so, kernel):
     return out
 
 
+B_SRC = int(os.environ.get("NCU_LINES_SRC", "10"))     # bucket width in source lines: hand-written sources / generated headers
+B_GEN = int(os.environ.get("NCU_LINES_GEN", "200"))
+TOP = int(os.environ.get("NCU_LINES_TOP", "60"))
+
+
 def main():
     rep, so = sys.argv[1], sys.argv[2]
     kernel = sys.argv[3] if len(sys.argv) > 3 else "pbgpu_solve_kernel"
@@ -43,7 +48,7 @@ def main():
     ex = hdr.index("Instructions Executed")
     agg = defaultdict(lambda: defaultdict(int))
     for (f, ln), r in zip(lines, data):
-        key = (f, ln // 10 * 10) if f.endswith(".cuh") or f.endswith(".cu") else (f, ln // 200 * 200)
+        key = (f, ln // B_SRC * B_SRC) if f.endswith(".cuh") or f.endswith(".cu") else (f, ln // B_GEN * B_GEN)
         a = agg[key]
         a["instr"] += 1
         a["exec"] += int(r[ex] or 0)
@@ -52,7 +57,7 @@ def main():
                 a[hdr[k][6:]] += int(r[k])
     tot = sum(sum(v for k, v in a.items() if k not in ("instr", "exec")) for a in agg.values())
     print("total samples", tot, "instructions", len(data))
-    for key, a in sorted(agg.items(), key=lambda kv: -sum(v for k, v in kv[1].items() if k not in ("instr", "exec")))[:60]:
+    for key, a in sorted(agg.items(), key=lambda kv: -sum(v for k, v in kv[1].items() if k not in ("instr", "exec")))[:TOP]:
         n = sum(v for k, v in a.items() if k not in ("instr", "exec"))
         top = sorted(((k, v) for k, v in a.items() if k not in ("instr", "exec")), key=lambda kv: -kv[1])[:4]
         print(f"{key[0]:18s} {key[1]:6d}  {100 * n / tot:5.1f}%  instr {a['instr']:6d} exec {a['exec']:10d}  " +
