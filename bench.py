@@ -52,6 +52,8 @@ V_BAR, T_BAR = 1e-6, 1e-3          # north_star: terminal voltage within 1e-6 V,
 def metric_name(args):
     if args.model == "dfn":
         return "DFN simulations/sec (10k input sets)"
+    if args.model == "dfn_thermal40":
+        return f"DFN + lumped thermal (40-point meshes) simulations/sec ({args.n_sys} input sets)"
     return f"{args.model.upper()} simulations/sec ({args.n_sys} input sets)"
 
 
@@ -73,10 +75,15 @@ def sample_inputs(bundle, n, rng):
 
 
 def workload_config(args, world, n_total):
+    if args.model == "dfn_thermal40":
+        what = (f"DFN + lumped thermal, Chen2020, x_n = x_s = x_p = r_n = r_p = 40 points (3523 states), constant-current discharge, "
+                f"{n_total} input sets sweeping the current over 0.5C-1.5C")
+    else:
+        what = (f"{args.model.upper()} Chen2020 default mesh, 1C-range constant-current discharge, "
+                f"{n_total} input sets varying {4 if args.model == 'dfn' else 2} parameters"
+                + (", 3.0 V cut-off" if args.model == "spme" else ""))
     return {
-        "workload": f"{args.model.upper()} Chen2020 default mesh, 1C-range constant-current discharge, "
-                    f"{n_total} input sets varying {4 if args.model == 'dfn' else 2} parameters"
-                    + (", 3.0 V cut-off" if args.model == "spme" else ""),
+        "workload": what,
         "model_states": None,  # filled by the caller
         "n_sys_per_gpu": args.n_sys if args.scaling == "weak" else None,
         "n_sys_total": n_total,
@@ -292,7 +299,9 @@ def run_reference_arm(args):
 def parity_block(bundle, p, n_t, flags, v_gpu, t_end_gpu, n_par, cores):
     """GPU vs the checker oracle at 1e-8 (banded LU, partial pivoting) and vs the oracle at 1e-11 ("truth"), per system."""
     o = cpu_oracle(bundle, fast=False)
-    ref, _ = run_cpu(o, p[:n_par], cores, "band")
+    # the pivoting banded LU is the independent checker; with a dense thermal row and column the band is the whole matrix
+    # (3523 x 3523 per system), so the largest model is checked against the static sparse LU in the device's ordering
+    ref, _ = run_cpu(o, p[:n_par], cores, "band" if bundle.n_states <= 2048 else "sparse")
     tru, _ = run_cpu(o, p[:n_par], cores, "sparse", tol=1e-11)
     # 1e-11 is beyond what the first step's error test accepts for a few input sets (the algebraic states move at O(1) V/s
     # right after the current step; IDA's first-order predictor for them costs h <= rtol |y| / |dy/dt|): those fall back to
@@ -509,7 +518,7 @@ def run_b200_arm(args):
         cfg["model_states"] = bundle.n_states
         big = D.smem_bytes > 48 * 1024
         cfg["rows_on_rank_0"] = n
-        cfg["waves_per_gpu"] = round(n / (148 * 2), 2) if big else None
+        cfg["waves_per_gpu"] = round(n / (148 * (1 if bundle.n_states > 2048 else 2)), 2) if big else None
         line = {
             "metric": metric_name(args), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
@@ -705,7 +714,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--model", default="dfn", choices=["spm", "spme", "dfn", "dfn_cccv"])
+    ap.add_argument("--model", default="dfn", choices=["spm", "spme", "dfn", "dfn_cccv", "dfn_thermal40"])
     ap.add_argument("--n-sys", type=int, default=10000, help="input sets per GPU (weak) or in total (strong, in-process)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--inproc-devices", type=int, default=0, help="run the one-process multi-device arm on this many GPUs")
@@ -719,6 +728,8 @@ def main():
         if args.n_sys == 10000:
             args.n_sys = 4000          # BASELINE config 5
         return run_experiment_arm(args)
+    if args.model == "dfn_thermal40":
+        args.no_full_state = True      # the full state of 10 000 x 362 points x 3523 states is 102 GB
     if args.impl == "reference":
         return run_reference_arm(args)
     if args.inproc_devices > 0:

@@ -119,14 +119,15 @@ def build_model(bundle: ModelBundle, force=False, team=None, verbose=False, prof
     if team is None:
         team = default_team(bundle)
     if gvec is None:
-        gvec = 1 if bundle.n_states > 256 else 0   # streamed vectors in global scratch for large models (pbgpu_ida.cuh)
+        # streamed vectors in global scratch for large models; 2: residual vector and solve stream as well (pbgpu_ida.cuh)
+        gvec = 0 if bundle.n_states <= 256 else (1 if bundle.n_states <= 2048 else 2)
     if min_teams is None:
         # register cap.  Large models: two 256-thread teams per SM (128 registers).  Tiny one-warp models (SPM, 42 states):
         # without a cap the kernel takes 255 registers and only 8 warps fit an SM; 16 warps at 128 registers measured +25 %
         # (24 / 32 warps spill too much).  In between (SPMe, 102 states) shared memory binds first and the cap only costs.
         # Which of the two wins depends on the batch size, so such an image carries both kernels (PB_MIN_TEAMS_WIDE) and the
         # launch picks: uncapped while every system of the batch is resident at once, capped beyond that.
-        min_teams = 2 if gvec else 1
+        min_teams = 2 if gvec == 1 else 1
     wide = 16 if (not gvec and team == 32 and bundle.n_states <= 64 and min_teams == 1) else 0
     dig = _src_digest(srcs) + f"-t{team}-g{gvec}-m{min_teams}-w{wide}-p{int(profile)}-{'-'.join(defines)}-{'-'.join(extra_flags)}-" + hashlib.sha256(" ".join(NVCC_FLAGS).encode()).hexdigest()[:8]
     stamp = out + ".stamp"

@@ -530,7 +530,9 @@ def default_team(n_states: int) -> int:
         return 32
     if n_states <= 512:
         return 64
-    return 256      # DFN-sized and larger: 8 warps per team, two teams per SM (128 registers per thread)
+    if n_states <= 2048:
+        return 256  # DFN-sized: 8 warps per team, two teams per SM (128 registers per thread)
+    return 512      # several thousand states: one team per SM
 
 
 def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):

@@ -57,6 +57,16 @@
 #define PBM_DENSE_N 0   /* rows of the dense top block of the elimination tree (symbolic_lu._dense_top) */
 #endif
 #define PB_GOFF_WD (PB_GOFF_TMPJ + PBM_NTMP_JAC)   /* W = (L_TT U_TT)^-1, row-major */
+// PB_GLOBAL_VEC == 2 (models of several thousand states: the DFN with 40-point meshes and a lumped thermal state, 3 523
+// states, 140 KB of L+U values): one 512-thread team per SM, and shared memory keeps only what the triangular solves and
+// the stencil reads touch -- y, w, the L+U values.  The residual vector, the correction, the error weights and the solve
+// stream join the streamed vectors in L2.
+#if PB_GLOBAL_VEC == 2
+#define PB_GOFF_DELTA (PB_GOFF_WD + PBM_DENSE_N * PBM_DENSE_N)
+#define PB_GVEC_DOUBLES (PB_GOFF_DELTA + PBM_N)
+#define PB_OFF_YY 0
+#define PB_SCRATCH_DOUBLES PB_GVEC_DOUBLES
+#else
 #define PB_GVEC_DOUBLES (PB_GOFF_WD + PBM_DENSE_N * PBM_DENSE_N)
 #if PB_GLOBAL_VEC
 #define PB_OFF_DELTA 0
@@ -66,6 +76,7 @@
 #define PB_SCRATCH_DOUBLES 0
 #endif
 #define PB_OFF_YY (PB_OFF_DELTA + PBM_N)
+#endif
 // The temporaries of the generated functions (residual, events, output variables) ALIAS the solve's w scratch: no
 // generated function runs while w is live (w holds a right-hand side only between the Newton loop's rhs pass and its
 // update pass, and inside pb_lu_solve / pb_lu_factor).  tmp[0, PB_TMP_EXTRA) is private, the rest is w[0, N); w[N], the
@@ -82,7 +93,11 @@
 #define PB_OFF_NPG (PB_OFF_STATS + 8)                          /* NoProgressGuard window: 32 step sizes + verdict */
 #define PB_NPG_MAX 32
 #define PB_OFF_SLV (PB_OFF_NPG + PB_NPG_MAX + 2)               /* packed solve stream (u32 words) */
+#if PB_GLOBAL_VEC == 2
+#define PB_OFF_FAC PB_OFF_SLV                                  /* the solve stream is read from the global table */
+#else
 #define PB_OFF_FAC (PB_OFF_SLV + (PBM_SLV_ALLOC + 1) / 2)      /* packed factor stream when it fits (PBM_FAC_SMEM) */
+#endif
 #if PBM_FAC_SMEM
 #define PB_OFF_END0 (PB_OFF_FAC + (PBM_FAC_WORDS + 1) / 2)
 #else
@@ -91,7 +106,7 @@
 // Large models: the correction ee and the error weights ewt, read by every Newton iteration and every norm, stay in
 // shared memory as well; the history, the predictors and the Jacobian temporaries are the ones streamed from L2.
 // (DFN: 113.9 KB per team; two teams and their 1 KB reservations still fit the 228 KB of an SM.)
-#if PB_GLOBAL_VEC
+#if PB_GLOBAL_VEC == 1
 #define PB_OFF_EE PB_OFF_END0
 #define PB_OFF_EWT_S (PB_OFF_EE + PBM_N)
 #define PB_SMEM_DOUBLES (PB_OFF_EWT_S + PBM_N)
@@ -135,7 +150,7 @@ struct pb_sys {
 };
 
 #define S_PHI(S, j) ((S).gv + PB_GOFF_PHI + (j) * PBM_N)
-#if PB_GLOBAL_VEC
+#if PB_GLOBAL_VEC == 1
 #define S_EE(S) ((S).sm + PB_OFF_EE)
 #define S_EWT(S) ((S).sm + PB_OFF_EWT_S)
 #else
@@ -146,7 +161,11 @@ struct pb_sys {
 #define S_YPPRED(S) ((S).gv + PB_GOFF_YPPRED)
 #define S_TMPJ(S) ((S).gv + PB_GOFF_TMPJ)
 #define S_WD(S) ((S).gv + PB_GOFF_WD)
+#if PB_GLOBAL_VEC == 2
+#define S_DELTA(S) ((S).gv + PB_GOFF_DELTA)
+#else
 #define S_DELTA(S) ((S).sm + PB_OFF_DELTA)
+#endif
 #define S_YY(S) ((S).sm + PB_OFF_YY)
 #define S_W(S) ((S).sm + PB_OFF_W)
 #define S_TMP(S) ((S).sm + PB_OFF_TMP)
@@ -2471,9 +2490,13 @@ static PB_DEV void pb_sys_tables(pb_sys& S) {
     S_LU(S)[PBM_NNZ_LU + 1] = 1.0;
     S_W(S)[PBM_N] = 0.0;
   }
+#if PB_GLOBAL_VEC == 2
+  S.slv = pbm_slv_tab;
+#else
   unsigned int* slv = (unsigned int*)(S.sm + PB_OFF_SLV);
   for (int i = PB_TID; i < PBM_SLV_ALLOC; i += PB_TEAM) slv[i] = PB_LD(pbm_slv_tab[i]);
   S.slv = slv;
+#endif
 #if PBM_FAC_SMEM
   unsigned int* fac = (unsigned int*)(S.sm + PB_OFF_FAC);
   for (int i = PB_TID; i < PBM_FAC_WORDS; i += PB_TEAM) fac[i] = PB_LD(pbm_fac_tab[i]);

@@ -218,8 +218,19 @@ def _peel_then_nd(sym: sp.csr_matrix, leaf=4):
     core = np.nonzero(alive)[0]
     if len(core):
         sub = sym[core][:, core].tocsr()
-        q = _nested_dissection(sub, leaf=leaf)
-        order.extend(core[q].tolist())
+        # hubs: vertices adjacent to a large part of the core (the lumped temperature of a thermal model couples to every
+        # through-cell variable).  Inside the dissection a hub makes every breadth-first level structure two levels deep and
+        # the separators useless; taken out and eliminated last it is the border of a bordered system.
+        deg = np.diff(sub.indptr)
+        hub = (deg > max(32, 0.25 * len(core))) if len(core) > 64 else np.zeros(len(core), bool)
+        if hub.any():
+            rest = np.nonzero(~hub)[0]
+            q = _nested_dissection(sub[rest][:, rest].tocsr(), leaf=leaf)
+            order.extend(core[rest[q]].tolist())
+            order.extend(core[np.nonzero(hub)[0]].tolist())
+        else:
+            q = _nested_dissection(sub, leaf=leaf)
+            order.extend(core[q].tolist())
     return np.asarray(order, dtype=np.int64)
 
 
@@ -299,7 +310,7 @@ def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01, tea
     and to validate it."""
     rows = np.asarray(rows, np.int64)
     cols = np.asarray(cols, np.int64)
-    candidates = []
+    candidates, late = [], []
     names = ["peel_nd", "nd", "COLAMD", "MMD_AT_PLUS_A"] if ordering == "auto" else [ordering]
     A0 = sp.csc_matrix((np.asarray(samples[0], float), (rows, cols)), shape=(n, n))
     pat = sp.csr_matrix((np.ones(len(rows)), (rows, cols)), shape=(n, n))
@@ -312,6 +323,23 @@ def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01, tea
                 # SuperLU: Pr A Pc = L U with perm_r[i] = new position of row i
                 pr = np.empty(n, np.int64)
                 pr[lu0.perm_r] = np.arange(n)
+                # The pivots SuperLU chose belong to ITS elimination sequence; after the symmetric re-ordering below an entry
+                # it matched may sit on the diagonal before any fill reaches it, and such an entry can be a structural
+                # non-zero that is numerically zero.  When that can happen the natural diagonal (J - cj M of a semi-explicit
+                # DAE has a full one) is a second candidate -- the first one for models so large that every candidate
+                # costs a minute of symbolic work.
+                dg = [np.abs(sp.csc_matrix((np.asarray(v, float), (rows, cols)), shape=(n, n))[pr, :].diagonal()) for v in samples]
+                variants = [pr]
+                if any(float(d.min()) == 0.0 for d in dg):
+                    variants = [np.arange(n), pr] if n > 2048 else [pr, np.arange(n)]
+                for vi, pr in enumerate(variants[1:]):
+                    Bp = pat[pr, :]
+                    sym = (Bp + Bp.T).tocsr()
+                    sym.setdiag(0)
+                    sym.eliminate_zeros()
+                    q = _nested_dissection(sym) if name == "nd" else _peel_then_nd(sym)
+                    late.append((name + "_alt", pr[q], q))
+                pr = variants[0]
                 Bp = pat[pr, :]
                 sym = (Bp + Bp.T).tocsr()
                 sym.setdiag(0)
@@ -331,32 +359,47 @@ def analyse(n, rows, cols, samples, ordering="auto", diag_pivot_thresh=0.01, tea
         except Exception as e:  # pragma: no cover
             print(f"[symbolic_lu] ordering {name} failed: {e}")
     best = None
-    for name, perm_r, perm_c in candidates:
-        try:
-            s = _build(n, rows, cols, perm_r, perm_c, name, team=team)
-        except AssertionError as e:      # an ordering the cluster schedule cannot express (unsymmetric fill): next candidate
-            print(f"[symbolic_lu] ordering {name} rejected: {e}")
-            continue
-        # cost proxy (cycles per factorisation interval): ~30 triangular solves per factorisation (measured on the
-        # battery models); the L+U values and the solve stream must stay in shared memory (8 + ~6 bytes per entry)
-        score = 30.0 * s.est_cycles_solve + s.est_cycles_factor + 30.0 * s.nnz_lu
-        ok = all(_validate(s, rows, cols, np.asarray(v, float)) < 1e-6 for v in samples)
-        if not ok:
-            continue
-        if best is None or score < best[0]:
-            best = (score, s)
+    # the alternatives (natural diagonal) are only looked at when no regular candidate is valid: the orders of the models
+    # that never needed them stay what they were
+    for pool in (candidates, late):
+        if best is not None:
+            break
+        for name, perm_r, perm_c in pool:
+            try:
+                s = _build(n, rows, cols, perm_r, perm_c, name, team=team)
+            except AssertionError:           # unsymmetric fill the cluster schedule cannot express: pad the pattern and retry
+                try:
+                    s = _build(n, rows, cols, perm_r, perm_c, name, team=team, symmetrise=True)
+                except AssertionError as e:  # still not expressible: next candidate
+                    print(f"[symbolic_lu] ordering {name} rejected: {e}")
+                    continue
+            # cost proxy (cycles per factorisation interval): ~30 triangular solves per factorisation (measured on the
+            # battery models); the L+U values and the solve stream must stay in shared memory (8 + ~6 bytes per entry)
+            score = 30.0 * s.est_cycles_solve + s.est_cycles_factor + 30.0 * s.nnz_lu
+            ok = all(_validate(s, rows, cols, np.asarray(v, float)) < 1e-6 for v in samples)
+            if not ok:
+                continue
+            if best is None or score < best[0]:
+                best = (score, s)
+            if n > 2048:      # every candidate costs a minute of symbolic work at this size: the first valid one is taken
+                break
     if best is None:
         raise RuntimeError("no static pivot order passed validation on the sample matrices")
     return best[1]
 
 
-def _build(n, rows, cols, perm_r, perm_c, name, team=128) -> SymbolicLU:
+def _build(n, rows, cols, perm_r, perm_c, name, team=128, symmetrise=False) -> SymbolicLU:
     inv_r = np.empty(n, np.int64)
     inv_r[perm_r] = np.arange(n)
     inv_c = np.empty(n, np.int64)
     inv_c[perm_c] = np.arange(n)
     bi, bj = inv_r[rows], inv_c[cols]
     B = sp.csr_matrix((np.ones(len(rows)), (bi, bj)), shape=(n, n))
+    if symmetrise:
+        # structural zeros that make the permuted pattern symmetric: the cluster schedule below relies on the elimination
+        # tree of a structurally symmetric matrix (every U entry of a row points at an ancestor); a lumped thermal state
+        # that reads more variables than it feeds breaks that by a few dozen entries
+        B = ((B + B.T) > 0).astype(float).tocsr()
     Lrows, Urows = _symbolic_fill(B)
     # slots: row-major over (L row, U row)
     # the diagonal of row i sits in slot i (the backward solve reads 1/u_ii as lu[row] without a table look-up)

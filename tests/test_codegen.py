@@ -27,7 +27,7 @@ def _close(got, ref, rtol=RTOL):
     np.testing.assert_allclose(got, ref, rtol=0, atol=rtol * scale)
 
 
-@pytest.mark.parametrize("name", util.BATTERY)
+@pytest.mark.parametrize("name", util.BATTERY + util.LARGE)
 def test_graph_matches_reference_evaluation(name):
     z, b = _golden(name), util.bundle(name)
     assert list(z["input_names"]) == b.input_names
@@ -42,7 +42,7 @@ def test_graph_matches_reference_evaluation(name):
         _close(b.graph.evaluate(b.jac_nodes, t, y, p), z["jac_vals"][k], 1e-11)
 
 
-@pytest.mark.parametrize("name", util.BATTERY)
+@pytest.mark.parametrize("name", util.BATTERY + util.LARGE)
 def test_c_dialect_matches_reference_evaluation(name):
     z, o = _golden(name), util.oracle(name)
     b = util.bundle(name)

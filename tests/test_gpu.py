@@ -33,7 +33,7 @@ def _close(got, ref, rtol=1e-12):
 
 
 # ---- generated device functions vs the reference's own evaluation ---------------------------------------
-@pytest.mark.parametrize("name", util.BATTERY)
+@pytest.mark.parametrize("name", util.BATTERY + util.LARGE)
 def test_device_functions_match_reference_evaluation(name):
     z = np.load(f"{util.GOLDEN}/{name}_eval.npz")
     b, s = util.bundle(name), gpu(name)
@@ -51,7 +51,7 @@ def test_device_functions_match_reference_evaluation(name):
         np.testing.assert_array_equal(allres[k], s.eval("res", z["y"][k], z["p"][k], 100.0)[0])
 
 
-@pytest.mark.parametrize("name", util.BATTERY)
+@pytest.mark.parametrize("name", util.BATTERY + util.LARGE)
 def test_device_sparse_lu_matches_scipy(name):
     z = np.load(f"{util.GOLDEN}/{name}_eval.npz")
     b, s = util.bundle(name), gpu(name)
@@ -415,6 +415,34 @@ def test_parity_on_the_baseline_batches(name, n):
         assert par["max_abs_dV_gpu_vs_oracle_1e-8"] <= util.V_TOL and par["max_abs_dV_gpu_vs_truth_1e-11"] <= util.V_TOL
     # the GPU's error against the truth is of the size of the reference algorithm's own (same tolerances, same method)
     assert par["median_abs_dV_gpu_vs_truth"] <= 3.0 * par["median_abs_dV_oracle_vs_truth"] + 1e-9
+
+
+def test_config4_thermal_dfn_batch_against_the_oracle():
+    """BASELINE config 4: DFN + lumped thermal on 40-point meshes (3 523 states; one 512-thread team per SM, L+U values in shared
+    memory, everything streamed in L2), a C-rate sweep of two waves of teams.  Same bars as configs 1-3.  The checker here is the
+    oracle's static sparse LU (the pivoting banded LU would be a dense 3523 x 3523 factorisation per system)."""
+    import os
+
+    import bench
+
+    b = util.bundle("dfn_thermal40")
+    n = 296
+    p = bench.sample_inputs(b, n, np.random.default_rng(20264))
+    r = gpu("dfn_thermal40").solve_arrays(util.T_EVAL, p, t_interp=util.T_INTERP)
+    nt = np.asarray(r["n_t"])
+    assert set(np.unique(r["flag"]).tolist()) <= {1, 2}
+    t_end = np.array([r["t"][i, int(nt[i]) - 1] for i in range(n)])
+    par, _ = bench.parity_block(b, p, nt, np.asarray(r["flag"]), np.asarray(r["y"])[:, :, 0], t_end, n, os.cpu_count() or 1)
+    print({k: v for k, v in par.items() if k != "bars"})
+    assert par["same_termination"]
+    assert par["max_abs_dt_end_gpu_vs_oracle"] <= util.T_EVENT_TOL and par["max_abs_dt_end_gpu_vs_truth"] <= util.T_EVENT_TOL
+    assert par["systems_failing_the_bar"] == 0, par
+    # a larger current heats the cell more: the final temperature state grows with the current among full discharges
+    cur = p[:, 0]
+    done = np.nonzero(r["flag"] == 2)[0]
+    temp = r["y_term"][done, b.n_diff - 1]
+    order = np.argsort(cur[done])
+    assert np.all(np.diff(temp[order]) > 0)
 
 
 @pytest.mark.parametrize("name", ["spm", "spme"])

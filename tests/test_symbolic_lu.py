@@ -166,3 +166,47 @@ def test_solve_form_overwrites_only_coupling_entries():
             for i in c:
                 j = s.Urows[i][1]
                 assert np.isclose(lu[s.slot_of[(i, j)]], U[i, j], rtol=1e-9, atol=1e-300)
+
+
+def test_hub_vertex_is_eliminated_last_and_the_streams_still_match_scipy():
+    """A lumped state coupled to every core unknown, reading more of them than it feeds (the temperature of a thermal DFN):
+    taken out of the dissection and eliminated last, static pivots on the natural diagonal."""
+    rng = np.random.default_rng(77)
+    n0, rows, cols, vals = chain_core_matrix(30, 10, 4, rng)
+    hub = n0
+    core = np.arange(30 * 10, n0)
+    feeds = core[::2]                                  # column of the hub: half of the core
+    rows = np.concatenate([rows, np.full(len(core), hub), feeds, [hub]])
+    cols = np.concatenate([cols, core, np.full(len(feeds), hub), [hub]])
+    vals = np.concatenate([vals, 0.05 * rng.standard_normal(len(core)), 0.05 * rng.standard_normal(len(feeds)), [5.0]])
+    n = n0 + 1
+    samples = [vals, vals * (1 + 0.1 * rng.standard_normal(len(vals)))]
+    s = slu.analyse(n, rows, cols, samples, ordering="peel_nd", team=256)
+    assert int(s.perm_c[-1]) == hub and int(s.perm_r[-1]) == hub
+    for v in samples:
+        A = sp.csc_matrix((v, (rows, cols)), shape=(n, n))
+        lu = slu.stream_factor(s, v)
+        b = rng.standard_normal(n)
+        x = slu.stream_solve(s, lu, b)
+        xr = spla.spsolve(A, b)
+        assert np.max(np.abs(x - xr)) <= 1e-10 * max(1.0, np.max(np.abs(xr)))
+
+
+def test_config4_thermal_dfn_fits_the_16_bit_streams():
+    """BASELINE config 4 (3 523 states, 13 031 structural entries): peel + dissection with the temperature as border
+    gives 17.5k L+U slots (SuperLU's MMD: 16.9k), inside the 16-bit slot / row indices of the packed streams."""
+    b = util.bundle("dfn_thermal40")
+    samples = codegen.sample_matrices(b)
+    s = slu.analyse(b.n_states, b.jac_rows, b.jac_cols, samples, team=512)
+    assert s.nnz_lu < 20000 and s.n_solve_records <= 24
+    t_row = b.n_diff - 1                                # the lumped temperature is the last differential state
+    assert int(s.perm_c[-1]) == t_row
+    rng = np.random.default_rng(5)
+    for v in (samples[0], samples[4]):
+        v = np.asarray(v, float)
+        A = sp.csc_matrix((v, (b.jac_rows, b.jac_cols)), shape=(b.n_states,) * 2)
+        lu = slu.stream_factor(s, v)
+        rhs = rng.standard_normal(b.n_states)
+        x = slu.stream_solve(s, lu, rhs)
+        xr = spla.spsolve(A, rhs)
+        assert np.max(np.abs(x - xr)) <= 1e-8 * max(1.0, np.max(np.abs(xr)))

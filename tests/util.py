@@ -11,6 +11,7 @@ from pybamm_b200 import build as pbuild
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 BATTERY = ("spm", "spme", "dfn")
+LARGE = ("dfn_thermal40",)     # BASELINE config 4: DFN + lumped thermal, 40-point meshes, 3 523 states
 T_EVAL = [0.0, 3700.0]
 T_INTERP = np.linspace(0.0, 3600.0, 361)
 
