@@ -461,6 +461,15 @@ def emit_solve_program(sym: slu.SymbolicLU) -> str:
             return f"pb_chain_rec<{r['mode'] & 1}>(st + {boff}, {nt}, lu, w);", boff + 3 * nt
         return f"pb_seq_rec<{r['mode'] & 1}>(st + {boff}, {nt}, lu, w);", boff + nt * (r["desc"][v] >> 16)
 
+    def span(k):        # word range of record k in the stream
+        q = recs[k]
+        return q["offset"], slu.SEQ_HDR + len(q["desc"]) + len(q["body"])
+
+    def prefetch(k):    # models whose solve stream stays in global memory: the next record's words are on their way to L1
+        if k < len(recs):
+            out.append("PB_SLV_PREFETCH({}, {})".format(*span(k)))
+
+    prefetch(0)
     i = 0
     while i < len(recs):
         r = recs[i]
@@ -470,6 +479,8 @@ def emit_solve_program(sym: slu.SymbolicLU) -> str:
                 j += 1
             run = recs[i:j + 1]
             assert all(q.get("narrow") and q["nblocks"] == 1 and q["first_warp"] == 0 for q in run)
+            for k in range(i + 1, j + 2):
+                prefetch(k)
             out.append("if (PB_WARP == 0) {")
             k = 0
             while k < len(run):
@@ -496,6 +507,7 @@ def emit_solve_program(sym: slu.SymbolicLU) -> str:
             out.append("PB_REC_MARK")
             i = j + 1
             continue
+        prefetch(i + 1)
         boff = r["offset"] + slu.SEQ_HDR + r["nblocks"]
         if r["kind"] == 3:              # dense top block: all threads, barriers inside
             out += [f"PB_DENSE_REC({boff})", "PB_REC_MARK"]

@@ -950,7 +950,7 @@ def build_seq_solve_stream(s: SymbolicLU, team=128):
         # lanes per row: as many as the warps can hold (with slack for packing whole clusters into warps)
         maxml_all = max(len(t[1]) for t in rows_ops)
         Gw = 1
-        while split_rows and 2 * Gw * len(rows_ops) <= 32 * nw and Gw < min(maxml_all, 8):
+        while split_rows and 2 * Gw * len(rows_ops) <= 32 * nw and Gw < min(maxml_all, 32):
             Gw *= 2
         while (PAR_WIDE_GROUPS and 2 * Gw * len(rows_ops) <= 24 * nw and 2 * Gw * len(units[0]) <= 32 and Gw < maxml_all
                and nw > 1):
