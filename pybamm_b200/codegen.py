@@ -265,11 +265,30 @@ def _emit_template(em: _Emitter, tp, dest, lines, ind):
     lines.append(f"{ind}PB_PAD")        # empty; the code-size sensitivity experiment defines it as a run of NOPs
 
 
-def emit_program(prog: Program, fname: str, prefix: str, batch=False):
-    """Return (tables_text, function_text).  batch: issue independent libm calls 2 / 4 at a time (PB_B2 / PB_B4)."""
+def emit_program(prog: Program, fname: str, prefix: str, batch=False, multi=False):
+    """Return (tables_text, function_text).  batch: issue independent libm calls 2 / 4 at a time (PB_B2 / PB_B4).
+    multi: the function evaluates ``npts`` points at once, (instance, point) pairs spread over the lanes -- for the output
+    variables of one-warp models, whose long scalar expressions leave 31 lanes idle (pbgpu_ida.cuh, PB_VARS_BATCH):
+    point k reads y from yb + k * PBM_N, its time from tb[k], writes outb + k * n_out and uses tmpb + k * n_tmp."""
     em = _Emitter(prefix)
     em.batch = batch
     L = []
+    if multi:
+        L.append(f"PB_FN void {fname}(const double* PB_RESTRICT yb, const double* PB_RESTRICT p, const double* PB_RESTRICT tb, "
+                 f"const int npts, double* PB_RESTRICT outb, double* PB_RESTRICT tmpb) {{")
+        L.append("  const double cj = 0.0; (void)cj; (void)p;")
+        for si, st in enumerate(prog.stages):
+            if si > 0:
+                L.append("  PB_SYNC();")
+            for t, dest in [(t, "tmp") for t in st.to_tmp] + [(t, "out") for t in st.to_out]:
+                L.append(f"  for (int idx = PB_TID; idx < {t.n_inst} * npts; idx += PB_TEAM) {{")
+                L.append(f"    const int q = idx % {t.n_inst}, pt = idx / {t.n_inst}; (void)q;")
+                L.append(f"    const double* PB_RESTRICT y = yb + pt * PBM_N; double* PB_RESTRICT tmp = tmpb + pt * {max(prog.n_tmp, 1)}; "
+                         f"double* PB_RESTRICT out = outb + pt * {prog.n_out}; const double t = tb[pt]; (void)y; (void)tmp; (void)out; (void)t;")
+                _emit_template(em, t, dest, L, "    ")
+                L.append("  }")
+        L.append("}")
+        return "\n".join(em.tables), "\n".join(L), em.table_bytes
     L.append(f"PB_FN void {fname}(const double* PB_RESTRICT y, const double* PB_RESTRICT p, const double t, const double cj, "
              f"double* PB_RESTRICT out, double* PB_RESTRICT tmp) {{")
     L.append("  (void)y; (void)p; (void)t; (void)cj; (void)out; (void)tmp;")
@@ -612,6 +631,12 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
                                      n_tmp=pr.n_tmp,
                                      templates=sum(len(s.to_tmp) + len(s.to_out) for s in pr.stages))
         out.append(f"#define PBM_FLOPS_{key.upper()} {pr.flops}")
+    if dialect == "cuda" and n_var > 0 and default_team(bundle.n_states) == 32:
+        tabs, fn, tb = emit_program(progs["vars"], "pbm_vars_multi", "pbm_varsm", multi=True)
+        out.append(f"#define PBM_VARS_MULTI 1\n#define PBM_NTMP_VARS {max(progs['vars'].n_tmp, 1)}")
+        out.append(tabs)
+        out.append(fn)
+        info["table_bytes"] += tb
     if dialect == "cuda":
         out.append(f"#define PBM_NNZ_LU {sym.nnz_lu}")
         lines = []

@@ -29,6 +29,9 @@ static __device__ __forceinline__ void pb_solve_body(const pbgpu_launch& L) {
   pb_sys_init(S, pb_smem, L.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES, L);
 #else
   pb_sys_init(S, pb_smem, pb_smem, L);
+#if PB_VARS_BATCH > 1
+  S.vb = L.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES;
+#endif
 #endif
 #if PB_ALIGN_TEAMS
   {   // the first two teams to arrive on an SM share its mailbox (persistent kernel: a team never leaves its SM)
@@ -225,6 +228,9 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_e
   pb_sys_init(S, pb_smem, L.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES, L);
 #else
   pb_sys_init(S, pb_smem, pb_smem, L);
+#if PB_VARS_BATCH > 1
+  S.vb = L.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES;
+#endif
 #endif
   for (;;) {
     if (threadIdx.x == 0) next_sys = atomicAdd(L.queue, 1u);
