@@ -203,10 +203,15 @@ struct pb_sys {
 #define S_STATS(S) ((S).sm + PB_OFF_STATS)
 #define S_NPG(S) ((S).sm + PB_OFF_NPG)
 
+#ifdef PB_PAIR_DEBUG
+#define PB_STAT_KEEP(k) ((k) < 4)   /* slots 4..7 carry the join statistics of tools/gpu_pair_debug.py */
+#else
+#define PB_STAT_KEEP(k) 1
+#endif
 #ifndef PB_PROFILE
 #define PB_STAT(S, k)                        \
   do {                                       \
-    if (PB_TID == 0) S_STATS(S)[k] += 1.0;   \
+    if (PB_TID == 0 && PB_STAT_KEEP(k)) S_STATS(S)[k] += 1.0;   \
   } while (0)
 #define PB_T0(v) ((void)0)
 #define PB_T1(S, v, k) ((void)0)
@@ -1241,6 +1246,65 @@ static PB_DEV void pb_align(pb_sys& S) {
 #define pb_align(S) ((void)0)
 #endif
 
+// ---- two teams of one CTA in lock-step through the large functions (PB_PAIR) -------------------------------------------
+// The integration is bound by instruction fetch: the generated residual alone is 45 KB of code against a 32 KB instruction
+// cache, and a team runs it 1.7x slower beside a neighbour that executes other code.  Two separate CTAs cannot be held
+// close enough (tried in round 1: a mailbox in L2, iteration granularity, +-1 %).  Inside one CTA they can: a team about
+// to enter function f posts a ticket; if the other team arrives for the same f within `limit` cycles it claims the
+// ticket and both run f on the CTA-wide barrier, stage by stage side by side; otherwise the first team withdraws and
+// runs alone on its own barrier.  Both functions execute a fixed sequence of barriers, whatever the data.
+// MEASURED, and therefore off (build with -DPB_PAIR=1 to repeat; tools/gpu_pair_debug.py prints the join statistics): DFN,
+// 2 960 systems, 4 669 sims/s without against 4 119 with.  With a 6 000-cycle wait 168 of a system's 1 030 residuals run
+// jointly (386 with 20 000 cycles, 53 with 300), and a joint residual takes 23.1k cycles against 26.1k alone: stage-level
+// lock-step of two DIFFERENT systems buys 10 %, not the 1.7x of two identical ones, and the waiting costs more than that.
+#define PB_FN_RES 1u
+#define PB_FN_SOLVE 2u
+#define PB_PAIR_JOINED 0x100u
+#ifndef PB_PAIR_LIMIT_RES
+#define PB_PAIR_LIMIT_RES 6000
+#endif
+#ifndef PB_PAIR_LIMIT_SOLVE
+#define PB_PAIR_LIMIT_SOLVE 1500
+#endif
+#if PB_PAIR && !defined(PB_EMU)
+static PB_DEV int pb_pair_enter(const unsigned int f, const long long limit) {
+  volatile unsigned int* ctl = PB_PAIR_CTL;
+  if (blockDim.x <= PB_TEAM_SIZE) return 0;        // kernels launched with one team per CTA
+  if (PB_TID == 0) {
+    unsigned int joined = 0u;
+    const unsigned int old = atomicCAS((unsigned int*)&ctl[0], 0u, f);
+    if (old == 0u) {                               // first to arrive: wait for the other team, for a bounded time
+      const long long t0 = clock64();
+      for (;;) {
+        if (ctl[0] == (f | PB_PAIR_JOINED)) {
+          joined = 1u;
+          break;
+        }
+        if (clock64() - t0 > limit) {
+          if (atomicCAS((unsigned int*)&ctl[0], f, 0u) != f) joined = 1u;   // claimed while giving up
+          break;
+        }
+      }
+      if (joined) ctl[0] = 0u;                     // the claimer is held at the first joint barrier until we arrive
+    } else if (old == f) {                         // the other team is waiting for the same function
+      if (atomicCAS((unsigned int*)&ctl[0], f, f | PB_PAIR_JOINED) == f) joined = 1u;
+    }
+    ctl[2 + PB_TEAM_ID] = joined;
+  }
+  pb_bar_solo();
+  return (int)ctl[2 + PB_TEAM_ID];
+}
+static PB_DEV void pb_pair_leave(const int joined) {
+  if (joined) {      // every thread of the team is past the last joint barrier
+    if (PB_TID == 0) PB_PAIR_CTL[2 + PB_TEAM_ID] = 0u;
+    pb_bar_solo();
+  }
+}
+#else
+#define pb_pair_enter(f, limit) 0
+#define pb_pair_leave(j) ((void)0)
+#endif
+
 static PB_DEV int pb_nls_impl(pb_sys& S) {
   int callLSetup = 0;
   if (S.nst == 0) {
@@ -1316,9 +1380,20 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
     {
       pb_align(S);
       PB_T0(tr_);
+      const int jn_ = pb_pair_enter(PB_FN_RES, PB_PAIR_LIMIT_RES);
+#ifdef PB_PAIR_DEBUG
+      const long long dbg0_ = clock64();
+#endif
       pbm_res(yy, S_P(S), S.tn, 0.0, delta, S_TMP(S));
       PB_STAT(S, PB_ST_NRE);
       PB_SYNC();
+#ifdef PB_PAIR_DEBUG
+      if (PB_TID == 0) {   // debug build: stats slots 4..7 = cycles of solo / joint residuals and their counts
+        S_STATS(S)[jn_ ? 5 : 4] += (double)(clock64() - dbg0_);
+        S_STATS(S)[jn_ ? 7 : 6] += 1.0;
+      }
+#endif
+      pb_pair_leave(jn_);
       PB_T1(S, tr_, 0);
     }
     int fail = 0;
@@ -1353,7 +1428,9 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
         PB_SYNC();
         {
           PB_T0(ts_);
+          const int jn_ = pb_pair_enter(PB_FN_SOLVE, PB_PAIR_LIMIT_SOLVE);
           pb_lu_solve_in_w(S);
+          pb_pair_leave(jn_);
           PB_T1(S, ts_, 1);
         }
         const double scale = (S.scalesol && S.cjratio != 1.0) ? 2.0 / (1.0 + S.cjratio) : 1.0;
@@ -1419,9 +1496,20 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
         {
           pb_align(S);
           PB_T0(tr_);
+          const int jn_ = pb_pair_enter(PB_FN_RES, PB_PAIR_LIMIT_RES);
+#ifdef PB_PAIR_DEBUG
+          const long long dbg0_ = clock64();
+#endif
           pbm_res(yy, S_P(S), S.tn, 0.0, delta, S_TMP(S));
           PB_STAT(S, PB_ST_NRE);
           PB_SYNC();
+#ifdef PB_PAIR_DEBUG
+          if (PB_TID == 0) {
+            S_STATS(S)[jn_ ? 5 : 4] += (double)(clock64() - dbg0_);
+            S_STATS(S)[jn_ ? 7 : 6] += 1.0;
+          }
+#endif
+          pb_pair_leave(jn_);
           PB_T1(S, tr_, 0);
         }
       }

@@ -21,14 +21,28 @@ static_assert(PB_TEAM_SIZE >= PBM_LU_TEAM_MIN, "team smaller than the widest rec
 #ifndef PB_MIN_TEAMS
 #define PB_MIN_TEAMS 1
 #endif
+// Kernels with one team per CTA.  In a PB_PAIR image every barrier looks at the control words in front of the team's
+// shared memory: they are there (and zero) for these kernels as well.
+#if PB_PAIR
+#define PB_SM0 (pb_smem + PB_PAIR_CTRL_DOUBLES)
+#define PB_SMEM_LAUNCH_BYTES (PB_SMEM_BYTES + 8 * PB_PAIR_CTRL_DOUBLES)
+#define PB_ONE_TEAM_PROLOGUE                                                                   \
+  if (threadIdx.x < 2 * PB_PAIR_CTRL_DOUBLES) ((unsigned int*)pb_smem)[threadIdx.x] = 0u;      \
+  __syncthreads();
+#else
+#define PB_SM0 pb_smem
+#define PB_SMEM_LAUNCH_BYTES PB_SMEM_BYTES
+#define PB_ONE_TEAM_PROLOGUE
+#endif
 static __device__ __forceinline__ void pb_solve_body(const pbgpu_launch& L) {
   extern __shared__ double pb_smem[];
   __shared__ unsigned int next_sys;
   pb_sys S;
+  PB_ONE_TEAM_PROLOGUE
 #if PB_GLOBAL_VEC
-  pb_sys_init(S, pb_smem, L.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES, L);
+  pb_sys_init(S, PB_SM0, L.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES, L);
 #else
-  pb_sys_init(S, pb_smem, pb_smem, L);
+  pb_sys_init(S, PB_SM0, PB_SM0, L);
 #if PB_VARS_BATCH > 1
   S.vb = L.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES;
 #endif
@@ -62,6 +76,29 @@ static __device__ __forceinline__ void pb_solve_body(const pbgpu_launch& L) {
 
 extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_solve_kernel(const pbgpu_launch L) { pb_solve_body(L); }
 
+#if PB_PAIR
+// Two teams per CTA (pbgpu_team.cuh, pb_pair_enter): team k of CTA b is global team 2 b + k, with its own slice of the
+// dynamic shared memory (after the control words) and of the global scratch, and pulls systems from the same queue.
+extern "C" __global__ void __launch_bounds__(2 * PB_TEAM_SIZE, 1) pbgpu_solve_kernel_pair(const pbgpu_launch L) {
+  extern __shared__ double pb_smem[];
+  __shared__ unsigned int next_sys2[2];
+  if (threadIdx.x < 2 * PB_PAIR_CTRL_DOUBLES) ((unsigned int*)pb_smem)[threadIdx.x] = 0u;
+  __syncthreads();
+  const int team = PB_TEAM_ID;
+  pb_sys S;
+  pb_sys_init(S, pb_smem + PB_PAIR_CTRL_DOUBLES + (size_t)team * PB_SMEM_DOUBLES,
+              L.scratch + ((size_t)blockIdx.x * 2 + team) * PB_SCRATCH_DOUBLES, L);
+  for (;;) {
+    if (PB_TID == 0) next_sys2[team] = atomicAdd(L.queue, 1u);
+    pb_bar_solo();
+    const unsigned int slot = next_sys2[team];
+    pb_bar_solo();
+    if (slot >= (unsigned int)L.n_sys) break;
+    pb_solve_system(S, L, L.order ? L.order[slot] : (int)slot);
+  }
+}
+#endif
+
 // The same integration under a tighter register cap (PB_MIN_TEAMS_WIDE teams per SM), for one-warp models whose uncapped
 // kernel takes 255 registers: more resident teams win once a batch has more systems than the uncapped kernel keeps
 // resident (SPM, 10 000 sets: +25 %), and lose below that (1 000 sets: -9 %, spills without anything to hide them).
@@ -76,13 +113,14 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS_WIDE) pb
 extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_eval_kernel(const pbgpu_eval_launch E) {
   extern __shared__ double pb_smem[];
   pb_sys S;
-  S.sm = pb_smem;
+  PB_ONE_TEAM_PROLOGUE
+  S.sm = PB_SM0;
 #if PB_GLOBAL_VEC
   S.gv = E.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES;
 #else
-  S.gv = pb_smem;
+  S.gv = PB_SM0;
 #endif
-  S.team.red = pb_smem + PB_OFF_RED;
+  S.team.red = PB_SM0 + PB_OFF_RED;
   S.team.red_phase = 0;
   pb_sys_tables(S);
   for (int sys = blockIdx.x; sys < E.n_sys; sys += gridDim.x) {
@@ -224,10 +262,11 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_e
   extern __shared__ double pb_smem[];
   __shared__ unsigned int next_sys;
   pb_sys S;
+  PB_ONE_TEAM_PROLOGUE
 #if PB_GLOBAL_VEC
-  pb_sys_init(S, pb_smem, L.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES, L);
+  pb_sys_init(S, PB_SM0, L.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES, L);
 #else
-  pb_sys_init(S, pb_smem, pb_smem, L);
+  pb_sys_init(S, PB_SM0, PB_SM0, L);
 #if PB_VARS_BATCH > 1
   S.vb = L.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES;
 #endif
@@ -247,11 +286,12 @@ extern "C" __global__ void __launch_bounds__(PB_TEAM_SIZE, PB_MIN_TEAMS) pbgpu_o
 #if PBM_NVAR > 0
   extern __shared__ double pb_smem[];
   pb_sys S;
-  S.sm = pb_smem;
+  PB_ONE_TEAM_PROLOGUE
+  S.sm = PB_SM0;
 #if PB_GLOBAL_VEC
   S.gv = O.scratch + (size_t)blockIdx.x * PB_SCRATCH_DOUBLES;
 #else
-  S.gv = pb_smem;
+  S.gv = PB_SM0;
 #endif
   for (int sys = blockIdx.x; sys < O.n_sys; sys += gridDim.x) pb_observe_system(S, O, sys);
 #endif
@@ -288,13 +328,13 @@ static int pb_configure(pb_dev_cfg* out, char* err, size_t errlen) {
     *out = g_cfg[dev];
     return 0;
   }
-  e = cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
+  e = cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_LAUNCH_BYTES);
   if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
+    e = cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_LAUNCH_BYTES);
   if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(pbgpu_observe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
+    e = cudaFuncSetAttribute(pbgpu_observe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_LAUNCH_BYTES);
   if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(pbgpu_experiment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
+    e = cudaFuncSetAttribute(pbgpu_experiment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_LAUNCH_BYTES);
   if (e != cudaSuccess) {
     snprintf(err, errlen, "model '%s' needs %d bytes of shared memory per team: %s", PBM_NAME, (int)PB_SMEM_BYTES,
              cudaGetErrorString(e));
@@ -315,7 +355,7 @@ static int pb_configure(pb_dev_cfg* out, char* err, size_t errlen) {
   if (carve_kb > 227) carve_kb = 227;
   const int total_kb = (int)(prop.sharedMemPerMultiprocessor / 1024);
   e = cudaFuncSetAttribute(pbgpu_solve_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c.blocks_per_sm, pbgpu_solve_kernel, PB_TEAM_SIZE, PB_SMEM_BYTES);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c.blocks_per_sm, pbgpu_solve_kernel, PB_TEAM_SIZE, PB_SMEM_LAUNCH_BYTES);
   if (e != cudaSuccess || c.blocks_per_sm < 1) {
     snprintf(err, errlen, "occupancy query failed for model '%s': %s", PBM_NAME, cudaGetErrorString(e));
     return 1;
@@ -336,13 +376,26 @@ static int pb_configure(pb_dev_cfg* out, char* err, size_t errlen) {
   cudaFuncSetAttribute(pbgpu_eval_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   cudaFuncSetAttribute(pbgpu_observe_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   cudaFuncSetAttribute(pbgpu_experiment_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+#if PB_PAIR
+  {
+    const int pair_bytes = 2 * (int)PB_SMEM_BYTES + 8 * PB_PAIR_CTRL_DOUBLES;
+    e = cudaFuncSetAttribute(pbgpu_solve_kernel_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, pair_bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(pbgpu_solve_kernel_pair, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    int bp = 0;
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bp, pbgpu_solve_kernel_pair, 2 * PB_TEAM_SIZE, pair_bytes);
+    if (e != cudaSuccess || bp < 1) {
+      snprintf(err, errlen, "pair kernel of model '%s' does not fit an SM: %s", PBM_NAME, cudaGetErrorString(e));
+      return 1;
+    }
+  }
+#endif
   c.blocks_per_sm_wide = 0;
 #ifdef PB_MIN_TEAMS_WIDE
   if (!getenv("PBGPU_NO_WIDE")) {
-    e = cudaFuncSetAttribute(pbgpu_solve_kernel_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_BYTES);
+    e = cudaFuncSetAttribute(pbgpu_solve_kernel_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM_LAUNCH_BYTES);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(pbgpu_solve_kernel_wide, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     int bw = 0;
-    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bw, pbgpu_solve_kernel_wide, PB_TEAM_SIZE, PB_SMEM_BYTES);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bw, pbgpu_solve_kernel_wide, PB_TEAM_SIZE, PB_SMEM_LAUNCH_BYTES);
     if (e == cudaSuccess && bw > by_carve) bw = by_carve;
     if (e == cudaSuccess && bw > c.blocks_per_sm && !getenv("PBGPU_TEAMS_PER_SM")) {
       c.blocks_per_sm_wide = bw;
@@ -393,6 +446,9 @@ extern "C" int pbgpu_image_plan(int n_sys, int* teams, char* err, size_t errlen)
   pb_dev_cfg c;
   if (pb_configure(&c, err, errlen)) return 1;
   *teams = pb_grid_for(c, n_sys);
+#if PB_PAIR
+  *teams = (*teams + 1) / 2 * 2;     // whole CTAs of two teams (the scratch block has a slot per team)
+#endif
   return 0;
 }
 
@@ -406,14 +462,20 @@ extern "C" int pbgpu_image_launch(const pbgpu_launch* L, void* stream, int grid,
     snprintf(err, errlen, "pbgpu_image_launch: grid %d was not planned for this device", grid);
     return 1;
   }
+#if PB_PAIR
+  static const bool no_pair = getenv("PBGPU_NO_PAIR") != nullptr;
+  if (L->sched.n_steps == 0 && !no_pair && grid % 2 == 0) {
+    pbgpu_solve_kernel_pair<<<grid / 2, 2 * PB_TEAM_SIZE, 2 * PB_SMEM_BYTES + 8 * PB_PAIR_CTRL_DOUBLES, (cudaStream_t)stream>>>(*L);
+  } else
+#endif
   if (L->sched.n_steps > 0) {
-    pbgpu_experiment_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*L);
+    pbgpu_experiment_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_LAUNCH_BYTES, (cudaStream_t)stream>>>(*L);
   } else if (wide) {
 #ifdef PB_MIN_TEAMS_WIDE
-    pbgpu_solve_kernel_wide<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*L);
+    pbgpu_solve_kernel_wide<<<grid, PB_TEAM_SIZE, PB_SMEM_LAUNCH_BYTES, (cudaStream_t)stream>>>(*L);
 #endif
   } else {
-    pbgpu_solve_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*L);
+    pbgpu_solve_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_LAUNCH_BYTES, (cudaStream_t)stream>>>(*L);
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
@@ -497,7 +559,7 @@ extern "C" int pbgpu_image_launch_static(const pbgpu_launch* L, void* stream, in
   // the queue must start at zero; the team slots keep the last call's contents, which no team reads before writing
   cudaError_t e = cudaMemsetAsync(base, 0, sizeof(double) * PB_STATIC_QUEUE_DOUBLES, (cudaStream_t)stream);
   if (e == cudaSuccess) {
-    pbgpu_solve_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(K);
+    pbgpu_solve_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_LAUNCH_BYTES, (cudaStream_t)stream>>>(K);
     e = cudaGetLastError();
   }
   if (e != cudaSuccess) {
@@ -517,7 +579,7 @@ extern "C" int pbgpu_image_eval(const pbgpu_eval_launch* E, void* stream, int gr
     snprintf(err, errlen, "pbgpu_image_eval: grid %d was not planned for this device", grid);
     return 1;
   }
-  pbgpu_eval_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*E);
+  pbgpu_eval_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_LAUNCH_BYTES, (cudaStream_t)stream>>>(*E);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     snprintf(err, errlen, "pbgpu_eval_kernel launch: %s", cudaGetErrorString(e));
@@ -539,7 +601,7 @@ extern "C" int pbgpu_image_observe(const pbgpu_observe_launch* O, void* stream, 
     snprintf(err, errlen, "pbgpu_image_observe: grid %d was not planned for this device", grid);
     return 1;
   }
-  pbgpu_observe_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_BYTES, (cudaStream_t)stream>>>(*O);
+  pbgpu_observe_kernel<<<grid, PB_TEAM_SIZE, PB_SMEM_LAUNCH_BYTES, (cudaStream_t)stream>>>(*O);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     snprintf(err, errlen, "pbgpu_observe_kernel launch: %s", cudaGetErrorString(e));

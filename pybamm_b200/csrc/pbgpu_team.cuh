@@ -50,15 +50,39 @@ PB_FN double pb_team_max(pb_team_ctx&, double x) { return x; }
 #define PB_FN static __device__ __noinline__
 #define PB_RESTRICT __restrict__
 #define PB_TEAM PB_TEAM_SIZE
-#define PB_TID ((int)threadIdx.x)
-#define PB_WARP ((int)(threadIdx.x >> 5))
 #define PB_NWARPS (PB_TEAM_SIZE / 32)
 #define PB_LANE ((int)(threadIdx.x & 31))
 #define PB_LANES 32
+#ifndef PB_PAIR
+#define PB_PAIR 0
+#endif
+#if PB_PAIR
+// Two teams in ONE CTA (pbgpu_solve_kernel_pair): each keeps its own named barrier, and when both are about to run the
+// same large function (generated residual, triangular solves) they run it on the CTA-wide barrier instead -- lock-step
+// stage by stage, so that the second team finds the instructions the first one fetched (see pb_pair_enter).
+// Control words at the start of dynamic shared memory: [0] ticket, [2 + team] 1 while the team is on the joint barrier.
+#define PB_PAIR_CTRL_DOUBLES 8
+extern __shared__ double pb_smem[];
+#define PB_TEAM_ID ((int)(threadIdx.x / PB_TEAM_SIZE))
+#define PB_TID ((int)(threadIdx.x % PB_TEAM_SIZE))
+#define PB_WARP ((int)((threadIdx.x % PB_TEAM_SIZE) >> 5))
+#define PB_PAIR_CTL ((volatile unsigned int*)pb_smem)
+static __device__ __forceinline__ void pb_bar_solo() {
+  asm volatile("bar.sync %0, %1;" ::"r"(1 + PB_TEAM_ID), "n"(PB_TEAM_SIZE) : "memory");
+}
+static __device__ __forceinline__ void pb_bar_team() {
+  if (PB_PAIR_CTL[2 + PB_TEAM_ID]) asm volatile("bar.sync 0, %0;" ::"n"(2 * PB_TEAM_SIZE) : "memory");
+  else pb_bar_solo();
+}
+#define PB_SYNC() pb_bar_team()
+#else
+#define PB_TID ((int)threadIdx.x)
+#define PB_WARP ((int)(threadIdx.x >> 5))
 #if PB_TEAM_SIZE == 32
 #define PB_SYNC() __syncwarp()
 #else
 #define PB_SYNC() __syncthreads()
+#endif
 #endif
 #define PB_SYNCWARP() __syncwarp()
 #define PB_STCG(p, v) __stcg(p, v)   /* L2 only: keep the small L1 for the tables */
@@ -168,7 +192,7 @@ PB_RED_FN double pb_team_sum_buf(double* buf, double x) {
   for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
 #if PB_TEAM_SIZE > 32
   if (PB_LANE == 0) buf[PB_WARP] = x;
-  __syncthreads();
+  PB_SYNC();
   x = buf[0];
 #pragma unroll
   for (int w = 1; w < PB_NWARPS; w++) x += buf[w];
@@ -184,7 +208,7 @@ PB_RED_FN double pb_team_max_buf(double* buf, double x) {
   }
 #if PB_TEAM_SIZE > 32
   if (PB_LANE == 0) buf[PB_WARP] = x;
-  __syncthreads();
+  PB_SYNC();
   x = buf[0];
 #pragma unroll
   for (int w = 1; w < PB_NWARPS; w++) {
