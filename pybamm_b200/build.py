@@ -55,8 +55,8 @@ def _src_digest(paths):
     return h.hexdigest()[:16]
 
 
-def generate(bundle: ModelBundle, dialect: str, outdir=BUILD, tag=""):
-    text, info = codegen.generate(bundle, dialect)
+def generate(bundle: ModelBundle, dialect: str, outdir=BUILD, tag="", extra_samples=None):
+    text, info = codegen.generate(bundle, dialect, extra_samples=extra_samples)
     path = os.path.join(outdir, f"{bundle.name}{tag}_{dialect}.h")
     _write_if_changed(path, text)
     with open(os.path.join(outdir, f"{bundle.name}{tag}_{dialect}.json"), "w") as f:
@@ -108,10 +108,11 @@ def lu_order(bundle: ModelBundle):
 
 
 def build_model(bundle: ModelBundle, force=False, team=None, verbose=False, profile=False, tag="", defines=(), extra_flags=(),
-                gvec=None, min_teams=None):
-    """Generate + nvcc-compile the sm_100a solver image of a bundle. Returns the .so path."""
+                gvec=None, min_teams=None, extra_samples=None):
+    """Generate + nvcc-compile the sm_100a solver image of a bundle. Returns the .so path.
+    extra_samples: see codegen.generate (a re-pivoted image; give it a tag of its own)."""
     os.makedirs(BUILD, exist_ok=True)
-    header, info = generate(bundle, "cuda", BUILD, tag=tag)
+    header, info = generate(bundle, "cuda", BUILD, tag=tag, extra_samples=extra_samples)
     out = os.path.join(BUILD, f"pbgpu_model_{bundle.name}{('_prof' + (str(int(profile)) if int(profile) > 1 else '')) if profile else ''}{tag}.so")
     kernel_srcs = [os.path.join(CSRC, f) for f in ("pbgpu_model.cu", "pbgpu_ida.cuh", "pbgpu_team.cuh")]
     inc = os.path.join(ROOT, "include")

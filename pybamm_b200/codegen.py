@@ -566,11 +566,14 @@ def default_team(n_states: int) -> int:
     return 512      # several thousand states: one team per SM
 
 
-def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None):
+def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None, extra_samples=None):
     """Return (source_text, info dict). The text is a header included by the integrator
-    translation unit (CUDA) or the oracle model shim (C)."""
+    translation unit (CUDA) or the oracle model shim (C).
+    extra_samples: value arrays of J - cj M (bundle entry order) the static pivot order must ALSO be valid for; they come
+    first, so the row matching is taken from them (solver.BatchedIDASolver re-pivots with the matrices of a failed system)."""
     if dialect == "cuda" and sym is None:
-        sym = slu.analyse(bundle.n_states, bundle.jac_rows, bundle.jac_cols, sample_matrices(bundle),
+        samples = [np.asarray(v, float) for v in (extra_samples or [])] + sample_matrices(bundle)
+        sym = slu.analyse(bundle.n_states, bundle.jac_rows, bundle.jac_cols, samples,
                           team=default_team(bundle.n_states))
     progs = model_functions(bundle, sym, dialect)
     n_tmp = max(p.n_tmp for p in progs.values())

@@ -229,7 +229,7 @@ class BatchedIDASolver:
     # options of this front end itself: hermite_interpolation (store dy/dt with the adaptive steps, idaklu_solver.py:318),
     # max_saved_steps (first guess of the adaptive-step capacity; the block is re-sized and the affected rows re-solved
     # when a system takes more steps: the reference grows its arrays instead, IDAKLUSolverOpenMP.inl:608-612)
-    FRONT_END_OPTIONS = {"hermite_interpolation": True, "max_saved_steps": 4096}
+    FRONT_END_OPTIONS = {"hermite_interpolation": True, "max_saved_steps": 4096, "repivot": True}
 
     def __init__(self, model, rtol=1e-4, atol=1e-6, options=None, output_variables=None, device=0,
                  on_failure="warn", image_path=None, devices=None, reuse_buffers=False):
@@ -271,6 +271,11 @@ class BatchedIDASolver:
         from .shard import CostModel
 
         self._cost_model = CostModel()
+        # rows whose integration failed are re-solved once on an image whose static pivot order is also valid for the
+        # matrices of the failed systems (see _repivot); "repivot": False in the options switches it off
+        self.repivot = bool(options.get("repivot", True))
+        self._fallback = None
+        self._is_fallback = False
 
     # -- native handles ---------------------------------------------------------------------
     def _ensure(self):
@@ -402,9 +407,65 @@ class BatchedIDASolver:
                     r[key][over] = sub[key]
             r["n_max"] = n_big
             r["_keep"] = None
+        bad = np.nonzero(np.asarray(r["flag"]) < 0)[0]
+        if len(bad) and self.repivot and not self._is_fallback and r["y_term"] is not None:
+            self._repivot(r, bad, t_eval, t_interp, inputs, y0, yp0, output_mode, want_stats, want_yp)
         if want_stats and r["stats"] is not None:
             self._cost_model.fit(inputs, r["stats"][:, 0])
         return r
+
+    def _repivot(self, r, bad, t_eval, t_interp, inputs, y0, yp0, output_mode, want_stats, want_yp):
+        """Slow path for rows whose integration failed (flag < 0).
+
+        The pivot order of the sparse LU is fixed per image from sample matrices taken around the initial state; KLU in
+        the reference keeps its order between refactorisations too, but factorises afresh when a refactorisation turns out
+        ill-conditioned.  The counterpart here: J - cj M of the failed systems at the states where they failed (evaluated
+        on the device) joins the samples, a second image is generated and compiled for that order (a minute, once; cached
+        by content), and the failed rows are solved again from the start on it.  Rows that fail again keep their flag."""
+        import hashlib
+
+        bad = bad[:16]                                    # a handful of failure states is enough to choose an order
+        yb, pb_ = np.ascontiguousarray(r["y_term"][bad]), np.ascontiguousarray(inputs[bad])
+        tb = np.asarray(r["t_event"])[bad] if r.get("t_event") is not None else np.zeros(len(bad))
+        if not np.all(np.isfinite(yb)):
+            return
+        extra = []
+        for cj in (1.0, 1e-3, 1e3):
+            vals = np.vstack([self.eval("jac", yb[k:k + 1], pb_[k:k + 1], float(tb[k]), cj)[0] for k in range(len(bad))])
+            extra += [v for v in vals if np.all(np.isfinite(v))]
+        if not extra:
+            return
+        if self._fallback is None:
+            tag = "_rp" + hashlib.sha256(np.round(np.asarray(extra), 6).tobytes()).hexdigest()[:10]
+            try:
+                img = build.build_model(self.bundle, tag=tag, extra_samples=extra)
+            except Exception as e:                        # no order is valid for old and new samples alike
+                warnings.warn(f"re-pivoting failed: {e}", stacklevel=3)
+                return
+            fb = BatchedIDASolver(self.bundle, rtol=self.rtol, atol=self.atol, options=dict(self.options),
+                                  output_variables=self.output_variables, device=self.device, on_failure="ignore",
+                                  image_path=img)
+            fb._is_fallback = True
+            self._fallback = fb
+        rows = np.nonzero(np.asarray(r["flag"]) < 0)[0]
+        sub = self._fallback.solve_arrays(t_eval, np.ascontiguousarray(inputs[rows]), t_interp=t_interp if len(t_interp) else None,
+                                          y0=None if y0 is None else y0[rows], output_mode=output_mode, want_stats=want_stats,
+                                          yp0=None if yp0 is None else yp0[rows], want_yp=want_yp)
+        better = np.asarray(sub["flag"]) >= 0
+        if not better.any():
+            return
+        n_keep = min(r["n_max"], sub["n_max"])
+        for key in ("t", "y", "yp"):
+            if r[key] is not None and sub[key] is not None:
+                r[key] = np.array(r[key])
+                r[key][rows[better], :n_keep] = np.asarray(sub[key])[better, :n_keep]
+        for key in ("n_t", "flag", "y_term", "stats", "event_idx", "t_event"):
+            if r[key] is not None and sub[key] is not None:
+                r[key] = np.array(r[key])
+                r[key][rows[better]] = np.asarray(sub[key])[better]
+        r["n_t"][rows[better]] = np.minimum(r["n_t"][rows[better]], n_keep) if sub["n_max"] != r["n_max"] else r["n_t"][rows[better]]
+        r["_keep"] = None
+        r["repivoted_rows"] = rows[better]
 
     def _solve_batch(self, t_eval, t_interp, inputs, y0, yp0, output_mode, n_ret, n_max, want_stats, want_yp):
         n_sys = inputs.shape[0]

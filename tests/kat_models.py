@@ -126,7 +126,22 @@ def hard_ic():
     return _finish(b, "kat_hard_ic", rhs, [g.const(1.0), g.const(5.0)], 1, variables={"v": [v]})
 
 
+def pivot_flip():
+    """A static pivot that dies on the way: u' = -u / 2, 0 = a x + z - 1, 0 = x - z with a = max(2 u - 1, 0) and u(0) = 1,
+    so x = z = 1 / (1 + a).  On the natural diagonal the pivot of x is a: one at t = 0, where the pivot order is chosen,
+    exactly zero from t = 2 ln 2 on (a pivot that merely passes through zero is stepped over).  KLU's refactorisation would
+    notice the condition number and factorise afresh; here the failed system is re-solved on an image whose order is also
+    valid for its matrices (BatchedIDASolver._repivot)."""
+    b = ModelBundle()
+    g = b.graph
+    u, x, z = g.state(0), g.state(1), g.state(2)
+    a = g.binary(ir.MAX, g.sub(g.mul(g.const(2.0), u), g.const(1.0)), g.const(0.0))
+    rhs = [g.mul(g.const(-0.5), u), g.sub(g.add(g.mul(a, x), z), g.const(1.0)), g.sub(x, z)]
+    return _finish(b, "kat_pivot_flip", rhs, [g.const(1.0), g.const(0.5), g.const(0.5)], 1, variables={"x": [x]})
+
+
 ALL = {
+    "kat_pivot_flip": pivot_flip,
     "kat_hard_ic": hard_ic,
     "kat_cccv": cccv_toy,
     "kat_roberts": roberts,

@@ -417,6 +417,26 @@ def test_parity_on_the_baseline_batches(name, n):
     assert par["median_abs_dV_gpu_vs_truth"] <= 3.0 * par["median_abs_dV_oracle_vs_truth"] + 1e-9
 
 
+def test_failed_static_pivot_is_repaired_by_the_repivoted_image():
+    """kat_pivot_flip: the pivot the order was chosen for at t = 0 is exactly zero from t = 2 ln 2 on.  Without the slow path
+    the system fails there; with it (default) the failed row is solved again on an image whose order is also valid for the
+    matrices at the failure state, and lands on the analytic solution x = 1 / (1 + max(2 u - 1, 0)), u = exp(-t / 2)."""
+    b = util.bundle("kat_pivot_flip")
+    t_i = np.linspace(0.0, 4.0, 41)
+    plain = BatchedIDASolver(b, rtol=1e-8, atol=1e-10, output_variables=["x"], options={"repivot": False}, on_failure="ignore")
+    r0 = plain.solve_arrays([0.0, 4.0], np.zeros((3, 0)), t_interp=t_i)
+    assert np.all(r0["flag"] < 0) and np.all(r0["t_event"] < 2.0 * np.log(2.0) + 0.11)
+    s = BatchedIDASolver(b, rtol=1e-8, atol=1e-10, output_variables=["x"], on_failure="ignore")
+    r = s.solve_arrays([0.0, 4.0], np.zeros((3, 0)), t_interp=t_i)
+    assert np.all(r["flag"] == 1), r["flag"]
+    assert sorted(r["repivoted_rows"].tolist()) == [0, 1, 2]
+    n = int(r["n_t"][0])
+    t = r["t"][0, :n]
+    np.testing.assert_allclose(r["y"][0, :n, 0], 1.0 / (1.0 + np.maximum(2.0 * np.exp(-0.5 * t) - 1.0, 0.0)), rtol=0, atol=2e-6)
+    ref = util.oracle("kat_pivot_flip").solve([0.0, 4.0], np.zeros((1, 0)), t_interp=t_i, rtol=1e-8, atol=1e-10, save_vars=True)
+    np.testing.assert_allclose(r["y"][0, :n, 0], ref["y"][0][:, 0], rtol=0, atol=1e-6)
+
+
 def test_config4_thermal_dfn_batch_against_the_oracle():
     """BASELINE config 4: DFN + lumped thermal on 40-point meshes (3 523 states; one 512-thread team per SM, L+U values in shared
     memory, everything streamed in L2), a C-rate sweep of two waves of teams.  Same bars as configs 1-3.  The checker here is the
