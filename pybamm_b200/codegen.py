@@ -355,8 +355,11 @@ def model_functions(bundle, sym: slu.SymbolicLU | None, dialect: str):
     jroots = [g.sub(int(n), cjn) if (r == c and r < bundle.n_diff) else int(n)
               for n, r, c in zip(bundle.jac_nodes, bundle.jac_rows, bundle.jac_cols)]
     progs = {}
+    # models of several thousand states (lumped thermal DFN on fine meshes): the heat-source integral is ONE residual row of
+    # 3 000 operations; its terms go to parallel lanes.  The smaller models keep the code they were measured with.
+    big = dialect == "cuda" and bundle.n_states > 2048
     # the team-parallel dialect splits heavy narrow templates of the residual over the warps (program.build_program)
-    progs["res"] = build_program(g, bundle.rhs_alg, "res", split=(dialect == "cuda" and SPLIT_RES))
+    progs["res"] = build_program(g, bundle.rhs_alg, "res", split=(dialect == "cuda" and SPLIT_RES), split_sums=big)
     if dialect == "cuda":
         progs["jac"] = build_program(g, jroots, "jac", out_index=sym.a_slot, n_out=sym.nnz_lu)
     else:

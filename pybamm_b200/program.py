@@ -32,6 +32,10 @@ MERGE_INPUTS = bool(int(__import__("os").environ.get("PBGPU_MERGE_INPUTS", "1"))
 MATERIALISE_COST = 6      # DFMA-equivalents: shared sub-expressions at least this costly get a tmp slot
 SPLIT_COST = int(__import__("os").environ.get("PBGPU_SPLIT_COST", "120"))   # for functions with few roots: split big trees at nodes at least this costly
 FEW_ROOTS = 64
+BIG_SUM_COST = int(__import__("os").environ.get("PBGPU_BIG_SUM_COST", "1500"))   # expression trees at least this costly have their sums split ...
+SPLIT_SUMS_ALWAYS = bool(int(__import__("os").environ.get("PBGPU_SPLIT_SUMS", "0")))   # A/B switch: also for the models that do not need it
+_BIG_SUM = 10 ** 9
+SUM_TERM_COST = 8                                                                # ... at terms at least this costly
 
 
 @dataclass
@@ -87,8 +91,11 @@ SPLIT_TEMPLATE_COST = 100     # a template at least this costly ...
 SPLIT_TEMPLATE_INST = 64      # ... with at most this many instances is split
 
 
-def build_program(g: ir.Graph, roots, name="f", out_index=None, n_out=None, split=False) -> Program:
-    """roots: node ids; root k is written to out[out_index[k]] (default k)."""
+def build_program(g: ir.Graph, roots, name="f", out_index=None, n_out=None, split=False, split_sums=False) -> Program:
+    """roots: node ids; root k is written to out[out_index[k]] (default k).
+    split_sums: the terms of very large sums become parallel template instances (BIG_SUM_COST)."""
+    global _BIG_SUM
+    _BIG_SUM = BIG_SUM_COST if (split_sums or SPLIT_SUMS_ALWAYS) else 10 ** 9
     prog = _build_program(g, roots, name, out_index, n_out, frozenset())
     if not split:
         return prog
@@ -157,9 +164,15 @@ def _build_program(g: ir.Graph, roots, name, out_index, n_out, forced) -> Progra
         claim(r, (0, k))
     materialised = set()
     few = len(roots) <= FEW_ROOTS
+    sum_term = set()      # nodes that are a term of a sum (argument of an ADD / SUB and not one themselves)
+    _SUM = (ir.ADD, ir.SUB)
     for n in ids[::-1]:
         n = int(n)
         o = owner[n]
+        if op[n] in _SUM:
+            for a in g.args(n):
+                if op[a] not in _SUM:
+                    sum_term.add(a)
         if op[n] not in ir.LEAF_OPS:
             if n in forced and not (o != MULTI and o[0] == 0 and roots[o[1]] == n):
                 materialised.add(n)
@@ -168,6 +181,13 @@ def _build_program(g: ir.Graph, roots, name, out_index, n_out, forced) -> Progra
                 if tc[n] >= MATERIALISE_COST:
                     materialised.add(n)
                     o = (1, n)
+            elif (n in sum_term and tc[n] >= SUM_TERM_COST and op[n] not in _SUM
+                  and tc[roots[o[1]] if o[0] == 0 else o[1]] >= _BIG_SUM):
+                # a term of a very large sum (the x-integral of the heat source in a lumped thermal model: one root, 3 000
+                # operations on one lane while the rest of the team waits): the terms become instances of a shared template
+                # in an earlier stage, the sum itself adds their slots
+                materialised.add(n)
+                o = (1, n)
             elif few and o[0] == 1 and tc[n] >= SPLIT_COST and op[n] in _TRANSCENDENTAL:
                 materialised.add(n)
                 o = (1, n)
