@@ -241,6 +241,7 @@ struct pb_sys {
 // lives in shared memory.
 #define PB_F_END 1u
 #define PB_F_BWD 2u
+#define PB_F_CHAINS 2u   /* factor stream: the chain record (no direction there) */
 #define PB_F_TEAM 4u
 #define PB_F_GROUP 8u
 
@@ -263,6 +264,36 @@ struct pb_sys {
 #define PB_FAC_STAGE 0
 #endif
 
+// The bidiagonal chains, one lane per chain, before every level (symbolic_lu._build): words r0 | K << 16 and L0 | U0 << 16;
+// the diagonal of row i is slot i, the L and U entries of a chain sit in consecutive slots.  Out of line and without
+// register arrays on purpose: it runs once per factorisation, and a larger frame of the solve kernel costs everywhere (a
+// first version with batched loads doubled the kernel's stack and slowed the whole DFN integration by 11 %).
+#ifdef PB_EMU
+static void pb_lu_factor_chains(double* lu, const unsigned int* body, const int nt, double& bad) {
+#else
+static __device__ __noinline__ void pb_lu_factor_chains(double* PB_RESTRICT lu, const unsigned int* PB_RESTRICT body, const int nt,
+                                                        double& bad) {
+#endif
+  for (int q = PB_TID; q < nt; q += PB_TEAM) {
+    const unsigned int h = PB_FAC_LD(body[q]), sl = PB_FAC_LD(body[nt + q]);
+    const int r0 = (int)(h & 0xFFFFu), K = (int)(h >> 16);
+    double* l = lu + (sl & 0xFFFFu) - 1;       // l[k] = L(r0 + k, r0 + k - 1)
+    const double* u = lu + (sl >> 16) - 1;     // u[k] = U(r0 + k - 1, r0 + k)
+    double* d = lu + r0;
+    double inv = 1.0 / d[0];
+    if (!(fabs(inv) <= 1.7e308) || d[0] == 0.0) bad = 1.0;
+    d[0] = inv;
+    for (int k = 1; k < K; k++) {
+      const double lk = l[k] * inv;
+      const double acc = d[k] - lk * u[k];
+      inv = 1.0 / acc;
+      if (!(fabs(inv) <= 1.7e308) || acc == 0.0) bad = 1.0;
+      l[k] = lk;
+      d[k] = inv;
+    }
+  }
+}
+
 // One record of the factor stream at st[off] (meta already fetched). Returns the offset of the next record.
 static PB_DEV int pb_lu_factor_record(double* PB_RESTRICT lu, const unsigned int* PB_RESTRICT st, const int off,
                                       const unsigned int meta, double& bad) {
@@ -270,6 +301,11 @@ static PB_DEV int pb_lu_factor_record(double* PB_RESTRICT lu, const unsigned int
   const unsigned int fl = meta >> 28;
   const int base = off + 1;
   const int wide = (fl & PB_F_TEAM) != 0;
+  if (fl & PB_F_CHAINS) {
+    pb_lu_factor_chains(lu, st + base, nt, bad);
+    PB_SYNC();
+    return base + nt * (1 + ml);
+  }
   if (fl & PB_F_GROUP) {   // narrow level, few long tasks: warp 0, 32/nt lanes per task
     if (PB_WARP == 0) {
 #ifndef PB_EMU

@@ -96,6 +96,7 @@ class SymbolicLU:
     t_ops: dict = None                 # row -> [(slot, w index)]: solve-form backward coupling T = -P U_C,anc
     dense_rows: list = None            # rows of the dense top block T (ascending), or None
     dense_slots: np.ndarray = None     # (nT, nT) slot of L/U entry (row, col) of the block, nnz_lu where structurally zero
+    factor_chains: list = None         # (first row, rows, first L slot, first U slot) of the chains factorised by the chain record
 
     def summary(self):
         return (f"n={self.n} nnz_lu={self.nnz_lu} ordering={self.ordering} streams: solve {len(self.solve_stream)} words/"
@@ -489,6 +490,19 @@ def _build(n, rows, cols, perm_r, perm_c, name, team=128, symmetrise=False) -> S
     for k in range(n):
         for j in Urows[k]:
             Ucol[j].append(k)
+    # Bidiagonal chains (the radial particle chains: 40 x 18 rows in the DFN) are factorised by ONE record that runs before
+    # every level, one lane per chain: d_0 = 1 / a_00, then l_k = a_{k,k-1} d_{k-1}, d_k = 1 / (a_kk - l_k u_{k-1,k}) down the
+    # chain.  Level-scheduled they were two dependency levels per row -- a quarter of the ~200 records of a DFN
+    # factorisation, each about 1 100 cycles of latency however few tasks it holds.  Same operations in the same order,
+    # bit-identical values.  PBGPU_FACTOR_CHAINS=0 keeps them in the levels (A/B).
+    chain_rows = {}
+    factor_chains = []      # (first row, rows, slot of the first L entry, slot of the first U entry)
+    if os.environ.get("PBGPU_FACTOR_CHAINS", "1") != "0":
+        for c, rws in enumerate(clusters):
+            if kinds[c] == "chain" and len(rws) >= 2:
+                for k, i in enumerate(rws):
+                    chain_rows[i] = k
+                factor_chains.append((rws[0], len(rws), slot_of[(rws[1], rws[0])], slot_of[(rws[0], Urows[rws[0]][1])]))
     # factor tasks with levels
     level = {}
     tasks_by_level = {}
@@ -496,6 +510,12 @@ def _build(n, rows, cols, perm_r, perm_c, name, team=128, symmetrise=False) -> S
     for i in range(n):
         row_entries = [(i, j) for j in Lrows[i]] + [(i, j) for j in Urows[i]]
         for (_, j) in row_entries:
+            if i in chain_rows and j <= i:
+                # done by the chain record, which runs before level 0 (the U entry of a chain row stays a plain entry)
+                assert (j == i or (j == i - 1 and chain_rows[i] >= 1)) and (chain_rows[i] >= 1 or not Lrows[i])
+                level[(i, j)] = -1
+                flops += 2
+                continue
             m = min(i, j)
             pairs = []
             lv = 0
@@ -566,7 +586,7 @@ def _build(n, rows, cols, perm_r, perm_c, name, team=128, symmetrise=False) -> S
     return build_streams(SymbolicLU(n, nnz_lu, np.asarray(perm_r), np.asarray(perm_c), slot_of, a_slot, diag_slot,
                                     factor, fwd, bwd, flops, sflops, name, Lrows=Lrows, Urows=Urows,
                                     clusters=clusters, cl=cl, inv_cluster=inv_cluster, cluster_kind=kinds,
-                                    s_ops=s_ops, t_ops=t_ops, dense_rows=dense_rows,
+                                    s_ops=s_ops, t_ops=t_ops, dense_rows=dense_rows, factor_chains=factor_chains,
                                     dense_slots=None if dense_rows is None else np.array(
                                         [[slot_of.get((i, k), nnz_lu) for k in dense_rows] for i in dense_rows], np.int64)),
                          team=team)
@@ -602,6 +622,7 @@ def _validate(s: SymbolicLU, rows, cols, vals):
 #   factor task  = out_slot | aux << 16             operand = lu_slot_a | lu_slot_b << 16
 # Padding operands are (zero slot nnz_lu, zero index n / zero slot nnz_lu).
 F_END, F_BWD, F_TEAM, F_GROUP = 1, 2, 4, 8
+F_CHAINS = F_BWD      # factor stream only (its records have no direction): the chain record, see _build
 MAX_GROUPS = 3
 
 
@@ -699,6 +720,13 @@ def build_streams(s: SymbolicLU, team=128):
     build_seq_solve_stream(s, team)
 
     words, nrec, cyc = [], 0, 0
+    if s.factor_chains:
+        # chain record: [nt | 1 << 16 | flags << 28] then nt words r0 | K << 16 and nt words L0 | U0 << 16 (one lane per chain)
+        nt = len(s.factor_chains)
+        words.append(nt | (1 << 16) | ((F_CHAINS | F_TEAM | F_END) << 28))
+        words += [r0 | (K << 16) for r0, K, l0, u0 in s.factor_chains]
+        words += [l0 | (u0 << 16) for r0, K, l0, u0 in s.factor_chains]
+        nrec, cyc = 1, 45 + 90 * max(K for _, K, _, _ in s.factor_chains)   # same scale as two levels per row
     nlev = s.factor.n_levels
     sizes = [int(s.factor.lev_meta[lv][1]) for lv in range(nlev)]
     for lv in range(nlev):
@@ -1172,6 +1200,18 @@ def stream_factor(s: SymbolicLU, a_vals):
     np.add.at(lu, s.a_slot, a_vals)
     st = s.factor_stream
     for off, nt, ml, fl in _walk(st):
+        if fl & F_CHAINS:
+            for q in range(nt):
+                h, sl = int(st[off + 1 + q]), int(st[off + 1 + nt + q])
+                r0, K, l0, u0 = h & 0xFFFF, h >> 16, sl & 0xFFFF, sl >> 16
+                inv = 1.0 / lu[r0]
+                lu[r0] = inv
+                for k in range(1, K):
+                    l = lu[l0 + k - 1] * inv
+                    lu[l0 + k - 1] = l
+                    inv = 1.0 / (lu[r0 + k] - l * lu[u0 + k - 1])
+                    lu[r0 + k] = inv
+            continue
         tw = st[off + 1:off + 1 + nt].astype(np.int64)
         out, aux = tw & 0xFFFF, tw >> 16
         acc = np.where(aux == AUX_NEG, 0.0, lu[out])
