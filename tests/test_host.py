@@ -166,3 +166,28 @@ def test_sharded_solve_world_size_2_gloo(tmp_path):
                         "127.0.0.1", "--master-port", "29513", str(script)], capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "GLOO_OK 2" in r.stdout
+
+
+def test_solution_batch_is_a_lazy_list_like_view_of_the_batch_arrays():
+    # what solve(inputs=[...]) returns: len / index / negative index / slice / iteration like the reference's list, Solution
+    # objects made on access (and kept), all of them views into the arrays of the batch
+    from pybamm_b200.solver import IDA_ROOT_RETURN, Solution, SolutionBatch
+
+    n, n_max = 5, 4
+    arrays = dict(t=np.arange(n * n_max, dtype=float).reshape(n, n_max), y=np.ones((n, n_max, 1)) * np.arange(n)[:, None, None],
+                  yp=None, n_t=np.array([4, 3, 9, 1, 2], np.int32), n_max=n_max, flag=np.array([1, IDA_ROOT_RETURN, 1, -3, IDA_ROOT_RETURN], np.int32),
+                  y_term=np.zeros((n, 3)), stats=np.zeros((n, 8), np.int64), event_idx=np.array([-1, 1, -1, -1, 0], np.int32),
+                  t_event=np.zeros(n))
+    inputs = [{"p": float(i)} for i in range(n)]
+    sols = SolutionBatch(arrays, inputs, {"v": slice(0, 1)}, ["low", "high"])
+    assert len(sols) == n and not sols._made
+    s1 = sols[1]
+    assert isinstance(s1, Solution) and sols[1] is s1 and list(sols._made) == [1]
+    assert s1.termination == "event: high" and s1.all_inputs == [inputs[1]] and len(s1.t) == 3
+    assert np.shares_memory(s1.t, arrays["t"]) and np.shares_memory(s1["v"], arrays["y"])
+    assert len(sols[2].t) == n_max                       # more points produced than stored: clipped to the block
+    assert sols[-1].termination == "event: low" and sols[3].termination == "failure"
+    assert [s.flag for s in sols[1:4]] == [IDA_ROOT_RETURN, 1, -3]
+    assert [float(s["v"][0, 0]) for s in sols] == [0.0, 1.0, 2.0, 3.0, 4.0]
+    with pytest.raises(IndexError):
+        sols[n]
