@@ -309,6 +309,9 @@ class BatchedIDASolver:
         self._lib, self._model, self._solver, self._solvers, self.desc = lib, mh, handles[0], handles, desc
 
     def close(self):
+        if getattr(self, "_fallback", None) is not None:
+            self._fallback.close()
+            self._fallback = None
         if self._solver is not None:
             for h in self._solvers:
                 self._lib.pbgpu_solver_destroy(h)
