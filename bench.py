@@ -356,8 +356,20 @@ def run_b200_arm(args):
     if world > 1:
         import torch.distributed as dist
 
-        os.environ.setdefault("NCCL_DEBUG", "WARN")   # no "NCCL version" banner on stdout: rank 0 prints ONE line, the JSON
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # rank 0 prints ONE line on stdout, the JSON: NCCL's "NCCL version ..." banner (written to file descriptor 1 when the
+        # first communicator comes up) goes to stderr instead
+        sys.stdout.flush()
+        saved_fd = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            warm = torch.zeros(1, device=torch.device("cuda", local_rank))
+            dist.all_reduce(warm)
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_fd, 1)
+            os.close(saved_fd)
 
     from pybamm_b200 import BatchedIDASolver, build
     from pybamm_b200.host import Result, canonical_time_grids
