@@ -55,6 +55,9 @@ _BIN = {
 }
 
 
+# one-warp teams: the templates of a stage as plain loops instead of the tile dispatch (A/B switch)
+ONE_WARP_LOOPS = bool(int(__import__("os").environ.get("PBGPU_ONE_WARP_LOOPS", "1")))
+
 # ops that compile to a call of an out-of-line libm copy (pbgpu_team.cuh) and can be issued 2 or 4 at a time (PB_B2 / PB_B4)
 _BATCH_UN = {ir.EXP: "exp", ir.LOG: "log", ir.TANH: "tanh", ir.SINH: "sinh", ir.COSH: "cosh", ir.ASINH: "asinh", ir.SQRT: "sqrt"}
 # Measured and left off (default 1): libdevice's exp / log / tanh branch on their argument ranges, so the copies inside a
@@ -265,7 +268,7 @@ def _emit_template(em: _Emitter, tp, dest, lines, ind):
     lines.append(f"{ind}PB_PAD")        # empty; the code-size sensitivity experiment defines it as a run of NOPs
 
 
-def emit_program(prog: Program, fname: str, prefix: str, batch=False, multi=False):
+def emit_program(prog: Program, fname: str, prefix: str, batch=False, multi=False, one_warp=False):
     """Return (tables_text, function_text).  batch: issue independent libm calls 2 / 4 at a time (PB_B2 / PB_B4).
     multi: the function evaluates ``npts`` points at once, (instance, point) pairs spread over the lanes -- for the output
     variables of one-warp models, whose long scalar expressions leave 31 lanes idle (pbgpu_ida.cuh, PB_VARS_BATCH):
@@ -307,11 +310,13 @@ def emit_program(prog: Program, fname: str, prefix: str, batch=False, multi=Fals
             L.append("  PB_SYNC();")
         if nt == 0:
             continue
-        if len(tpls) == 1:
-            t, dest = tpls[0]
-            L.append(f"  for (int q = PB_TID; q < {t.n_inst}; q += PB_TEAM) {{")
-            _emit_template(em, t, dest, L, "    ")
-            L.append("  }")
+        if len(tpls) == 1 or one_warp:
+            # one template, or a one-warp team (its warp would take every tile anyway): plain loops, no dispatch tables
+            for k in order:
+                t, dest = tpls[k]
+                L.append(f"  for (int q = PB_TID; q < {t.n_inst}; q += PB_TEAM) {{")
+                _emit_template(em, t, dest, L, "    ")
+                L.append("  }")
             continue
         # tile dispatch tables: warp-uniform look-ups on the critical path of every tile -> constant memory
         ttp = em.table("unsigned char" if len(tpls) < 256 else "unsigned short", tiles_tp, "tt", qual="PB_CTABLE")
@@ -628,7 +633,8 @@ def generate(bundle, dialect="cuda", sym: slu.SymbolicLU | None = None, extra_sa
     out.append(f"#define PBM_NVAR {n_var}")
     info = dict(n_tmp=n_tmp, n_var=n_var, table_bytes=0, programs={})
     for key in ("res", "jac", "events", "ic", "vars"):
-        tabs, fn, tb = emit_program(progs[key], f"pbm_{key}", f"pbm_{key}", batch=(dialect == "cuda"))
+        tabs, fn, tb = emit_program(progs[key], f"pbm_{key}", f"pbm_{key}", batch=(dialect == "cuda"),
+                                    one_warp=(dialect == "cuda" and ONE_WARP_LOOPS and default_team(bundle.n_states) == 32))
         out.append(tabs)
         out.append(fn)
         info["table_bytes"] += tb
