@@ -1282,6 +1282,16 @@ static PB_DEV void pb_align(pb_sys& S) {
 #define pb_align(S) ((void)0)
 #endif
 
+// x^y of the step-size and convergence-rate formulas (x > 0): through the out-of-line exp / log the generated functions
+// already keep resident, instead of another 150 instructions of libdevice pow() on the path of every step (the kernels are
+// bound by instruction fetch).  SPM x 1 000: 135.4k -> 147.7k, x 10 000: 170k -> 185.7k, DFN 5 297 -> 5 385 sims/s.  The last
+// bits of the step sizes differ from pow()'s; -DPB_POW_LIBM restores it.
+#if !defined(PB_POW_LIBM) && !defined(PB_EMU)
+#define PB_IPOW(x, y) PB_EXP((y) * PB_LOG(x))
+#else
+#define PB_IPOW(x, y) pow(x, y)
+#endif
+
 // ---- two teams of one CTA in lock-step through the large functions (PB_PAIR) -------------------------------------------
 // The integration is bound by instruction fetch: the generated residual alone is 45 KB of code against a 32 KB instruction
 // cache, and a team runs it 1.7x slower beside a neighbour that executes other code.  Two separate CTAs cannot be held
@@ -1515,7 +1525,7 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
           oldnrm = delnrm;
           if (delnrm <= 1e-4 * S.toldel) retval = PB_NLS_SUCCESS;
         } else {
-          const double rate = pow(delnrm / oldnrm, 1.0 / mnewt);
+          const double rate = PB_IPOW(delnrm / oldnrm, 1.0 / mnewt);
           if (rate > 0.9) {
             retval = PB_NLS_CONV_RECVR;
             break;
@@ -1637,7 +1647,7 @@ static PB_DEV int pb_handle_nflag(pb_sys& S, int nflag, double err_k, double err
   if (*nef == 1) {
     const double err_knew = (S.kk == S.knew) ? err_k : err_km1;
     S.kk = S.knew;
-    S.rr = 0.9 * pow(2.0 * err_knew + 0.0001, -1.0 / (S.kk + 1));
+    S.rr = 0.9 * PB_IPOW(2.0 * err_knew + 0.0001, -1.0 / (S.kk + 1));
     S.rr = fmax(0.25, fmin(0.9, S.rr));
     S.hh *= S.rr;
     return PB_PREDICT_AGAIN;
@@ -1719,7 +1729,7 @@ static PB_DEV void pb_complete_step(pb_sys& S, double err_k, double err_km1) {
       err_knew = err_k;
     }
     double hnew = S.hh;
-    S.rr = pow(2.0 * err_knew + 0.0001, -1.0 / (S.kk + 1));
+    S.rr = PB_IPOW(2.0 * err_knew + 0.0001, -1.0 / (S.kk + 1));
     if (S.rr >= 2.0) {
       hnew = 2.0 * S.hh;
       const double tmp = fabs(hnew) * S.hmax_inv;
