@@ -38,6 +38,17 @@
 
 #define PB_NEV_PAD ((PBM_NEV > 0) ? PBM_NEV : 1)
 
+// Scalar divisions and square roots of the step / order control: the shared out-of-line copies (PB_DIV, PB_SQRT) instead of an
+// inline expansion of twenty-odd instructions at every site (-DPB_SCALAR_INLINE: the plain operators).
+#ifdef PB_SCALAR_INLINE
+#define PB_IDIV(a, b) ((a) / (b))
+#define PB_RMS(s) sqrt((s) / PBM_N)
+#else
+#define PB_IDIV(a, b) PB_DIV(a, b)
+#define PB_RMS(s) PB_SQRT(PB_DIV(s, (double)PBM_N))
+#endif
+
+
 // ---- memory layout (in doubles) ---------------------------------------------------------------------
 // Shared memory always holds what is accessed at random inside the latency-critical loops: y (stencil reads of the
 // generated functions), delta / w (triangular solves), the L+U values, small temporaries, the packed solve stream.
@@ -1038,7 +1049,7 @@ static PB_DEV double pb_wrms(pb_sys& S, const double* PB_RESTRICT x) {
     const double v = xv[k] * ev[k];
     acc += v * v;
   }
-  return sqrt(pb_team_sum(S.team, acc) / PBM_N);
+  return PB_RMS(pb_team_sum(S.team, acc));
 }
 
 // ewt_i = 1 / (rtol |y_i| + atol_i); returns non-zero if a weight is not positive. Ends with a barrier.
@@ -1078,7 +1089,7 @@ static PB_DEV double pb_ewt_set_norm(pb_sys& S, const double* y) {
     acc += v * v;
   }
   PB_SYNC();
-  return sqrt(pb_team_sum(S.team, acc) / PBM_N);
+  return PB_RMS(pb_team_sum(S.team, acc));
 }
 
 // ---- interpolation (IDAGetSolution / IDAGetDky k=0,1) ------------------------------------------
@@ -1194,23 +1205,23 @@ void pb_set_coeffs_t0(double* coef, const int kk, const int ns, const double hh)
     for (int i = 1; i <= kk; i++) {
       const double temp2 = psi[i - 1];
       psi[i - 1] = temp1;
-      beta[i] = beta[i - 1] * psi[i - 1] / temp2;
+      beta[i] = PB_IDIV(beta[i - 1] * psi[i - 1], temp2);
       temp1 = temp2 + hh;
-      alpha[i] = hh / temp1;
+      alpha[i] = PB_IDIV(hh, temp1);
       sigma[i] = i * sigma[i - 1] * alpha[i];
-      gamma[i] = gamma[i - 1] + alpha[i - 1] / hh;
+      gamma[i] = gamma[i - 1] + PB_IDIV(alpha[i - 1], hh);
     }
     psi[kk] = temp1;
   }
   double alphas = 0.0, alpha0 = 0.0;
 #pragma unroll 1
   for (int i = 0; i < kk; i++) {
-    alphas -= 1.0 / (i + 1);
+    alphas -= PB_IDIV(1.0, (double)(i + 1));
     alpha0 -= alpha[i];
   }
   double c = fabs(alpha[kk] + alphas - alpha0);
   if (alpha[kk] > c) c = alpha[kk];
-  coef[30] = -alphas / hh;
+  coef[30] = PB_IDIV(-alphas, hh);
   coef[31] = c;
 }
 static PB_DEV void pb_set_coeffs(pb_sys& S, double* ck) {
@@ -1358,7 +1369,7 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
     S.ss = 20.0;
     callLSetup = 1;
   }
-  S.cjratio = S.cj / S.cjold;
+  S.cjratio = PB_IDIV(S.cj, S.cjold);
   {
     const double temp1 = (1.0 - 0.25) / (1.0 + 0.25), temp2 = 1.0 / temp1;
     if (S.cjratio < temp1 || S.cjratio > temp2) callLSetup = 1;
@@ -1479,7 +1490,7 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
           pb_pair_leave(jn_);
           PB_T1(S, ts_, 1);
         }
-        const double scale = (S.scalesol && S.cjratio != 1.0) ? 2.0 / (1.0 + S.cjratio) : 1.0;
+        const double scale = (S.scalesol && S.cjratio != 1.0) ? PB_IDIV(2.0, 1.0 + S.cjratio) : 1.0;
         double acc = 0.0;
         {
 #if PB_GLOBAL_VEC
@@ -1515,7 +1526,7 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
 #endif
         }
         PB_SYNC();
-        const double delnrm = sqrt(pb_team_sum(S.team, acc) / PBM_N);
+        const double delnrm = PB_RMS(pb_team_sum(S.team, acc));
         retval = -99;
         if (!(delnrm == delnrm)) {
           retval = PB_NLS_CONV_RECVR;
@@ -1525,12 +1536,12 @@ static PB_DEV int pb_nls_impl(pb_sys& S) {
           oldnrm = delnrm;
           if (delnrm <= 1e-4 * S.toldel) retval = PB_NLS_SUCCESS;
         } else {
-          const double rate = PB_IPOW(delnrm / oldnrm, 1.0 / mnewt);
+          const double rate = PB_IPOW(PB_IDIV(delnrm, oldnrm), PB_IDIV(1.0, (double)mnewt));
           if (rate > 0.9) {
             retval = PB_NLS_CONV_RECVR;
             break;
           }
-          S.ss = rate / (1.0 - rate);
+          S.ss = PB_IDIV(rate, 1.0 - rate);
         }
         if (retval != PB_NLS_SUCCESS && S.ss * delnrm <= S.epsNewt) retval = PB_NLS_SUCCESS;
         if (retval == PB_NLS_SUCCESS) return PB_NLS_SUCCESS;
@@ -1612,15 +1623,15 @@ static PB_DEV int pb_test_error(pb_sys& S, double ck, double* err_k, double* err
       }
     }
   }
-  const double enorm_k = sqrt(pb_team_sum(S.team, a0) / PBM_N);
+  const double enorm_k = PB_RMS(pb_team_sum(S.team, a0));
   *err_k = sigma[kk] * enorm_k;
   const double terr_k = (kk + 1) * (*err_k);
   S.knew = kk;
   if (kk > 1) {
-    *err_km1 = sigma[kk - 1] * sqrt(pb_team_sum(S.team, a1) / PBM_N);
+    *err_km1 = sigma[kk - 1] * PB_RMS(pb_team_sum(S.team, a1));
     const double terr_km1 = kk * (*err_km1);
     if (kk > 2) {
-      const double err_km2 = sigma[kk - 2] * sqrt(pb_team_sum(S.team, a2) / PBM_N);
+      const double err_km2 = sigma[kk - 2] * PB_RMS(pb_team_sum(S.team, a2));
       const double terr_km2 = (kk - 1) * err_km2;
       if (fmax(terr_km1, terr_km2) <= terr_k) S.knew = kk - 1;
     } else if (terr_km1 <= 0.5 * terr_k) {
@@ -1647,7 +1658,7 @@ static PB_DEV int pb_handle_nflag(pb_sys& S, int nflag, double err_k, double err
   if (*nef == 1) {
     const double err_knew = (S.kk == S.knew) ? err_k : err_km1;
     S.kk = S.knew;
-    S.rr = 0.9 * PB_IPOW(2.0 * err_knew + 0.0001, -1.0 / (S.kk + 1));
+    S.rr = 0.9 * PB_IPOW(2.0 * err_knew + 0.0001, PB_IDIV(-1.0, (double)(S.kk + 1)));
     S.rr = fmax(0.25, fmin(0.9, S.rr));
     S.hh *= S.rr;
     return PB_PREDICT_AGAIN;
@@ -1707,8 +1718,8 @@ static PB_DEV void pb_complete_step(pb_sys& S, double err_k, double err_km1) {
           acc += v * v;
         }
       }
-      const double enorm = sqrt(pb_team_sum(S.team, acc) / PBM_N);
-      err_kp1 = enorm / (S.kk + 2);
+      const double enorm = PB_RMS(pb_team_sum(S.team, acc));
+      err_kp1 = PB_IDIV(enorm, (double)(S.kk + 2));
       const double terr_k = (S.kk + 1) * err_k, terr_kp1 = (S.kk + 2) * err_kp1;
       if (S.kk == 1) {
         action = (terr_kp1 >= 0.5 * terr_k) ? 2 : 3;
@@ -1729,7 +1740,7 @@ static PB_DEV void pb_complete_step(pb_sys& S, double err_k, double err_km1) {
       err_knew = err_k;
     }
     double hnew = S.hh;
-    S.rr = PB_IPOW(2.0 * err_knew + 0.0001, -1.0 / (S.kk + 1));
+    S.rr = PB_IPOW(2.0 * err_knew + 0.0001, PB_IDIV(-1.0, (double)(S.kk + 1)));
     if (S.rr >= 2.0) {
       hnew = 2.0 * S.hh;
       const double tmp = fabs(hnew) * S.hmax_inv;
