@@ -40,6 +40,11 @@
 
 // Scalar divisions and square roots of the step / order control: the shared out-of-line copies (PB_DIV, PB_SQRT) instead of an
 // inline expansion of twenty-odd instructions at every site (-DPB_SCALAR_INLINE: the plain operators).
+#ifdef PB_VECTOR_DIV_INLINE   /* the divisions of the error-weight pass and of the factorisation: out of line as well (DFN 5 562 -> 5 609) */
+#define PB_VDIV(a, b) ((a) / (b))
+#else
+#define PB_VDIV(a, b) PB_DIV(a, b)
+#endif
 #ifdef PB_SCALAR_INLINE
 #define PB_IDIV(a, b) ((a) / (b))
 #define PB_RMS(s) sqrt((s) / PBM_N)
@@ -342,7 +347,7 @@ static PB_DEV int pb_lu_factor_record(double* PB_RESTRICT lu, const unsigned int
         if (aux == PB_AUX_U || aux == PB_AUX_NEG) {
           lu[out] = acc;
         } else if (aux == PB_AUX_DIAG) {
-          const double inv = 1.0 / acc;
+          const double inv = PB_VDIV(1.0, acc);
           if (!(fabs(inv) <= 1.7e308) || acc == 0.0) bad = 1.0;
           lu[out] = inv;
         } else {
@@ -362,7 +367,7 @@ static PB_DEV int pb_lu_factor_record(double* PB_RESTRICT lu, const unsigned int
         if (aux == PB_AUX_U || aux == PB_AUX_NEG) {
           lu[out] = acc;
         } else if (aux == PB_AUX_DIAG) {
-          const double inv = 1.0 / acc;
+          const double inv = PB_VDIV(1.0, acc);
           if (!(fabs(inv) <= 1.7e308) || acc == 0.0) bad = 1.0;
           lu[out] = inv;
         } else {
@@ -403,7 +408,7 @@ static PB_DEV int pb_lu_factor_record(double* PB_RESTRICT lu, const unsigned int
       if (aux == PB_AUX_U || aux == PB_AUX_NEG) {
         lu[out] = acc;
       } else if (aux == PB_AUX_DIAG) {
-        const double inv = 1.0 / acc;
+        const double inv = PB_VDIV(1.0, acc);
         if (!(fabs(inv) <= 1.7e308) || acc == 0.0) bad = 1.0;
         lu[out] = inv;
       } else {
@@ -1064,7 +1069,7 @@ static PB_DEV int pb_ewt_set(pb_sys& S, const double* y) {
   PB_VEC_FOR(k, i) {
     const double w = S.rtol * fabs(yv[k]) + av[k];
     if (!(w > 0.0)) bad = 1.0;
-    if (i < PBM_N) ewt[i] = 1.0 / w;
+    if (i < PBM_N) ewt[i] = PB_VDIV(1.0, w);
   }
   PB_SYNC();
   return pb_team_max(S.team, bad) != 0.0;
@@ -1083,7 +1088,7 @@ static PB_DEV double pb_ewt_set_norm(pb_sys& S, const double* y) {
   PB_VEC_FOR(k, i) {
     const double w = S.rtol * fabs(yv[k]) + av[k];
     if (!(w > 0.0)) acc = PB_NAN;
-    const double e = 1.0 / w;
+    const double e = PB_VDIV(1.0, w);
     if (i < PBM_N) ewt[i] = e;
     const double v = yv[k] * e;
     acc += v * v;
